@@ -1,0 +1,304 @@
+"""g.p.u-pathtracer_b200 -- Python host mirror of the C-ABI in include/gpt.h.
+
+Thin ctypes layer over ``libgpt_b200.so`` (hand-written sm_100a CUDA, built in-tree by
+``g.p.u-pathtracer_b200/Makefile``).  Names follow the reference: ``kernelInfo`` / ``CamInfo`` /
+``BVHData`` / ``Sphere`` (GpuPathTracer/CpuStructs.hpp:19-72, CommomStructs.hpp:11-48) and
+``BasicScene.launchKernel`` (GpuPathTracer/tracer.cu:405-415, BasicScene.cpp:368-477).
+
+PyTorch is used only as plumbing (device buffers, streams, torch.distributed); all rendering
+happens inside the shared library.  There is no CPU or PyTorch fallback: a missing library or a
+missing GPU raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgpt_b200.so")
+
+# enums: CommomStructs.hpp:11-12 (order is ABI)
+TRI, SPHERE, BOX, NONE = 0, 1, 2, 3
+DIFF, METAL, SPEC, REFR = 0, 1, 2, 3
+
+FLAG_NO_JITTER = 1 << 0
+FLAG_METAL_FIXED = 1 << 1
+FLAG_WAVEFRONT = 1 << 2
+FLAG_COUNT_BOUNCES = 1 << 3
+
+
+class GptError(RuntimeError):
+    pass
+
+
+class Sphere(C.Structure):  # CommomStructs.hpp:18-39
+    _fields_ = [("posRad", C.c_float * 4), ("emi", C.c_float * 3), ("col", C.c_float * 3), ("mat", C.c_int32)]
+
+
+class Box(C.Structure):  # CommomStructs.hpp:42-48
+    _fields_ = [("mn", C.c_float * 3), ("mx", C.c_float * 3), ("emi", C.c_float * 3), ("col", C.c_float * 3), ("mat", C.c_int32)]
+
+
+class CamInfo(C.Structure):  # CpuStructs.hpp:19-29
+    _fields_ = [("front", C.c_float * 3), ("right", C.c_float * 3), ("up", C.c_float * 3), ("pos", C.c_float * 3),
+                ("dist", C.c_float), ("pitch", C.c_float), ("yaw", C.c_float), ("aspect", C.c_float), ("fov", C.c_float),
+                ("dirty", C.c_uint8), ("_pad0", C.c_uint8 * 3), ("bias", C.c_float * 2),
+                ("enabled", C.c_uint8), ("_pad1", C.c_uint8 * 3)]
+
+
+class BVHData(C.Structure):  # CpuStructs.hpp:31-42
+    _fields_ = [("dev_triNode", C.c_void_p), ("triNodeSize", C.c_size_t),
+                ("dev_triIndicesPtr", C.c_void_p), ("triIndicesSize", C.c_size_t),
+                ("dev_triPtr", C.c_void_p), ("triSize", C.c_size_t)]
+
+
+class kernelInfo(C.Structure):  # CpuStructs.hpp:45-72 (296 bytes, bit-compatible)
+    _fields_ = [("blockSize", C.c_uint32 * 3), ("_pad0", C.c_uint32),
+                ("hash", C.c_uint64), ("dev_drawRes", C.c_void_p), ("accumBuffer", C.c_void_p),
+                ("width", C.c_int32), ("height", C.c_int32), ("cam", CamInfo), ("_pad1", C.c_uint32),
+                ("triangleTex", C.c_void_p), ("numVerts", C.c_size_t),
+                ("sphereTex", C.c_void_p), ("numSpheres", C.c_size_t),
+                ("cullBackFaces", C.c_uint8), ("_pad2", C.c_uint8 * 3), ("depth", C.c_uint32),
+                ("constantPdf", C.c_uint64), ("bvhData", BVHData),
+                ("time_elapsed", C.c_float), ("air_ref_index", C.c_float), ("glass_ref_index", C.c_float),
+                ("triCurrentMat", C.c_int32), ("clearBuffer", C.c_uint8), ("_pad3", C.c_uint8 * 3),
+                ("bkColor", C.c_float * 3), ("phongExpo", C.c_float), ("emi", C.c_float * 3), ("col", C.c_float * 3),
+                ("_pad4", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("rays_by_bounce", C.c_uint64 * 16), ("paths", C.c_uint64), ("kernel_launches", C.c_uint64)]
+
+
+assert C.sizeof(Sphere) == 44 and C.sizeof(Box) == 52 and C.sizeof(CamInfo) == 84
+assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
+
+# every symbol include/gpt.h declares (tests check the library exports each one)
+EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
+           "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
+           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats",
+           "gpt_hash64", "gpt_default_spheres", "gpt_default_kernel_info", "gpt_set_camera"]
+
+_lib = None
+
+
+def load_library():
+    """Load libgpt_b200.so (built by the in-tree Makefile). Raises if it is missing: no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise GptError("%s not found: build it with `make -C %s` (or __graft_entry__.build()); "
+                       "there is no CPU/PyTorch fallback" % (LIB_PATH, _HERE))
+    L = C.CDLL(LIB_PATH)
+    L.gpt_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+    L.gpt_destroy.argtypes = [C.c_void_p]
+    L.gpt_destroy.restype = None
+    L.gpt_set_flags.argtypes = [C.c_void_p, C.c_uint32]
+    L.gpt_last_error_string.argtypes = [C.c_void_p]
+    L.gpt_last_error_string.restype = C.c_char_p
+    L.gpt_version.restype = C.c_char_p
+    L.gpt_sync.argtypes = [C.c_void_p, C.c_void_p]
+    L.gpt_upload_scene.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                   C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int]
+    L.gpt_launch.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_void_p]
+    L.gpt_render.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p]
+    L.gpt_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gpt_render_frame_host.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]
+    L.gpt_trace_primary.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gpt_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gpt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+    L.gpt_reset_stats.argtypes = [C.c_void_p]
+    L.gpt_hash64.argtypes = [C.c_uint64]
+    L.gpt_hash64.restype = C.c_uint64
+    L.gpt_default_spheres.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.gpt_default_kernel_info.argtypes = [C.POINTER(kernelInfo), C.c_int, C.c_int]
+    L.gpt_default_kernel_info.restype = None
+    L.gpt_set_camera.argtypes = [C.POINTER(CamInfo), C.c_void_p, C.c_float, C.c_float]
+    L.gpt_set_camera.restype = None
+    _lib = L
+    return L
+
+
+# ---------------------------------------------------------------- host-only helpers
+def hash64(key):
+    """uf::hash, utilfun.cpp:380-389 (per-frame seed)."""
+    return int(load_library().gpt_hash64(C.c_uint64(key & 0xFFFFFFFFFFFFFFFF)))
+
+
+def default_spheres():
+    """The 8 hard-coded spheres of BasicScene.cpp:177-218 as a ctypes array."""
+    n = C.c_size_t(0)
+    L = load_library()
+    L.gpt_default_spheres(None, 0, C.byref(n))
+    arr = (Sphere * n.value)()
+    rc = L.gpt_default_spheres(arr, n.value, C.byref(n))
+    if rc != 0:
+        raise GptError("gpt_default_spheres rc=%d" % rc)
+    return arr
+
+
+def default_kernel_info(width, height):
+    """kernelInfo filled like BasicScene's constructor (BasicScene.cpp:220-259)."""
+    info = kernelInfo()
+    load_library().gpt_default_kernel_info(C.byref(info), int(width), int(height))
+    return info
+
+
+def set_camera(info, pos=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0):
+    p = (C.c_float * 3)(*pos)
+    load_library().gpt_set_camera(C.byref(info.cam), p, C.c_float(yaw), C.c_float(pitch))
+
+
+def spheres_from_list(items):
+    """items: iterable of (posRad[4], emi[3], col[3], mat)."""
+    items = list(items)
+    arr = (Sphere * len(items))()
+    for s, (pr, emi, col, mat) in zip(arr, items):
+        s.posRad[:] = pr
+        s.emi[:] = emi
+        s.col[:] = col
+        s.mat = int(mat)
+    return arr
+
+
+def _ptr(x):
+    """numpy array / torch tensor / ctypes array / int / None -> raw address."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    if hasattr(x, "data_ptr"):
+        return x.data_ptr()
+    return C.addressof(x)
+
+
+class Context:
+    """One render context on one GPU (gpt_create .. gpt_destroy)."""
+
+    def __init__(self, device=0, flags=0):
+        self._L = load_library()
+        h = C.c_void_p()
+        rc = self._L.gpt_create(C.byref(h), int(device))
+        if rc != 0:
+            raise GptError("gpt_create failed (%d): %s" % (rc, self._L.gpt_last_error_string(None).decode()))
+        self._h = h
+        self.device = int(device)
+        self._keep = []
+        if flags:
+            self.set_flags(flags)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.gpt_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise GptError("%s failed (%d): %s" % (what, rc, self._L.gpt_last_error_string(self._h).decode()))
+
+    def set_flags(self, flags):
+        self._ck(self._L.gpt_set_flags(self._h, C.c_uint32(flags)), "gpt_set_flags")
+
+    def sync(self, stream=None):
+        self._ck(self._L.gpt_sync(self._h, _ptr(stream)), "gpt_sync")
+
+    def upload_scene(self, nodes=None, tris=None, indices=None, spheres=None, boxes=None, on_device=False):
+        """nodes/tris: (n,4) float32, indices: int32 -- the CudaBVH arrays; spheres/boxes: ctypes arrays."""
+        def cnt(a, div=1):
+            if a is None:
+                return 0
+            n = a.numel() if hasattr(a, "numel") else a.size
+            return int(n) // div
+        ns = len(spheres) if spheres is not None else 0
+        nb = len(boxes) if boxes is not None else 0
+        self._ck(self._L.gpt_upload_scene(self._h, _ptr(nodes), cnt(nodes, 4), _ptr(tris), cnt(tris, 4), _ptr(indices), cnt(indices),
+                                          _ptr(spheres) if ns else None, ns, _ptr(boxes) if nb else None, nb, 1 if on_device else 0),
+                 "gpt_upload_scene")
+
+    def launch(self, info, stream=None):
+        """Drop-in for BasicScene::launchKernel (tracer.cu:405-415): one legacy 1-spp pass."""
+        self._ck(self._L.gpt_launch(self._h, C.byref(info), _ptr(stream)), "gpt_launch")
+
+    def render(self, info, accum_f4, seed, sample_begin, sample_count, stream=None):
+        self._ck(self._L.gpt_render(self._h, C.byref(info), _ptr(accum_f4), C.c_uint64(seed), C.c_uint64(sample_begin),
+                                    C.c_uint32(sample_count), _ptr(stream)), "gpt_render")
+
+    def resolve(self, accum_f4, width, height, out_rgba8=None, out_rgb_f32=None, stream=None):
+        self._ck(self._L.gpt_resolve(self._h, _ptr(accum_f4), int(width), int(height), _ptr(out_rgba8), _ptr(out_rgb_f32), _ptr(stream)),
+                 "gpt_resolve")
+
+    def render_frame_host(self, info, seed, sample_begin, spp, host_rgba8=None, host_accum_f4=None):
+        self._ck(self._L.gpt_render_frame_host(self._h, C.byref(info), C.c_uint64(seed), C.c_uint64(sample_begin), C.c_uint32(spp),
+                                               _ptr(host_rgba8), _ptr(host_accum_f4)), "gpt_render_frame_host")
+
+    def trace_primary(self, info, seed, sample, geom=None, tri_idx=None, prim_idx=None, t=None, stream=None):
+        self._ck(self._L.gpt_trace_primary(self._h, C.byref(info), C.c_uint64(seed), C.c_uint64(sample),
+                                           _ptr(geom), _ptr(tri_idx), _ptr(prim_idx), _ptr(t), _ptr(stream)), "gpt_trace_primary")
+
+    def trace_rays(self, o, d, n, cull, tri_idx=None, tri_addr=None, t=None, stream=None):
+        self._ck(self._L.gpt_trace_rays(self._h, _ptr(o), _ptr(d), int(n), int(bool(cull)), _ptr(tri_idx), _ptr(tri_addr), _ptr(t), _ptr(stream)),
+                 "gpt_trace_rays")
+
+    def stats(self):
+        s = Stats()
+        self._ck(self._L.gpt_get_stats(self._h, C.byref(s)), "gpt_get_stats")
+        return s
+
+    def reset_stats(self):
+        self._ck(self._L.gpt_reset_stats(self._h), "gpt_reset_stats")
+
+
+class BasicScene:
+    """Headless mirror of the reference's BasicScene (BasicScene.hpp:21-60): owns kernelInfo, the
+    accumulation buffer and the draw buffer, and exposes launchKernel(info) + the per-frame contract
+    of BasicScene::run (BasicScene.cpp:395-404).  The GLFW/ImGui/GL parts are out of scope."""
+
+    def __init__(self, width, height, nodes=None, tris=None, indices=None, spheres=None, device=0, flags=0):
+        import torch
+        if not torch.cuda.is_available():
+            raise GptError("BasicScene needs a CUDA device (no CPU fallback)")
+        self.width, self.height = int(width), int(height)
+        self.torch = torch
+        self.dev = torch.device("cuda", device)
+        self.ctx = Context(device, flags)
+        self.info = default_kernel_info(width, height)
+        self.spheres = spheres if spheres is not None else default_spheres()
+        self.ctx.upload_scene(nodes, tris, indices, self.spheres)
+        # cudaMalloc dev_drawRes / accumBuffer, BasicScene.cpp:137-151
+        self.accumBuffer = torch.zeros(self.height * self.width * 3, dtype=torch.float32, device=self.dev)
+        self.drawRes = torch.zeros(self.height * self.width, dtype=torch.int32, device=self.dev)
+        self.info.accumBuffer = self.accumBuffer.data_ptr()
+        self.info.dev_drawRes = self.drawRes.data_ptr()
+        self.frameNumber = 0
+
+    def launchKernel(self, info):
+        self.ctx.launch(info, self.torch.cuda.current_stream(self.dev).cuda_stream)
+
+    def frame(self, reset=False):
+        """One iteration of the loop body BasicScene.cpp:395-404 (minus GL)."""
+        self.torch.cuda.current_stream(self.dev).synchronize()
+        self.info.hash = hash64(self.frameNumber)
+        self.info.constantPdf = 1 if (reset or self.frameNumber == 0) else self.info.constantPdf + 1
+        self.launchKernel(self.info)
+        self.frameNumber += 1
+
+    def run(self, frames):
+        for _ in range(frames):
+            self.frame()
+        self.torch.cuda.current_stream(self.dev).synchronize()
+        return self.accumBuffer.view(self.height, self.width, 3), self.drawRes.view(self.height, self.width)

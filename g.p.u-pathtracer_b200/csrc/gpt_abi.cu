@@ -1,0 +1,343 @@
+// gpt_abi.cu -- implementation of the C-ABI declared in include/gpt.h.
+//
+// Host-side orchestration only: context, scene upload + device re-pack, parameter flattening and
+// kernel launches.  No CPU fallback exists: without a usable CUDA device every compute entry fails
+// with GPT_ERR_CUDA and a message.
+#include "../../include/gpt.h"
+#include "gpt_kernels.h"
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+struct gpt_ctx {
+    int device = 0;
+    int sm_count = 0;
+    uint32_t flags = 0;
+    // uploaded scene (owned)
+    float4* nodes = nullptr; float4* tris = nullptr; int n_nodes = 0; int n_tris = 0;
+    float* spheres = nullptr; int n_spheres = 0;
+    float* boxes = nullptr; int n_boxes = 0;
+    bool has_scene = false;
+    // identity of the reference arrays the packed BVH was built from (gpt_launch re-packs on change)
+    const void* src_nodes = nullptr; const void* src_tris = nullptr; const void* src_idx = nullptr;
+    size_t src_n_nodes = 0, src_n_tris = 0, src_n_idx = 0;
+    // scratch
+    unsigned int* work_counter = nullptr;
+    unsigned long long* stats = nullptr;       // [0]=rays [1]=paths [2..17]=rays by bounce
+    float4* frame_accum = nullptr; uint32_t* frame_rgba = nullptr; size_t frame_pixels = 0;
+    unsigned long long launches = 0;
+    std::string err;
+};
+
+static thread_local std::string g_create_err;
+
+static int fail(gpt_ctx* c, int code, const char* what, cudaError_t e = cudaSuccess)
+{
+    char buf[512];
+    if (e != cudaSuccess) snprintf(buf, sizeof(buf), "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+    else snprintf(buf, sizeof(buf), "%s", what);
+    if (c) c->err = buf; else g_create_err = buf;
+    return code;
+}
+#define CU(c, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail((c), GPT_ERR_CUDA, #call, e_); } while (0)
+
+extern "C" {
+
+const char* gpt_version(void) { return "gpt_b200 0.1 (sm_100a)"; }
+
+const char* gpt_last_error_string(gpt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int gpt_create(gpt_ctx** out, int device)
+{
+    if (!out) return fail(nullptr, GPT_ERR_INVALID, "gpt_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) return fail(nullptr, GPT_ERR_CUDA, "gpt_create: no CUDA device (this library has no CPU path)", e);
+    if (device < 0 || device >= n) return fail(nullptr, GPT_ERR_INVALID, "gpt_create: device index out of range");
+    CU(nullptr, cudaSetDevice(device));
+    gpt_ctx* c = new (std::nothrow) gpt_ctx();
+    if (!c) return fail(nullptr, GPT_ERR_INVALID, "gpt_create: out of host memory");
+    c->device = device;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) { delete c; return fail(nullptr, GPT_ERR_CUDA, "cudaGetDeviceProperties", e); }
+    c->sm_count = prop.multiProcessorCount;
+    if ((e = cudaMalloc(&c->work_counter, sizeof(unsigned int))) != cudaSuccess ||
+        (e = cudaMalloc(&c->stats, 18 * sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMemset(c->stats, 0, 18 * sizeof(unsigned long long))) != cudaSuccess) {
+        cudaFree(c->work_counter); cudaFree(c->stats); delete c;
+        return fail(nullptr, GPT_ERR_CUDA, "gpt_create: scratch allocation", e);
+    }
+    *out = c;
+    return GPT_OK;
+}
+
+static void free_scene(gpt_ctx* c)
+{
+    cudaFree(c->nodes); cudaFree(c->tris); cudaFree(c->spheres); cudaFree(c->boxes);
+    c->nodes = c->tris = nullptr; c->spheres = c->boxes = nullptr;
+    c->n_nodes = c->n_tris = c->n_spheres = c->n_boxes = 0;
+    c->has_scene = false;
+    c->src_nodes = c->src_tris = c->src_idx = nullptr;
+}
+
+void gpt_destroy(gpt_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_scene(c);
+    cudaFree(c->work_counter); cudaFree(c->stats); cudaFree(c->frame_accum); cudaFree(c->frame_rgba);
+    delete c;
+}
+
+int gpt_set_flags(gpt_ctx* c, uint32_t flags)
+{
+    if (!c) return GPT_ERR_INVALID;
+    c->flags = flags;
+    return GPT_OK;
+}
+
+int gpt_sync(gpt_ctx* c, gpt_stream stream)
+{
+    if (!c) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize((cudaStream_t)stream));
+    return GPT_OK;
+}
+
+// (re)build the packed BVH from reference-layout arrays that are already on the device
+static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec4, const void* tris, size_t n_tri_vec4,
+                                const int32_t* idx, size_t n_idx)
+{
+    cudaFree(c->nodes); cudaFree(c->tris); c->nodes = c->tris = nullptr; c->n_nodes = c->n_tris = 0;
+    if (n_node_vec4 == 0 || !nodes) return GPT_OK;     // sphere-only scene
+    if (!tris || !idx) return fail(c, GPT_ERR_INVALID, "BVH nodes given without triangle / index arrays");
+    RepackResult r;
+    cudaError_t e = gptk_repack((const float4*)nodes, n_node_vec4, (const float4*)tris, n_tri_vec4, idx, n_idx, &r, 0);
+    c->launches += 2;
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "device re-pack", e);
+    if (r.bad_layout) {
+        char buf[128]; snprintf(buf, sizeof(buf), "malformed BVH arrays (code %d): not a CudaBVH BVHLayout_Compact tree", r.bad_layout);
+        return fail(c, GPT_ERR_LAYOUT, buf);
+    }
+    c->nodes = r.nodes; c->tris = r.tris; c->n_nodes = r.n_nodes; c->n_tris = r.n_tris;
+    return GPT_OK;
+}
+
+int gpt_upload_scene(gpt_ctx* c, const void* nodes, size_t n_node_vec4, const void* tris, size_t n_tri_vec4,
+                     const int32_t* tri_indices, size_t n_indices, const gpt_sphere* spheres, size_t n_spheres,
+                     const gpt_box* boxes, size_t n_boxes, int on_device)
+{
+    if (!c) return GPT_ERR_INVALID;
+    if ((n_spheres && !spheres) || (n_boxes && !boxes)) return fail(c, GPT_ERR_INVALID, "gpt_upload_scene: NULL primitive array with non-zero count");
+    if (n_spheres > (1u << 20) || n_boxes > (1u << 20)) return fail(c, GPT_ERR_INVALID, "gpt_upload_scene: too many primitives");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());
+    free_scene(c);
+    const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    int rc = GPT_OK;
+    if (n_node_vec4 && nodes) {
+        if (on_device) {
+            rc = pack_bvh_from_device(c, nodes, n_node_vec4, tris, n_tri_vec4, tri_indices, n_indices);
+        } else {
+            if (!tris || !tri_indices) return fail(c, GPT_ERR_INVALID, "BVH nodes given without triangle / index arrays");
+            void *dn = nullptr, *dt = nullptr; int32_t* di = nullptr;
+            cudaError_t e;
+            if ((e = cudaMalloc(&dn, n_node_vec4 * 16)) != cudaSuccess || (e = cudaMalloc(&dt, (n_tri_vec4 ? n_tri_vec4 : 1) * 16)) != cudaSuccess ||
+                (e = cudaMalloc((void**)&di, (n_indices ? n_indices : 1) * 4)) != cudaSuccess ||
+                (e = cudaMemcpy(dn, nodes, n_node_vec4 * 16, cudaMemcpyHostToDevice)) != cudaSuccess ||
+                (e = cudaMemcpy(dt, tris, n_tri_vec4 * 16, cudaMemcpyHostToDevice)) != cudaSuccess ||
+                (e = cudaMemcpy(di, tri_indices, n_indices * 4, cudaMemcpyHostToDevice)) != cudaSuccess) {
+                cudaFree(dn); cudaFree(dt); cudaFree(di);
+                return fail(c, GPT_ERR_CUDA, "gpt_upload_scene: staging copy", e);
+            }
+            rc = pack_bvh_from_device(c, dn, n_node_vec4, dt, n_tri_vec4, di, n_indices);
+            cudaFree(dn); cudaFree(dt); cudaFree(di);
+        }
+        if (rc != GPT_OK) return rc;
+    }
+    if (n_spheres) {
+        CU(c, cudaMalloc(&c->spheres, n_spheres * sizeof(gpt_sphere)));
+        CU(c, cudaMemcpy(c->spheres, spheres, n_spheres * sizeof(gpt_sphere), kind));
+        c->n_spheres = (int)n_spheres;
+    }
+    if (n_boxes) {
+        CU(c, cudaMalloc(&c->boxes, n_boxes * sizeof(gpt_box)));
+        CU(c, cudaMemcpy(c->boxes, boxes, n_boxes * sizeof(gpt_box), kind));
+        c->n_boxes = (int)n_boxes;
+    }
+    c->has_scene = true;
+    return GPT_OK;
+}
+
+static int make_params(gpt_ctx* c, const gpt_kernel_info* info, uint64_t seed, RenderParams* p)
+{
+    if (info->width < 2 || info->height < 2 || (long long)info->width * info->height > 0x7fffffffLL / 4)
+        return fail(c, GPT_ERR_INVALID, "width/height out of range (need >= 2: the camera divides by w-1, h-1)");
+    if (info->depth > 4096) return fail(c, GPT_ERR_INVALID, "depth out of range");
+    p->width = info->width; p->height = info->height;
+    for (int i = 0; i < 3; ++i) {
+        p->front[i] = info->cam.front[i]; p->right[i] = info->cam.right[i]; p->up[i] = info->cam.up[i]; p->pos[i] = info->cam.pos[i];
+        p->bk[i] = info->bkColor[i]; p->emi[i] = info->emi[i]; p->col[i] = info->col[i];
+    }
+    p->dist = info->cam.dist; p->aspect = info->cam.aspect; p->fov = info->cam.fov;
+    p->cull = info->cullBackFaces ? 1 : 0;
+    p->depth = info->depth;
+    p->air = info->air_ref_index; p->glass = info->glass_ref_index;
+    p->tri_mat = info->triCurrentMat;
+    p->phong = info->phongExpo;
+    p->seed = seed;
+    p->flags = c->flags & (GPT_FLAG_NO_JITTER | GPT_FLAG_METAL_FIXED | GPT_FLAG_COUNT_BOUNCES);
+    return GPT_OK;
+}
+
+static void uploaded_scene(const gpt_ctx* c, DevScene* sc)
+{
+    sc->nodes = c->nodes; sc->tris = c->tris; sc->n_nodes = c->n_nodes; sc->n_tris = c->n_tris;
+    sc->spheres = c->spheres; sc->n_spheres = c->n_spheres;
+    sc->boxes = c->boxes; sc->n_boxes = c->n_boxes;
+}
+
+// scene for a launch: pointers carried by kernelInfo win (drop-in use), else the uploaded scene
+static int launch_scene(gpt_ctx* c, const gpt_kernel_info* info, DevScene* sc)
+{
+    const gpt_bvh_data& b = info->bvhData;
+    if (b.dev_triNode && b.triNodeSize) {
+        const bool same = c->src_nodes == b.dev_triNode && c->src_tris == b.dev_triPtr && c->src_idx == b.dev_triIndicesPtr &&
+                          c->src_n_nodes == b.triNodeSize && c->src_n_tris == b.triSize && c->src_n_idx == b.triIndicesSize;
+        if (!same) {
+            CU(c, cudaDeviceSynchronize());
+            int rc = pack_bvh_from_device(c, b.dev_triNode, b.triNodeSize, b.dev_triPtr, b.triSize, b.dev_triIndicesPtr, b.triIndicesSize);
+            if (rc != GPT_OK) return rc;
+            c->src_nodes = b.dev_triNode; c->src_tris = b.dev_triPtr; c->src_idx = b.dev_triIndicesPtr;
+            c->src_n_nodes = b.triNodeSize; c->src_n_tris = b.triSize; c->src_n_idx = b.triIndicesSize;
+        }
+    } else if (!c->has_scene && !(info->sphereTex && info->numSpheres)) {
+        return fail(c, GPT_ERR_NO_SCENE, "no scene: call gpt_upload_scene or pass BVH/sphere device pointers in kernelInfo");
+    }
+    uploaded_scene(c, sc);
+    if (info->sphereTex && info->numSpheres) {        // read live from the caller's array like the reference (tracer.cu:39)
+        if (info->numSpheres > (1u << 20)) return fail(c, GPT_ERR_INVALID, "numSpheres out of range");
+        sc->spheres = reinterpret_cast<const float*>(info->sphereTex); sc->n_spheres = (int)info->numSpheres;
+    }
+    return GPT_OK;
+}
+
+int gpt_launch(gpt_ctx* c, const gpt_kernel_info* info, gpt_stream stream)
+{
+    if (!c || !info) return GPT_ERR_INVALID;
+    if (!info->accumBuffer) return fail(c, GPT_ERR_INVALID, "gpt_launch: accumBuffer is NULL");
+    if (info->constantPdf == 0) return fail(c, GPT_ERR_INVALID, "gpt_launch: constantPdf must be >= 1");
+    CU(c, cudaSetDevice(c->device));
+    RenderParams p; DevScene sc;
+    int rc = make_params(c, info, info->hash, &p); if (rc) return rc;
+    rc = launch_scene(c, info, &sc); if (rc) return rc;
+    cudaError_t e = gptk_render_legacy(sc, p, info->accumBuffer, info->dev_drawRes, info->constantPdf,
+                                       c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "render launch", e);
+    c->launches += 1;
+    return GPT_OK;
+}
+
+int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_t seed, uint64_t sample_begin,
+               uint32_t sample_count, gpt_stream stream)
+{
+    if (!c || !info || !accum_f4) return GPT_ERR_INVALID;
+    if (sample_count == 0) return GPT_OK;
+    CU(c, cudaSetDevice(c->device));
+    RenderParams p; DevScene sc;
+    int rc = make_params(c, info, seed, &p); if (rc) return rc;
+    rc = launch_scene(c, info, &sc); if (rc) return rc;
+    cudaError_t e = gptk_render_mega(sc, p, reinterpret_cast<float4*>(accum_f4), sample_begin, sample_count,
+                                     c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "render launch", e);
+    c->launches += 1;
+    return GPT_OK;
+}
+
+int gpt_resolve(gpt_ctx* c, const float* accum_f4, int width, int height, uint32_t* out_rgba8, float* out_rgb_f32, gpt_stream stream)
+{
+    if (!c || !accum_f4 || width <= 0 || height <= 0) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    cudaError_t e = gptk_resolve(reinterpret_cast<const float4*>(accum_f4), width * height, out_rgba8, out_rgb_f32, c->sm_count, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "resolve launch", e);
+    c->launches += 1;
+    return GPT_OK;
+}
+
+int gpt_render_frame_host(gpt_ctx* c, const gpt_kernel_info* info, uint64_t seed, uint64_t sample_begin, uint32_t spp,
+                          uint32_t* host_rgba8, float* host_accum_f4)
+{
+    if (!c || !info) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    const size_t n = (size_t)info->width * (size_t)info->height;
+    if (n == 0) return fail(c, GPT_ERR_INVALID, "empty frame");
+    if (c->frame_pixels != n) {
+        cudaFree(c->frame_accum); cudaFree(c->frame_rgba); c->frame_accum = nullptr; c->frame_rgba = nullptr; c->frame_pixels = 0;
+        CU(c, cudaMalloc(&c->frame_accum, n * sizeof(float4)));
+        CU(c, cudaMalloc(&c->frame_rgba, n * sizeof(uint32_t)));
+        c->frame_pixels = n;
+    }
+    CU(c, cudaMemsetAsync(c->frame_accum, 0, n * sizeof(float4), 0));
+    int rc = gpt_render(c, info, reinterpret_cast<float*>(c->frame_accum), seed, sample_begin, spp, 0); if (rc) return rc;
+    rc = gpt_resolve(c, reinterpret_cast<const float*>(c->frame_accum), info->width, info->height, c->frame_rgba, nullptr, 0); if (rc) return rc;
+    if (host_rgba8) CU(c, cudaMemcpyAsync(host_rgba8, c->frame_rgba, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, 0));
+    if (host_accum_f4) CU(c, cudaMemcpyAsync(host_accum_f4, c->frame_accum, n * sizeof(float4), cudaMemcpyDeviceToHost, 0));
+    CU(c, cudaStreamSynchronize(0));
+    return GPT_OK;
+}
+
+int gpt_trace_primary(gpt_ctx* c, const gpt_kernel_info* info, uint64_t seed, uint64_t sample,
+                      int32_t* geom, int32_t* tri_idx, int32_t* prim_idx, float* t, gpt_stream stream)
+{
+    if (!c || !info) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    RenderParams p; DevScene sc;
+    int rc = make_params(c, info, seed, &p); if (rc) return rc;
+    rc = launch_scene(c, info, &sc); if (rc) return rc;
+    cudaError_t e = gptk_primary(sc, p, sample, geom, tri_idx, prim_idx, t, c->sm_count, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "primary launch", e);
+    c->launches += 1;
+    return GPT_OK;
+}
+
+int gpt_trace_rays(gpt_ctx* c, const float* o, const float* d, size_t n, int cull, int32_t* tri_idx, int32_t* tri_addr,
+                   float* t, gpt_stream stream)
+{
+    if (!c || (n && (!o || !d))) return GPT_ERR_INVALID;
+    if (!c->has_scene) return fail(c, GPT_ERR_NO_SCENE, "gpt_trace_rays: no uploaded scene");
+    CU(c, cudaSetDevice(c->device));
+    DevScene sc; uploaded_scene(c, &sc);
+    cudaError_t e = gptk_trace_rays(sc, o, d, n, cull, tri_idx, tri_addr, t, c->sm_count, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "trace_rays launch", e);
+    if (n) c->launches += 1;
+    return GPT_OK;
+}
+
+int gpt_get_stats(gpt_ctx* c, gpt_stats* out)
+{
+    if (!c || !out) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());
+    unsigned long long h[18];
+    CU(c, cudaMemcpy(h, c->stats, sizeof(h), cudaMemcpyDeviceToHost));
+    out->rays = h[0]; out->paths = h[1];
+    for (int i = 0; i < 16; ++i) out->rays_by_bounce[i] = h[2 + i];
+    out->kernel_launches = c->launches;
+    return GPT_OK;
+}
+
+int gpt_reset_stats(gpt_ctx* c)
+{
+    if (!c) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());
+    CU(c, cudaMemset(c->stats, 0, 18 * sizeof(unsigned long long)));
+    c->launches = 0;
+    return GPT_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,23 @@
+// gpt_kernels.h -- host-callable launchers of the device code (internal; the public surface is include/gpt.h)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "gpt_scene.cuh"
+
+cudaError_t gptk_render_mega(const DevScene& sc, const RenderParams& p, float4* accum_f4, unsigned long long sample_begin,
+                             uint32_t sample_count, unsigned int* work_counter, unsigned long long* stats,
+                             int sm_count, cudaStream_t st);
+cudaError_t gptk_render_legacy(const DevScene& sc, const RenderParams& p, float* accum_v3, uint32_t* draw,
+                               unsigned long long constant_pdf, unsigned int* work_counter, unsigned long long* stats,
+                               int sm_count, cudaStream_t st);
+cudaError_t gptk_primary(const DevScene& sc, const RenderParams& p, unsigned long long sample,
+                         int* geom, int* tri_idx, int* prim_idx, float* t, int sm_count, cudaStream_t st);
+cudaError_t gptk_trace_rays(const DevScene& sc, const float* o, const float* d, size_t n, int cull,
+                            int* tri_idx, int* tri_addr, float* t, int sm_count, cudaStream_t st);
+cudaError_t gptk_resolve(const float4* accum, int n, uint32_t* rgba8, float* rgb, int sm_count, cudaStream_t st);
+
+// device re-pack (gpt_repack.cu): reference arrays (device pointers) -> packed nodes / triangles.
+// *out_nodes / *out_tris are cudaMalloc'd by the callee; returns the packed triangle count.
+struct RepackResult { float4* nodes; float4* tris; int n_nodes; int n_tris; int bad_layout; };
+cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float4* ref_tris, size_t n_tri_vec4,
+                        const int* ref_indices, size_t n_indices, RepackResult* out, cudaStream_t st);

@@ -1,0 +1,128 @@
+// gpt_repack.cu -- device-side re-pack of the arrays CudaBVH::createCompact emits (CudaBVH.cpp:121-270)
+// into the layout described in gpt_scene.cuh.  The SAME binary tree, child order and per-leaf triangle
+// order are kept, so traversal order -- and therefore tie-breaking -- is unchanged.
+//
+// Three passes over the 2*n_inner child slots:
+//   1. count : a leaf child (~slot, CudaBVH.cpp:177) is walked exactly the way the reference kernel reads
+//              it (v0 first; bits(v0.x)==0x80000000 ends the leaf, cudaUtils.h:405-416) -> triangles per leaf
+//   2. scan  : exclusive prefix sum (CUB) -> first packed triangle of each leaf
+//   3. write : packed triangles (v0, e1, e2 + index / slot / last flag) and patched child pointers
+#include "gpt_kernels.h"
+#include <cub/device/device_scan.cuh>
+
+#define LEAF_TERM 0x80000000u
+
+__global__ void k_count_leaf_tris(const float4* __restrict__ ref_nodes, int n_inner, const float4* __restrict__ ref_tris,
+                                  size_t n_tri_vec4, size_t n_node_vec4, int* __restrict__ counts, int* __restrict__ bad)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * n_inner) return;
+    const int4 ch = *reinterpret_cast<const int4*>(ref_nodes + 4 * (i >> 1) + 3);
+    const int c = (i & 1) ? ch.y : ch.x;
+    int cnt = 0;
+    if (c < 0) {
+        size_t slot = (size_t)(~c);
+        while (true) {
+            if (slot >= n_tri_vec4) { atomicExch(bad, 1); break; }              // ran off the array
+            if (__float_as_uint(ref_tris[slot].x) == LEAF_TERM) break;
+            if (slot + 2 >= n_tri_vec4) { atomicExch(bad, 1); break; }
+            ++cnt; slot += 3;
+        }
+    } else {
+        // inner child: byte offset, 64-B aligned, inside the node array (CudaBVH.cpp:161)
+        // and, as createCompact appends children after their parent, strictly behind it (rules out cycles)
+        if ((c & 63) != 0 || (size_t)(c >> 4) + 4 > n_node_vec4 || (c >> 6) <= (i >> 1)) atomicExch(bad, 3);
+    }
+    counts[i] = cnt;
+}
+
+__global__ void k_write_packed(const float4* __restrict__ ref_nodes, int n_inner, const float4* __restrict__ ref_tris,
+                               const int* __restrict__ ref_indices, size_t n_indices, const int* __restrict__ offsets,
+                               const int n_total, float4* __restrict__ nodes, float4* __restrict__ tris)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * n_inner) return;
+    const int node = i >> 1;
+    const int4 ch = *reinterpret_cast<const int4*>(ref_nodes + 4 * node + 3);
+    const int c = (i & 1) ? ch.y : ch.x;
+    int packed_child;
+    if (c >= 0) {
+        packed_child = c >> 4;                       // byte offset -> float4 index
+    } else {
+        const int base = offsets[i];
+        // A leaf whose FIRST v0.x is -0.0 reads as empty in the reference kernel (cudaUtils.h:413, the
+        // "-0.0 hazard"); it points at the shared null triangle appended behind the last real one.
+        packed_child = (__float_as_uint(ref_tris[~c].x) == LEAF_TERM) ? ~n_total : ~base;
+        int slot = ~c, k = 0;
+        while (__float_as_uint(ref_tris[slot].x) != LEAF_TERM) {
+            const float4 v0 = ref_tris[slot], v1 = ref_tris[slot + 1], v2 = ref_tris[slot + 2];
+            const bool last = __float_as_uint(ref_tris[slot + 3].x) == LEAF_TERM;
+            const int orig = ((size_t)slot < n_indices) ? ref_indices[slot] : -1;
+            float4* dst = tris + 3 * (size_t)(base + k);
+            dst[0] = make_float4(v0.x, v0.y, v0.z, __int_as_float(orig));
+            dst[1] = make_float4(v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, __int_as_float(slot));
+            dst[2] = make_float4(v2.x - v0.x, v2.y - v0.y, v2.z - v0.z, __int_as_float(last ? 1 : 0));
+            ++k; slot += 3;
+        }
+    }
+    // boxes are copied by the even lane of the pair; child pointers written per child
+    if ((i & 1) == 0) {
+        nodes[4 * node + 0] = ref_nodes[4 * node + 0];
+        nodes[4 * node + 1] = ref_nodes[4 * node + 1];
+        nodes[4 * node + 2] = ref_nodes[4 * node + 2];
+    }
+    reinterpret_cast<int*>(nodes + 4 * node + 3)[i & 1] = packed_child;
+    if ((i & 1) == 0) { reinterpret_cast<int*>(nodes + 4 * node + 3)[2] = 0; reinterpret_cast<int*>(nodes + 4 * node + 3)[3] = 0; }
+    if (i == 0) {   // null triangle: zero area -> det == 0 -> never hit; flagged last-in-leaf
+        tris[3 * (size_t)n_total + 0] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        tris[3 * (size_t)n_total + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        tris[3 * (size_t)n_total + 2] = make_float4(0.f, 0.f, 0.f, __int_as_float(1));
+    }
+}
+
+cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float4* ref_tris, size_t n_tri_vec4,
+                        const int* ref_indices, size_t n_indices, RepackResult* out, cudaStream_t st)
+{
+    out->nodes = nullptr; out->tris = nullptr; out->n_nodes = 0; out->n_tris = 0; out->bad_layout = 0;
+    const int n_inner = (int)(n_node_vec4 / 4);
+    if (n_inner == 0) return cudaSuccess;
+    if (n_node_vec4 % 4 != 0 || n_node_vec4 / 4 > 0x1fffffffull) { out->bad_layout = 4; return cudaSuccess; }
+    const int n_child = 2 * n_inner;
+    int *counts = nullptr, *offsets = nullptr, *bad = nullptr;
+    void* tmp = nullptr; size_t tmp_bytes = 0;
+    cudaError_t e;
+#define CK(x) do { e = (x); if (e != cudaSuccess) goto fail; } while (0)
+    CK(cudaMalloc(&counts, sizeof(int) * (size_t)(n_child + 1)));
+    CK(cudaMalloc(&offsets, sizeof(int) * (size_t)(n_child + 1)));
+    CK(cudaMalloc(&bad, sizeof(int)));
+    CK(cudaMemsetAsync(bad, 0, sizeof(int), st));
+    CK(cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)(n_child + 1), st));
+    k_count_leaf_tris<<<(n_child + 127) / 128, 128, 0, st>>>(ref_nodes, n_inner, ref_tris, n_tri_vec4, n_node_vec4, counts, bad);
+    CK(cudaGetLastError());
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, offsets, n_child + 1, st));
+    CK(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 16));
+    CK(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, counts, offsets, n_child + 1, st));
+    {
+        int h_bad = 0, h_total = 0;
+        CK(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&h_total, offsets + n_child, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (h_bad) { out->bad_layout = h_bad; goto done; }
+        CK(cudaMalloc(&out->nodes, sizeof(float4) * 4 * (size_t)n_inner));
+        CK(cudaMalloc(&out->tris, sizeof(float4) * 3 * ((size_t)h_total + 1)));
+        k_write_packed<<<(n_child + 127) / 128, 128, 0, st>>>(ref_nodes, n_inner, ref_tris, ref_indices, n_indices, offsets, h_total, out->nodes, out->tris);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(st));
+        out->n_nodes = n_inner; out->n_tris = h_total;
+    }
+done:
+    cudaFree(counts); cudaFree(offsets); cudaFree(bad); cudaFree(tmp);
+    return cudaSuccess;
+fail:
+    cudaFree(counts); cudaFree(offsets); cudaFree(bad); cudaFree(tmp);
+    if (out->nodes) cudaFree(out->nodes);
+    if (out->tris) cudaFree(out->tris);
+    out->nodes = nullptr; out->tris = nullptr;
+    return e;
+#undef CK
+}

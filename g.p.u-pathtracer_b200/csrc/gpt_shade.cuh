@@ -1,0 +1,156 @@
+// gpt_shade.cuh -- camera ray generation and the per-bounce shading step.
+//
+// Replaces getCamRayDir (cudaUtils.h:111-134), uniformSampleHemisphere (:185-192) and the body of the
+// bounce loop of getSample (tracer.cu:72-300), including every quirk SURVEY.md 8-Q lists (Q1 METAL `w`
+// = image width, Q2 unweighted miss colour, Q4 un-flipped triangle normal, Q5 non-cosine diffuse lobe,
+// Q7 REFR constants).  One call = one bounce, so the same code serves the megakernel and the wavefront
+// shade kernel.
+#pragma once
+#include "gpt_traverse.cuh"
+
+struct PathState {
+    f3 o, d;        // current ray
+    f3 mask;        // colour mask   (tracer.cu:68)
+    f3 accu;        // accumulated colour (tracer.cu:69)
+};
+
+// getCamRayDir, cudaUtils.h:111-134.  Row 0 is the bottom of the image; origin lies ON the image plane.
+__device__ __forceinline__ void camera_ray(const RenderParams& p, int px, int py, float jx, float jy, f3& o, f3& d)
+{
+    float xs = ((float)px - (float)p.width / 2.0f) + 0.5f;
+    xs = xs + jx;
+    xs = xs * p.dist; xs = xs * p.aspect; xs = xs * p.fov; xs = xs / (float)(p.width - 1);
+    float ys = ((float)py - (float)p.height / 2.0f) + 0.5f;
+    ys = ys + jy;
+    ys = ys * p.dist; ys = ys * p.fov; ys = ys / (float)(p.height - 1);
+    const f3 dir = mad3(ld3(p.up), ys, mad3(ld3(p.right), xs, scale3(ld3(p.front), p.dist)));
+    o = add3(ld3(p.pos), dir);
+    d = normalize3(dir);
+}
+
+__device__ __forceinline__ void start_path(const RenderParams& p, int px, int py, uint32_t pixel, uint64_t sample, PathState& ps)
+{
+    float jx = 0.0f, jy = 0.0f;
+    if (!(p.flags & RP_NO_JITTER)) {
+        const float4 u = rng_block(p.seed, pixel, sample, 0u);
+        jx = u.x - 0.5f; jy = u.y - 0.5f;          // cudaUtils.h:117-118
+    }
+    camera_ray(p, px, py, jx, jy, ps.o, ps.d);
+    ps.mask = mk3(1.0f, 1.0f, 1.0f);
+    ps.accu = mk3(0.0f, 0.0f, 0.0f);
+}
+
+// Box::normalAt spec, cudaUtils.h:61-76
+__device__ __forceinline__ f3 box_normal(const float* bx, f3 p)
+{
+    const float eps = 0.001f;
+    if (fabsf(bx[0] - p.x) < eps) return mk3(-1, 0, 0);
+    if (fabsf(bx[3] - p.x) < eps) return mk3(1, 0, 0);
+    if (fabsf(bx[1] - p.y) < eps) return mk3(0, -1, 0);
+    if (fabsf(bx[4] - p.y) < eps) return mk3(0, 1, 0);
+    if (fabsf(bx[2] - p.z) < eps) return mk3(0, 0, -1);
+    return mk3(0, 0, 1);
+}
+
+// One bounce of tracer.cu:112-296.  Returns false when the path ended on a miss (ps.accu then holds
+// the background colour, Q2); true when the path continues with the new ray in ps.
+__device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderParams& p,
+                                             const float* s_spheres, const float* s_boxes,
+                                             const SceneHit h, const uint32_t pixel, const uint64_t sample,
+                                             const uint32_t bounce, PathState& ps)
+{
+    if (h.geom == GEO_NONE) { ps.accu = ld3(p.bk); return false; }       // tracer.cu:140-142
+    f3 hitpos = mad3(ps.d, h.t, ps.o);                                   // :112
+    f3 n, nl, objcol, emit; int mat;
+    if (h.geom == GEO_SPHERE) {                                          // :113-122
+        const float* s = s_spheres + 11 * h.prim;
+        n = normalize3(sub3(hitpos, mk3(s[0], s[1], s[2])));
+        nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
+        emit = mk3(s[4], s[5], s[6]); objcol = mk3(s[7], s[8], s[9]); mat = __float_as_int(s[10]);
+    } else if (h.geom == GEO_TRI) {                                      // :123-139
+        const float4 b = __ldg(sc.tris + 3 * h.prim + 1);
+        const float4 c = __ldg(sc.tris + 3 * h.prim + 2);
+        // cross(v0-v1, v0-v2) == cross(e1, e2) bit for bit (negation is exact)   cudaUtils.h:432
+        n = normalize3(cross3(mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z)));
+        nl = n;                                                          // Q4: not face-forwarded
+        emit = ld3(p.emi); objcol = ld3(p.col); mat = p.tri_mat;
+    } else {                                                             // BOX (commented branch :143-152)
+        const float* bx = s_boxes + 13 * h.prim;
+        n = box_normal(bx, hitpos);
+        nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
+        emit = mk3(bx[6], bx[7], bx[8]); objcol = mk3(bx[9], bx[10], bx[11]); mat = __float_as_int(bx[12]);
+    }
+    ps.accu = add3(ps.accu, mul3(ps.mask, emit));                        // :120/:133
+
+    const float4 u = rng_block(p.seed, pixel, sample, bounce + 1u);
+    f3 nextdir;
+    if (mat == MAT_DIFF) {                                               // :156-186 (Q5)
+        f3 nt = (fabsf(nl.x) > fabsf(nl.y)) ? mk3(nl.z, 0.0f, -nl.x) : mk3(0.0f, -nl.z, nl.y);
+        nt = normalize3(nt);
+        const f3 nb = normalize3(cross3(nl, nt));
+        float sn, cs; sincos2pi(u.x, sn, cs);
+        const float f2 = u.y;                                            // sin(theta), uniform (cudaUtils.h:185-192)
+        const f3 rv = mk3(cs * f2, sqrtf(fmaf(-f2, f2, 1.0f)), sn * f2);
+        nextdir = mk3(fmaf(nt.x, rv.z, fmaf(nl.x, rv.y, nb.x * rv.x)),
+                      fmaf(nt.y, rv.z, fmaf(nl.y, rv.y, nb.y * rv.x)),
+                      fmaf(nt.z, rv.z, fmaf(nl.z, rv.y, nb.z * rv.x)));
+        nextdir = normalize3(nextdir);
+        hitpos = mad3(nl, 0.001f, hitpos);
+        ps.mask = mul3(ps.mask, objcol);
+    } else if (mat == MAT_SPEC) {                                        // :190-203 (Q6)
+        const float k = dot3(nl, ps.d) * 2.0f;
+        nextdir = normalize3(mad3(nl, -k, ps.d));
+        hitpos = mad3(nl, 0.001f, hitpos);
+        ps.mask = mul3(ps.mask, objcol);
+    } else if (mat == MAT_REFR) {                                        // :205-256 (Q7)
+        const bool into = dot3(n, nl) > 0.0f;
+        const float nc = p.air, ntr = p.glass;
+        const float nnt = into ? nc / ntr : ntr / nc;
+        const float ddn = dot3(ps.d, nl);
+        const float cos2t = 1.0f - (nnt * nnt) * (1.0f - ddn * ddn);
+        if (cos2t < 0.0f) {
+            const float k = dot3(n, ps.d) * 2.0f;
+            nextdir = normalize3(mad3(n, -k, ps.d));
+        } else {
+            const float s = (into ? 1.0f : -1.0f) * fmaf(ddn, nnt, sqrtf(cos2t));
+            const f3 tdir = normalize3(mad3(n, -s, scale3(ps.d, nnt)));
+            const float R0 = ((ntr - nc) * (ntr - nc)) / (ntr + nc) * (ntr + nc);   // :230 precedence kept
+            const float c = 1.0f - (into ? -ddn : dot3(tdir, n));
+            const float Re = R0 + (1.0f - R0) * c * c * c * c * c;
+            const float Tr = 1.0f - Re;
+            const float P = 0.25f + 0.5f * Re;
+            const float RP = Re / P, TP = Tr / (1.0f - P);
+            if (u.x < 0.2f) {                                            // :239 constant, not P
+                ps.mask = scale3(ps.mask, RP);
+                const float k = dot3(n, ps.d) * 2.0f;
+                nextdir = normalize3(mad3(n, -k, ps.d));
+            } else {
+                ps.mask = scale3(ps.mask, TP);
+                nextdir = normalize3(tdir);
+            }
+        }
+        hitpos = mad3(nl, 0.001f, hitpos);
+    } else {                                                             // METAL :257-293 (Q1)
+        float sphi, cphi; sincos2pi(u.x, sphi, cphi);
+        const float cosT = det_powf(1.0f - u.y, 1.0f / (p.phong + 1.0f));
+        const float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));
+        const float k = dot3(nl, ps.d) * 2.0f;
+        const f3 w1 = normalize3(mad3(nl, -k, ps.d));
+        const f3 uu = normalize3(cross3(fabsf(w1.x) >= 0.1f ? mk3(0, 1, 0) : mk3(1, 0, 0), w1));
+        const f3 vv = cross3(w1, uu);
+        const float a = cphi * sinT, b = sphi * sinT;
+        if (p.flags & RP_METAL_FIXED) {
+            nextdir = mk3(fmaf(w1.x, cosT, fmaf(vv.x, b, uu.x * a)),
+                          fmaf(w1.y, cosT, fmaf(vv.y, b, uu.y * a)),
+                          fmaf(w1.z, cosT, fmaf(vv.z, b, uu.z * a)));
+        } else {
+            const float wc = (float)p.width * cosT;                      // :280 `w` = int image width
+            nextdir = mk3(fmaf(vv.x, b, uu.x * a) + wc, fmaf(vv.y, b, uu.y * a) + wc, fmaf(vv.z, b, uu.z * a) + wc);
+        }
+        nextdir = normalize3(nextdir);
+        hitpos = mad3(nl, 0.0001f, hitpos);
+        ps.mask = mul3(ps.mask, objcol);
+    }
+    ps.o = hitpos; ps.d = nextdir;
+    return true;
+}

@@ -1,0 +1,160 @@
+// gpt_traverse.cuh -- nearest-hit BVH2 traversal + ray/triangle/sphere/box intersection.
+//
+// Replaces intersectBVHandTriangles (cudaUtils.h:256-460), intersectRayTriangleEdge (:135-172),
+// spanBegin/EndKepler (:239-250), intersectAllSpeheres (:221-236), Sphere::intersect
+// (CommomStructs.hpp:23-31) and the Box spec (cudaUtils.h:31-77).
+//
+// Same algorithmic contract as the reference (depth-first, near child first by entry distance,
+// strict t < hitT so the first-visited triangle wins ties), different mechanics:
+//   * one 64-B node = 4 x LDG.128 through the read-only path issued together (the reference
+//     fetches the child pointers with a dependent second load),
+//   * triangles are pre-packed (v0, e1, e2) with the original index / last-in-leaf flag in the w
+//     lanes, so a leaf costs 48 B per triangle and no terminator or index-array read,
+//   * FMNMX min/max instead of the Kepler video instructions,
+//   * leaf postponing voted with __ballot_sync over the currently converged lanes.
+#pragma once
+#include "gpt_scene.cuh"
+
+struct TriHit { float t; int tri; };   // tri = packed triangle index, -1 = none
+
+// Moller-Trumbore on a packed triangle; formulas and test order of cudaUtils.h:143-169.
+// Returns t, or a negative value for a miss.
+__device__ __forceinline__ float tri_test(const float4 a, const float4 b, const float4 c, const f3 o, const f3 d, const bool cull)
+{
+    const f3 v0 = mk3(a.x, a.y, a.z), e1 = mk3(b.x, b.y, b.z), e2 = mk3(c.x, c.y, c.z);
+    const f3 pvec = cross3(d, e2);
+    const float det = dot3(e1, pvec);
+    if (det < -0.00001f) { if (cull) return -1.0f; }
+    else if (det < 0.00001f) return -1.0f;
+    const float invdet = 1.0f / det;
+    const f3 tvec = sub3(o, v0);
+    const float u = dot3(tvec, pvec) * invdet;
+    if (u < 0.0f || u > 1.0f) return -1.0f;
+    const f3 qvec = cross3(tvec, e1);
+    const float v = dot3(d, qvec) * invdet;
+    if (v < 0.0f || (u + v) > 1.0f) return -1.0f;
+    const float t = dot3(e2, qvec) * invdet;
+    return (t > 0.0f && t < GPT_F32_MAX) ? t : -1.0f;
+}
+
+__device__ __forceinline__ float guard_dir(float d)
+{
+    const float ooeps = 8.2718061255302767e-25f;   // 2^-80, cudaUtils.h:283
+    return fabsf(d) > ooeps ? d : copysignf(ooeps, d);
+}
+
+__device__ __forceinline__ TriHit traverse_bvh(const float4* __restrict__ nodes, const float4* __restrict__ tris,
+                                               const f3 o, const f3 d, const bool cull)
+{
+    int stack[GPT_STACK_SIZE];
+    TriHit hit; hit.t = GPT_F32_MAX; hit.tri = -1;
+    const float idx = 1.0f / guard_dir(d.x), idy = 1.0f / guard_dir(d.y), idz = 1.0f / guard_dir(d.z);
+    const float oodx = o.x * idx, oody = o.y * idy, oodz = o.z * idz;
+    int sp = 0;
+    stack[0] = GPT_SENTINEL;
+    int node = 0;      // float4 index of the current inner node (root = 0); <0 = leaf; SENTINEL = done
+    int leaf = 0;      // postponed leaf (<0) or none (>=0)
+
+    while (node != GPT_SENTINEL) {
+        // ---- inner nodes until every converged lane holds a leaf ----
+        while ((unsigned)node < (unsigned)GPT_SENTINEL) {
+            const float4 n0 = __ldg(nodes + node);
+            const float4 n1 = __ldg(nodes + node + 1);
+            const float4 nz = __ldg(nodes + node + 2);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(nodes + node + 3));
+            const float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
+            const float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
+            const float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
+            const float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
+            const float c0loz = fmaf(nz.x, idz, -oodz), c0hiz = fmaf(nz.y, idz, -oodz);
+            const float c1loz = fmaf(nz.z, idz, -oodz), c1hiz = fmaf(nz.w, idz, -oodz);
+            // tmin = 0 (tracer.cu:94): max(...,0) ; tmax = current hitT
+            const float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), 0.0f));
+            const float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), hit.t));
+            const float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), 0.0f));
+            const float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), hit.t));
+            // cudaUtils.h:333-334: (min<=max) && (min>=tmin) && (min<=F32_MAX)
+            const bool t0 = (c0min <= c0max) && (c0min <= GPT_F32_MAX);
+            const bool t1 = (c1min <= c1max) && (c1min <= GPT_F32_MAX);
+            if (!t0 && !t1) {
+                node = stack[sp]; --sp;
+            } else {
+                node = t0 ? ch.x : ch.y;
+                if (t0 && t1) {
+                    int far_child = ch.y;
+                    if (c1min < c0min) { far_child = node; node = ch.y; }
+                    ++sp; stack[sp] = far_child;
+                }
+            }
+            if (node < 0 && leaf >= 0) {         // first leaf: postpone, keep descending
+                leaf = node;
+                node = stack[sp]; --sp;
+            }
+            if (!__any_sync(__activemask(), leaf >= 0)) break;
+        }
+        // ---- leaves ----
+        while (leaf < 0) {
+            for (int ti = ~leaf;; ++ti) {
+                const float4 a = __ldg(tris + 3 * ti);
+                const float4 b = __ldg(tris + 3 * ti + 1);
+                const float4 c = __ldg(tris + 3 * ti + 2);
+                const float t = tri_test(a, b, c, o, d, cull);
+                if (t > 0.0f && t < hit.t) { hit.t = t; hit.tri = ti; }   // cudaUtils.h:428, strict
+                if (__float_as_int(c.w) != 0) break;                      // last triangle of the leaf
+            }
+            leaf = node;
+            if (node < 0) { node = stack[sp]; --sp; }
+        }
+    }
+    return hit;
+}
+
+// Sphere::intersect, CommomStructs.hpp:23-31; s = 11 floats (posRad, emi, col, mat)
+__device__ __forceinline__ float sphere_test(const float* s, const f3 o, const f3 d)
+{
+    const f3 op = sub3(mk3(s[0], s[1], s[2]), o);
+    const float b = dot3(op, d);
+    float disc = fmaf(b, b, -dot3(op, op)) + s[3] * s[3];
+    if (disc < 0.0f) return 0.0f;
+    disc = sqrtf(disc);
+    float t = b - disc;
+    if (t > 0.01f) return t;
+    t = b + disc;
+    return t > 0.01f ? t : 0.0f;
+}
+
+// Box spec, cudaUtils.h:43-58; bx = 13 floats (min, max, emi, col, mat)
+__device__ __forceinline__ float box_test(const float* bx, const f3 o, const f3 d)
+{
+    const float t0x = (bx[0] - o.x) / d.x, t1x = (bx[3] - o.x) / d.x;
+    const float t0y = (bx[1] - o.y) / d.y, t1y = (bx[4] - o.y) / d.y;
+    const float t0z = (bx[2] - o.z) / d.z, t1z = (bx[5] - o.z) / d.z;
+    const float minmax = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+    const float maxmin = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+    if (minmax >= maxmin) return maxmin > 0.001f ? maxmin : 0.0f;
+    return 0.0f;
+}
+
+// Full nearest hit of one bounce: BVH, then the sphere sweep (cudaUtils.h:221-236: a sphere
+// replaces the triangle hit only if strictly closer and > 0.01), then boxes.
+struct SceneHit { float t; int geom; int prim; };   // prim = packed tri / sphere / box index
+
+__device__ __forceinline__ SceneHit intersect_scene(const DevScene& sc, const float* s_spheres, const float* s_boxes,
+                                                    const f3 o, const f3 d, const bool cull)
+{
+    SceneHit h; h.t = GPT_F32_MAX; h.geom = GEO_NONE; h.prim = -1;
+    if (sc.n_nodes > 0) {
+        const TriHit th = traverse_bvh(sc.nodes, sc.tris, o, d, cull);
+        h.t = th.t;
+        if (th.tri >= 0) { h.geom = GEO_TRI; h.prim = th.tri; }
+    }
+    for (int i = 0; i < sc.n_spheres; ++i) {
+        const float t = sphere_test(s_spheres + 11 * i, o, d);
+        if (t != 0.0f && t < h.t && t > 0.01f) { h.t = t; h.geom = GEO_SPHERE; h.prim = i; }
+    }
+    for (int i = 0; i < sc.n_boxes; ++i) {
+        const float t = box_test(s_boxes + 13 * i, o, d);
+        if (t != 0.0f && t < h.t) { h.t = t; h.geom = GEO_BOX; h.prim = i; }
+    }
+    return h;
+}

@@ -1,0 +1,197 @@
+/*
+ * include/gpt.h -- C-ABI of the B200-native progressive path-tracing hot path.
+ *
+ * Drop-in boundary for G.P.U-PathTracer's render launch:
+ *   reference call site   BasicScene::run -> launchKernel(info)     GpuPathTracer/BasicScene.cpp:395-404
+ *   reference definition  void BasicScene::launchKernel(const kernelInfo&)  GpuPathTracer/tracer.cu:405-415
+ *   reference data        kernelInfo / CamInfo / BVHData            GpuPathTracer/CpuStructs.hpp:19-72
+ *                         Sphere / Box / GeoType / Mat              GpuPathTracer/CommomStructs.hpp:11-82
+ *                         node / triangle / index arrays            GpuPathTracer/CudaBVH.hpp:58-66, CudaBVH.cpp:121-270
+ *
+ * Plain C: pointers and sizes only, no C++/torch types.  Every entry returns a gpt_status
+ * (0 = ok, negative = error) and never calls exit() (the reference's checkCudaErrors does,
+ * utilfun.hpp:81-90).  One frame in flight per context, like the reference (BasicScene.cpp:395).
+ * There is NO CPU fallback: without a CUDA device every compute entry returns GPT_ERR_CUDA.
+ */
+#ifndef GPT_H
+#define GPT_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define GPT_API
+#else
+#define GPT_API __attribute__((visibility("default")))
+#endif
+
+typedef enum {
+    GPT_OK = 0,
+    GPT_ERR_INVALID = -1,     /* bad argument */
+    GPT_ERR_CUDA = -2,        /* CUDA runtime error; see gpt_last_error_string */
+    GPT_ERR_NO_SCENE = -3,    /* launch before gpt_upload_scene / without BVH pointers */
+    GPT_ERR_LAYOUT = -4,      /* malformed node/triangle arrays */
+    GPT_ERR_IO = -5
+} gpt_status;
+
+/* CommomStructs.hpp:11-12 -- the enum ORDER is ABI (Mat::METAL == 1, SPEC == 2) */
+typedef enum { GPT_GEO_TRI = 0, GPT_GEO_SPHERE = 1, GPT_GEO_BOX = 2, GPT_GEO_NONE = 3 } gpt_geo_type;
+typedef enum { GPT_MAT_DIFF = 0, GPT_MAT_METAL = 1, GPT_MAT_SPEC = 2, GPT_MAT_REFR = 3 } gpt_mat;
+
+/* Sphere, CommomStructs.hpp:18-39 (44 B) */
+typedef struct { float posRad[4]; float emi[3]; float col[3]; int32_t mat; } gpt_sphere;
+/* Box, CommomStructs.hpp:42-48 (52 B).  A stub in the reference (intersect returns 0);
+ * implemented here from its commented spec cudaUtils.h:31-77. */
+typedef struct { float mn[3]; float mx[3]; float emi[3]; float col[3]; int32_t mat; } gpt_box;
+
+/* CamInfo, CpuStructs.hpp:19-29 (84 B) */
+typedef struct {
+    float front[3], right[3], up[3], pos[3];
+    float dist;
+    float pitch, yaw;
+    float aspect;
+    float fov;
+    uint8_t dirty; uint8_t _pad0[3];
+    float bias[2];
+    uint8_t enabled; uint8_t _pad1[3];
+} gpt_cam_info;
+
+/* BVHData, CpuStructs.hpp:31-42 (48 B): device pointers + element counts (vec4s / ints) */
+typedef struct {
+    void*   dev_triNode;       size_t triNodeSize;
+    int32_t* dev_triIndicesPtr; size_t triIndicesSize;
+    void*   dev_triPtr;        size_t triSize;
+} gpt_bvh_data;
+
+/* kernelInfo, CpuStructs.hpp:45-72 (296 B) -- bit-compatible, so a maintainer's adapter is
+ *   void BasicScene::launchKernel(const kernelInfo& i){ gpt_launch(ctx,(const gpt_kernel_info*)&i,0); } */
+typedef struct {
+    uint32_t blockSize[3]; uint32_t _pad0;   /* dim3; accepted and ignored (persistent grid) */
+    uint64_t hash;                           /* per-frame seed, uf::hash(frame) utilfun.cpp:380-389 */
+    uint32_t* dev_drawRes;                   /* W*H RGBA8 0x00BBGGRR, row 0 = bottom */
+    float*   accumBuffer;                    /* W*H vec3 running mean (legacy contract) */
+    int32_t  width, height;
+    gpt_cam_info cam;
+    uint32_t _pad1;
+    void*    triangleTex;  size_t numVerts;  /* dead brute-force input; ignored */
+    gpt_sphere* sphereTex; size_t numSpheres;
+    uint8_t  cullBackFaces; uint8_t _pad2[3];
+    uint32_t depth;
+    uint64_t constantPdf;                    /* N = samples since last reset */
+    gpt_bvh_data bvhData;
+    float    time_elapsed;                   /* ignored (never written in the reference either) */
+    float    air_ref_index, glass_ref_index;
+    int32_t  triCurrentMat;                  /* gpt_mat */
+    uint8_t  clearBuffer; uint8_t _pad3[3];
+    float    bkColor[3];
+    float    phongExpo;
+    float    emi[3], col[3];
+    uint32_t _pad4;
+} gpt_kernel_info;
+
+/* context flags (gpt_set_flags) */
+enum {
+    GPT_FLAG_NO_JITTER   = 1u << 0,  /* camera jitter off (hit-ID parity runs) */
+    GPT_FLAG_METAL_FIXED = 1u << 1,  /* use the reflection vector w1 instead of the reference's int `w` */
+    GPT_FLAG_WAVEFRONT   = 1u << 2,  /* gpt_render uses the wavefront pipeline instead of the megakernel */
+    GPT_FLAG_COUNT_BOUNCES = 1u << 3 /* fill gpt_stats.rays_by_bounce (slower) */
+};
+
+typedef struct {
+    uint64_t rays;                /* bounce-loop iterations executed since the last gpt_reset_stats */
+    uint64_t rays_by_bounce[16];  /* only with GPT_FLAG_COUNT_BOUNCES */
+    uint64_t paths;               /* (pixel,sample) paths started */
+    uint64_t kernel_launches;     /* library kernels launched */
+} gpt_stats;
+
+typedef struct gpt_ctx gpt_ctx;
+typedef void* gpt_stream;   /* cudaStream_t */
+
+/* ---- lifetime ---- */
+GPT_API int  gpt_create(gpt_ctx** out, int device);          /* replaces uf::findCudaDevice, utilfun.cpp:72-99 */
+GPT_API void gpt_destroy(gpt_ctx* ctx);
+GPT_API int  gpt_set_flags(gpt_ctx* ctx, uint32_t flags);
+GPT_API const char* gpt_last_error_string(gpt_ctx* ctx);     /* ctx may be NULL: last create error */
+GPT_API const char* gpt_version(void);
+GPT_API int  gpt_sync(gpt_ctx* ctx, gpt_stream stream);      /* cudaStreamSynchronize, BasicScene.cpp:395 */
+
+/* ---- scene ---- */
+/* Takes the arrays CudaBVH returns (getGpuNodes/getDebugTri/getGpuTriIndices, CudaBVH.hpp:58-66),
+ * as host (on_device=0) or device (on_device=1) pointers; replaces the cudaMalloc+cudaMemcpy block
+ * BasicScene.cpp:294-313 and the sphere upload :213-216.  The library re-packs them on the device
+ * (see DESIGN.md "HBM layout"); the caller keeps ownership of everything it passes. */
+GPT_API int gpt_upload_scene(gpt_ctx* ctx,
+                             const void* nodes, size_t n_node_vec4,
+                             const void* tris, size_t n_tri_vec4,
+                             const int32_t* tri_indices, size_t n_indices,
+                             const gpt_sphere* spheres, size_t n_spheres,
+                             const gpt_box* boxes, size_t n_boxes,
+                             int on_device);
+
+/* ---- render launch ---- */
+/* Drop-in for launchKernel (tracer.cu:405-415): ONE progressive pass (1 spp) with the reference's
+ * exact field meanings: vec3 running mean with per-frame clamp into info->accumBuffer, RGBA8 pack into
+ * info->dev_drawRes (tracer.cu:386-398), seed = info->hash.  If the BVH/sphere device pointers in
+ * `info` differ from the uploaded scene they are (re-)packed first. Asynchronous on `stream`. */
+GPT_API int gpt_launch(gpt_ctx* ctx, const gpt_kernel_info* info, gpt_stream stream);
+
+/* Native contract: adds `sample_count` samples with GLOBAL indices [sample_begin, sample_begin+count)
+ * to accum_f4 (device, W*H float4 = sum r,g,b + sample count; never clamped).  RNG is keyed by
+ * (seed, pixel, global sample, bounce), so any split of the index range over GPUs gives the same sum.
+ * info->accumBuffer / dev_drawRes / hash / constantPdf are ignored here. */
+GPT_API int gpt_render(gpt_ctx* ctx, const gpt_kernel_info* info, float* accum_f4,
+                       uint64_t seed, uint64_t sample_begin, uint32_t sample_count, gpt_stream stream);
+
+/* mean = sum/count, clamp [0,1], pack like tracer.cu:394-398.  Either output may be NULL. */
+GPT_API int gpt_resolve(gpt_ctx* ctx, const float* accum_f4, int width, int height,
+                        uint32_t* out_rgba8, float* out_rgb_f32, gpt_stream stream);
+
+/* End-to-end convenience with HOST output: zero an internal float4 buffer, render `spp` samples,
+ * resolve, copy RGBA8 (and optionally the float4 sums) back to host memory, synchronise. */
+GPT_API int gpt_render_frame_host(gpt_ctx* ctx, const gpt_kernel_info* info, uint64_t seed,
+                                  uint64_t sample_begin, uint32_t spp,
+                                  uint32_t* host_rgba8, float* host_accum_f4);
+
+/* ---- test hooks / diagnostics ---- */
+/* first bounce of every pixel: geometry type, remapped triangle index (or -1), sphere/box index
+ * (or -1) and hit distance; device or NULL outputs of W*H elements. */
+GPT_API int gpt_trace_primary(gpt_ctx* ctx, const gpt_kernel_info* info, uint64_t seed, uint64_t sample,
+                              int32_t* geom, int32_t* tri_idx, int32_t* prim_idx, float* t, gpt_stream stream);
+/* nearest triangle hit of arbitrary rays (device arrays: o,d = n*3 floats): remapped index,
+ * slot address in the caller's triangle array (as the reference's hitIndex before remap), t */
+GPT_API int gpt_trace_rays(gpt_ctx* ctx, const float* o, const float* d, size_t n, int cull_back_faces,
+                           int32_t* tri_idx, int32_t* tri_addr, float* t, gpt_stream stream);
+GPT_API int gpt_get_stats(gpt_ctx* ctx, gpt_stats* out);      /* synchronises the context's streams */
+GPT_API int gpt_reset_stats(gpt_ctx* ctx);
+
+/* ---- host-side helpers mirroring the reference's scene setup (no GPU needed) ---- */
+GPT_API uint64_t gpt_hash64(uint64_t key);                                   /* uf::hash, utilfun.cpp:380-389 */
+GPT_API int  gpt_default_spheres(gpt_sphere* out, size_t cap, size_t* n);   /* BasicScene.cpp:177-218 */
+GPT_API void gpt_default_kernel_info(gpt_kernel_info* info, int width, int height); /* BasicScene.cpp:220-259 */
+GPT_API void gpt_set_camera(gpt_cam_info* cam, const float pos[3], float yaw_deg, float pitch_deg); /* BasicScene.cpp:42-64 */
+
+#ifdef __cplusplus
+}
+#endif
+
+#ifdef __cplusplus
+#include <cstddef>
+static_assert(sizeof(gpt_sphere) == 44, "Sphere ABI");
+static_assert(sizeof(gpt_box) == 52, "Box ABI");
+static_assert(sizeof(gpt_cam_info) == 84, "CamInfo ABI");
+static_assert(sizeof(gpt_bvh_data) == 48, "BVHData ABI");
+static_assert(sizeof(gpt_kernel_info) == 296, "kernelInfo ABI");
+static_assert(offsetof(gpt_kernel_info, accumBuffer) == 32, "kernelInfo.accumBuffer");
+static_assert(offsetof(gpt_kernel_info, cam) == 48, "kernelInfo.cam");
+static_assert(offsetof(gpt_kernel_info, sphereTex) == 152, "kernelInfo.sphereTex");
+static_assert(offsetof(gpt_kernel_info, depth) == 172, "kernelInfo.depth");
+static_assert(offsetof(gpt_kernel_info, constantPdf) == 176, "kernelInfo.constantPdf");
+static_assert(offsetof(gpt_kernel_info, bvhData) == 184, "kernelInfo.bvhData");
+static_assert(offsetof(gpt_kernel_info, triCurrentMat) == 244, "kernelInfo.triCurrentMat");
+static_assert(offsetof(gpt_kernel_info, bkColor) == 252, "kernelInfo.bkColor");
+static_assert(offsetof(gpt_kernel_info, emi) == 268, "kernelInfo.emi");
+#endif
+#endif /* GPT_H */
