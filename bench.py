@@ -186,19 +186,30 @@ def time_oracle_port(gpt, sc, args, rows, threads):
     return cnt.rays, secs, cnt.algorithmic_bytes() / max(1, cnt.rays)
 
 
+def sized_rows(probe_rows, probe_secs, target_secs, height):
+    """rows of the frame that should take about target_secs, from a short probe run"""
+    rate = probe_rows / max(probe_secs, 1e-3)
+    return int(max(probe_rows, min(height, rate * target_secs)))
+
+
 def cpu_baseline(gpt, sc, args):
+    """Bounded samples (~12 s each) of the same workload on all host cores: the reference CPU tracer
+    (kind=reference) and the scalar oracle port of the GPU algorithm (kind=port)."""
     threads = os.cpu_count() or 1
-    # size the sample for ~10-30 s: the reference CPU tracer does roughly 0.1-0.3 Mrays/s/core
-    rows = max(2, min(args.height, int(4 * threads)))
-    r = time_cpuref(sc, args, rows, threads)
+    probe = max(2, min(args.height, 2 * threads))
     out = None
+    r = time_cpuref(sc, args, probe, threads)
     if r is not None and r[1] > 0:
+        rows = sized_rows(probe, r[1], 12.0, args.height)
+        r = time_cpuref(sc, args, rows, threads)
         out = {"value": r[0] / r[1] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference",
                "sample": "%d of %d rows at %dx%d, %d spp (reference CpuRayTracer: own scene/tree/RR, throughput only); %.1f s; cpu=%s"
                          % (rows, args.height, args.width, args.height, args.spp, r[1], cpu_model())}
+    o = time_oracle_port(gpt, sc, args, probe, threads)
+    rows = sized_rows(probe, o[1], 12.0, args.height)
     o = time_oracle_port(gpt, sc, args, rows, threads)
     port = {"value": o[0] / o[1] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
-            "sample": "%d rows, %d spp, scalar oracle with OpenMP over rows; %.1f s" % (rows, args.spp, o[1]),
+            "sample": "%d of %d rows, %d spp, scalar oracle with OpenMP over rows; %.1f s" % (rows, args.height, args.spp, o[1]),
             "bytes_per_ray_sample": o[2]}
     if out is None:
         return port, None
@@ -213,8 +224,12 @@ def run_reference_arm(args):
     import gpt_b200 as gpt      # host-only helpers (scene preset); no GPU used on this arm
     sc = load_scene_arrays()
     threads = os.cpu_count() or 1
-    rows = max(2, min(args.height, int(2 * threads)))
-    if cpuref_lib(sc) is None:
+    probe = max(2, min(args.height, int(2 * threads)))
+    have_ref = cpuref_lib(sc) is not None
+    pr = time_cpuref(sc, args, probe, threads) if have_ref else time_oracle_port(gpt, sc, args, probe, threads)
+    # whole run (warmup + steps) bounded to about two minutes of CPU time
+    rows = sized_rows(probe, pr[1], 120.0 / max(1, args.steps + args.warmup), args.height)
+    if not have_ref:
         # oracle/_ref absent (reference never compiled on this snapshot): time the oracle port instead
         kind = "port"
 
@@ -271,7 +286,7 @@ def run_ours(args):
     sc = load_scene_arrays()
     sph = bench_spheres(gpt)
     info = bench_info(gpt, args)
-    flags = gpt.FLAG_WAVEFRONT if args.pipeline == "wavefront" else 0
+    flags = gpt.FLAG_MEGAKERNEL if args.pipeline == "mega" else 0
     ctx = gpt.Context(local, flags)
     ctx.upload_scene(sc["nodes"], sc["tris"], sc["indices"], sph)
     frame = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
@@ -335,7 +350,7 @@ def run_ours(args):
     total_rays = float(rays.item())
     launches = int(st.kernel_launches)
     # ---- e2e: same steps through the C-ABI with HOST output, D2H (+ the 296-B kernelInfo H2D) inside the timing ----
-    if world == 1 and args.pipeline == "mega":
+    if world == 1:
         def e2e_step(i):
             flush.zero_()
             ctx.render_frame_host(info, args.seed, i * SPP, SPP, host_rgba, None)     # gpt_render_frame_host: host buffers
@@ -387,7 +402,7 @@ def run_ours(args):
                             if world == 1 else "render + NCCL reduce + resolve + RGBA8 D2H to pinned host on rank 0, sync per step"},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
-                         "kernel": "k_render_mega<false>", "kernel_ms_avg": k_avg_ms, "kernel_share_of_step": k_avg_ms * len(kernel_ms) / ms,
+                         "kernel": "k_render_mega<false>" if args.pipeline == "mega" else "k_wf_extend_ww (+ k_wf_shade, k_wf_generate, k_wf_accumulate: whole gpt_render pass timed)", "kernel_ms_avg": k_avg_ms, "kernel_share_of_step": k_avg_ms * len(kernel_ms) / ms,
                          "algorithmic_bytes_per_ray": bpr, "rays_per_launch": rays_per_launch, "peak_source": peak_src,
                          "note": "scene is L1/L2 resident, so the HBM fraction is low by construction; see profiles/ for L1/L2/issue-slot counters"},
             "clocks": sampler.summary(),
@@ -416,7 +431,7 @@ def main():
     ap.add_argument("--spp", type=int, default=16)
     ap.add_argument("--depth", type=int, default=8)
     ap.add_argument("--seed", type=int, default=0)
-    ap.add_argument("--pipeline", default="mega", choices=["mega", "wavefront"])
+    ap.add_argument("--pipeline", default="wavefront", choices=["mega", "wavefront"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

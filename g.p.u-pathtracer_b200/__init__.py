@@ -23,7 +23,7 @@ DIFF, METAL, SPEC, REFR = 0, 1, 2, 3
 
 FLAG_NO_JITTER = 1 << 0
 FLAG_METAL_FIXED = 1 << 1
-FLAG_WAVEFRONT = 1 << 2
+FLAG_MEGAKERNEL = 1 << 2
 FLAG_COUNT_BOUNCES = 1 << 3
 
 

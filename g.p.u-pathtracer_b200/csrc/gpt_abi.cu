@@ -7,6 +7,7 @@
 #include "gpt_kernels.h"
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <new>
 #include <string>
 
@@ -26,6 +27,7 @@ struct gpt_ctx {
     unsigned int* work_counter = nullptr;
     unsigned long long* stats = nullptr;       // [0]=rays [1]=paths [2..17]=rays by bounce
     float4* frame_accum = nullptr; uint32_t* frame_rgba = nullptr; size_t frame_pixels = 0;
+    WaveBuffers wave = {}; size_t wave_pixels = 0; size_t wave_counters = 0;   // wavefront scratch
     unsigned long long launches = 0;
     std::string err;
 };
@@ -65,8 +67,8 @@ int gpt_create(gpt_ctx** out, int device)
     if (e != cudaSuccess) { delete c; return fail(nullptr, GPT_ERR_CUDA, "cudaGetDeviceProperties", e); }
     c->sm_count = prop.multiProcessorCount;
     if ((e = cudaMalloc(&c->work_counter, sizeof(unsigned int))) != cudaSuccess ||
-        (e = cudaMalloc(&c->stats, 18 * sizeof(unsigned long long))) != cudaSuccess ||
-        (e = cudaMemset(c->stats, 0, 18 * sizeof(unsigned long long))) != cudaSuccess) {
+        (e = cudaMalloc(&c->stats, 32 * sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMemset(c->stats, 0, 32 * sizeof(unsigned long long))) != cudaSuccess) {
         cudaFree(c->work_counter); cudaFree(c->stats); delete c;
         return fail(nullptr, GPT_ERR_CUDA, "gpt_create: scratch allocation", e);
     }
@@ -83,6 +85,31 @@ static void free_scene(gpt_ctx* c)
     c->src_nodes = c->src_tris = c->src_idx = nullptr;
 }
 
+static void free_wave(gpt_ctx* c)
+{
+    WaveBuffers& w = c->wave;
+    cudaFree(w.ray_o); cudaFree(w.ray_d); cudaFree(w.mask); cudaFree(w.accu); cudaFree(w.lsum); cudaFree(w.hit);
+    cudaFree(w.queue[0]); cudaFree(w.queue[1]); cudaFree(w.counters);
+    w = WaveBuffers{}; c->wave_pixels = 0; c->wave_counters = 0;
+}
+
+// wavefront scratch: one entry per pixel (72 B + 2 queue slots), grown on demand
+static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth)
+{
+    const size_t nc = gptk_wave_counter_count(depth);
+    if (c->wave_pixels >= n_pix && c->wave_counters >= nc) return GPT_OK;
+    CU(c, cudaDeviceSynchronize());
+    free_wave(c);
+    WaveBuffers& w = c->wave;
+    CU(c, cudaMalloc(&w.ray_o, n_pix * sizeof(float4))); CU(c, cudaMalloc(&w.ray_d, n_pix * sizeof(float4)));
+    CU(c, cudaMalloc(&w.mask, n_pix * sizeof(float4)));  CU(c, cudaMalloc(&w.accu, n_pix * sizeof(float4)));
+    CU(c, cudaMalloc(&w.lsum, n_pix * sizeof(float4)));  CU(c, cudaMalloc(&w.hit, n_pix * sizeof(int2)));
+    CU(c, cudaMalloc(&w.queue[0], n_pix * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], n_pix * sizeof(uint32_t)));
+    CU(c, cudaMalloc(&w.counters, nc * sizeof(unsigned int)));
+    c->wave_pixels = n_pix; c->wave_counters = nc;
+    return GPT_OK;
+}
+
 void gpt_destroy(gpt_ctx* c)
 {
     if (!c) return;
@@ -90,6 +117,7 @@ void gpt_destroy(gpt_ctx* c)
     cudaDeviceSynchronize();
     free_scene(c);
     cudaFree(c->work_counter); cudaFree(c->stats); cudaFree(c->frame_accum); cudaFree(c->frame_rgba);
+    free_wave(c);
     delete c;
 }
 
@@ -235,10 +263,17 @@ int gpt_launch(gpt_ctx* c, const gpt_kernel_info* info, gpt_stream stream)
     RenderParams p; DevScene sc;
     int rc = make_params(c, info, info->hash, &p); if (rc) return rc;
     rc = launch_scene(c, info, &sc); if (rc) return rc;
-    cudaError_t e = gptk_render_legacy(sc, p, info->accumBuffer, info->dev_drawRes, info->constantPdf,
-                                       c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
+    cudaError_t e;
+    if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
+        rc = ensure_wave(c, (size_t)p.width * p.height, p.depth); if (rc) return rc;
+        e = gptk_render_wavefront(sc, p, c->wave, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u,
+                                  c->stats, c->sm_count, (cudaStream_t)stream, &c->launches);
+    } else {
+        e = gptk_render_legacy(sc, p, info->accumBuffer, info->dev_drawRes, info->constantPdf,
+                               c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
+        c->launches += 1;
+    }
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "render launch", e);
-    c->launches += 1;
     return GPT_OK;
 }
 
@@ -251,10 +286,17 @@ int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_
     RenderParams p; DevScene sc;
     int rc = make_params(c, info, seed, &p); if (rc) return rc;
     rc = launch_scene(c, info, &sc); if (rc) return rc;
-    cudaError_t e = gptk_render_mega(sc, p, reinterpret_cast<float4*>(accum_f4), sample_begin, sample_count,
-                                     c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
+    cudaError_t e;
+    if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
+        rc = ensure_wave(c, (size_t)p.width * p.height, p.depth); if (rc) return rc;
+        e = gptk_render_wavefront(sc, p, c->wave, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count,
+                                  c->stats, c->sm_count, (cudaStream_t)stream, &c->launches);
+    } else {
+        e = gptk_render_mega(sc, p, reinterpret_cast<float4*>(accum_f4), sample_begin, sample_count,
+                             c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
+        c->launches += 1;
+    }
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "render launch", e);
-    c->launches += 1;
     return GPT_OK;
 }
 
@@ -322,7 +364,7 @@ int gpt_get_stats(gpt_ctx* c, gpt_stats* out)
     if (!c || !out) return GPT_ERR_INVALID;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaDeviceSynchronize());
-    unsigned long long h[18];
+    unsigned long long h[32];
     CU(c, cudaMemcpy(h, c->stats, sizeof(h), cudaMemcpyDeviceToHost));
     out->rays = h[0]; out->paths = h[1];
     for (int i = 0; i < 16; ++i) out->rays_by_bounce[i] = h[2 + i];
@@ -335,7 +377,7 @@ int gpt_reset_stats(gpt_ctx* c)
     if (!c) return GPT_ERR_INVALID;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaDeviceSynchronize());
-    CU(c, cudaMemset(c->stats, 0, 18 * sizeof(unsigned long long)));
+    CU(c, cudaMemset(c->stats, 0, 32 * sizeof(unsigned long long)));
     c->launches = 0;
     return GPT_OK;
 }

@@ -9,6 +9,7 @@
 // accumulation buffer and a deterministic summation order.
 #include "gpt_shade.cuh"
 #include "gpt_kernels.h"
+#include <cstdlib>
 
 #define MEGA_THREADS 128
 #define TILE_W 8
@@ -67,11 +68,52 @@ k_render_mega(const DevScene sc, const RenderParams p, float4* __restrict__ accu
     bool have_job = false, done = false;
     int px = 0, py = 0; uint32_t pixel = 0, s = 0, bounce = 0;
     PathState ps;
+    TravState ts;
+    int stack[GPT_STACK_SIZE];
     f3 sum = mk3(0.0f, 0.0f, 0.0f);
     unsigned long long n_rays = 0, n_paths = 0;
+    const bool has_mesh = sc.n_nodes > 0;
+    ts.node = GPT_SENTINEL; ts.leaf = 0; ts.sp = 0; ts.t = GPT_F32_MAX; ts.tri = -1; ts.tri_cur = 0;
 
+    // One trip = for every lane: finish the previous bounce (sphere sweep + shading), move on to the next
+    // sample / pixel if the path ended, arm the next ray, then traverse it to completion (while-while).
+    // Schedules that re-arm lanes mid-traversal were measured and lost (profiles/r01_schedules.md): in a
+    // megakernel re-arming costs a full shading step.  The wavefront pipeline (gpt_wavefront.cu), where
+    // re-arming is a 32-byte load, is the default for gpt_render; this kernel is the single-launch alternative.
     while (true) {
-        // ---- warp-level work fetch: one atomic for all idle lanes ----
+        // ---- finish the bounce whose traversal just ended: tracer.cu:98-296 ----
+        if (have_job && bounce < p.depth) {
+            const SceneHit h = finish_scene_hit(sc, s_spheres, s_boxes, ts.t, ts.tri, ps.o, ps.d);
+            const bool cont = shade_bounce(sc, p, s_spheres, s_boxes, h, pixel, sample_begin + s, bounce, ps);
+            ++bounce;
+            if (!cont) bounce = p.depth;                     // miss: path over (ps.accu = bkColor)
+        }
+        if (have_job && bounce >= p.depth) {
+            // path finished: result = ps.accu (tracer.cu:305, or bkColor on a miss :141)
+            sum.x += ps.accu.x; sum.y += ps.accu.y; sum.z += ps.accu.z;
+            ++s;
+            if (s < sample_count) {
+                bounce = 0;
+                start_path(p, px, py, pixel, sample_begin + s, ps); ++n_paths;
+            } else {
+                if (LEGACY) {
+                    // tracer.cu:386-398
+                    const float nm1 = (float)(constant_pdf - 1ull), inv = 1.0f / (float)constant_pdf;
+                    float* a = accum_v3 + 3 * (size_t)pixel;
+                    const float ax = clamp01((a[0] * nm1 + sum.x) * inv);
+                    const float ay = clamp01((a[1] * nm1 + sum.y) * inv);
+                    const float az = clamp01((a[2] * nm1 + sum.z) * inv);
+                    a[0] = ax; a[1] = ay; a[2] = az;
+                    if (draw) draw[pixel] = pack_rgb(ax, ay, az);
+                } else {
+                    float4 a = accum_f4[pixel];
+                    a.x += sum.x; a.y += sum.y; a.z += sum.z; a.w += (float)sample_count;
+                    accum_f4[pixel] = a;
+                }
+                have_job = false;
+            }
+        }
+        // ---- warp-level work fetch: one atomic for all lanes that need a pixel ----
         const unsigned need = __ballot_sync(GPT_FULL_MASK, !have_job && !done);
         if (need) {
             const int leader = __ffs(need) - 1;
@@ -89,49 +131,22 @@ k_render_mega(const DevScene sc, const RenderParams p, float4* __restrict__ accu
                         have_job = true; pixel = (uint32_t)(py * p.width + px);
                         s = 0; bounce = 0; sum = mk3(0.0f, 0.0f, 0.0f);
                         start_path(p, px, py, pixel, sample_begin, ps); ++n_paths;
-                    }
+                    }                                        // else: off-image slot of an edge tile, fetch again next trip
                 }
             }
         }
-        if (!__any_sync(GPT_FULL_MASK, have_job)) {
-            if (__all_sync(GPT_FULL_MASK, done)) break;
-            continue;
-        }
-        if (have_job) {
-            // ---- one bounce: tracer.cu:72-300 ----
-            bool alive = bounce < p.depth;
-            if (alive) {
-                ++n_rays;
-                if (count_bounces && bounce < 16) atomicAdd(&sm.bounce_cnt[bounce], 1ull);
-                const SceneHit h = intersect_scene(sc, s_spheres, s_boxes, ps.o, ps.d, cull);
-                alive = shade_bounce(sc, p, s_spheres, s_boxes, h, pixel, sample_begin + s, bounce, ps);
-                ++bounce;
-                alive = alive && (bounce < p.depth);
-            }
-            if (!alive) {
-                // path finished: result = ps.accu (tracer.cu:305, or bkColor on a miss :141)
-                sum.x += ps.accu.x; sum.y += ps.accu.y; sum.z += ps.accu.z;
-                ++s;
-                if (s < sample_count) {
-                    bounce = 0;
-                    start_path(p, px, py, pixel, sample_begin + s, ps); ++n_paths;
-                } else {
-                    if (LEGACY) {
-                        // tracer.cu:386-398
-                        const float nm1 = (float)(constant_pdf - 1ull), inv = 1.0f / (float)constant_pdf;
-                        float* a = accum_v3 + 3 * (size_t)pixel;
-                        const float ax = clamp01((a[0] * nm1 + sum.x) * inv);
-                        const float ay = clamp01((a[1] * nm1 + sum.y) * inv);
-                        const float az = clamp01((a[2] * nm1 + sum.z) * inv);
-                        a[0] = ax; a[1] = ay; a[2] = az;
-                        if (draw) draw[pixel] = pack_rgb(ax, ay, az);
-                    } else {
-                        float4 a = accum_f4[pixel];
-                        a.x += sum.x; a.y += sum.y; a.z += sum.z; a.w += (float)sample_count;
-                        accum_f4[pixel] = a;
-                    }
-                    have_job = false;
+        if (__all_sync(GPT_FULL_MASK, done && !have_job)) break;
+        // ---- arm and traverse the next ray of this lane's path (tracer.cu:72,94) ----
+        if (have_job && bounce < p.depth) {
+            ++n_rays;
+            if (count_bounces && bounce < 16) atomicAdd(&sm.bounce_cnt[bounce], 1ull);
+            trav_init(ts, stack, ps.o, ps.d, has_mesh);
+            while (!trav_finished(ts)) {
+                while (trav_wants_node(ts)) {
+                    node_step(sc.nodes, ts, stack);
+                    if (!__any_sync(__activemask(), ts.leaf >= 0)) break;
                 }
+                while (trav_wants_tri(ts)) tri_step(sc.tris, ts, stack, ps.o, ps.d, cull);
             }
         }
     }

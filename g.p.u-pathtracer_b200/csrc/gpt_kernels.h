@@ -21,3 +21,16 @@ cudaError_t gptk_resolve(const float4* accum, int n, uint32_t* rgba8, float* rgb
 struct RepackResult { float4* nodes; float4* tris; int n_nodes; int n_tris; int bad_layout; };
 cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float4* ref_tris, size_t n_tri_vec4,
                         const int* ref_indices, size_t n_indices, RepackResult* out, cudaStream_t st);
+
+// wavefront pipeline (gpt_wavefront.cu).  All buffers hold one entry per pixel of the frame.
+struct WaveBuffers {
+    float4 *ray_o, *ray_d, *mask, *accu, *lsum;
+    int2* hit;
+    uint32_t* queue[2];
+    unsigned int* counters;     // gptk_wave_counter_count(depth) entries
+};
+size_t gptk_wave_counter_count(unsigned int depth);
+cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,
+                                  float4* accum_f4, float* accum_v3, uint32_t* draw, unsigned long long constant_pdf,
+                                  unsigned long long sample_begin, uint32_t sample_count,
+                                  unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches);

@@ -43,69 +43,111 @@ __device__ __forceinline__ float guard_dir(float d)
     return fabsf(d) > ooeps ? d : copysignf(ooeps, d);
 }
 
+// Per-lane traversal state.  Two ways to drive it:
+//   * traverse_bvh(): the classic while-while loop (inner nodes until the converged lanes all hold a leaf,
+//     then the leaves) run to completion -- used by the test hooks;
+//   * node_step()/tri_step(): ONE inner-node visit or ONE triangle test per call -- used by the render
+//     megakernel, whose warps vote each trip on which kind of step to run (see gpt_kernels.cu).
+// Both visit nodes and triangles of a ray in the same depth-first, near-child-first order as the reference
+// (cudaUtils.h:298-448), so (hitT, hit triangle) -- including ties -- are identical.
+struct TravState {
+    float idx, idy, idz;      // 1/dir (2^-80 guarded, cudaUtils.h:283-286)
+    float oodx, oody, oodz;   // origin/dir
+    float t;                  // closest hit so far (hitT)
+    int   tri;                // packed triangle index of that hit, -1 = none
+    int   node;               // float4 index of the current inner node; <0 a second leaf; SENTINEL = stack empty
+    int   leaf;               // postponed leaf (<0) or none (>=0)
+    int   tri_cur;            // next triangle of the postponed leaf to test
+    int   sp;
+};
+
+__device__ __forceinline__ void trav_init(TravState& s, int* stack, const f3 o, const f3 d, const bool has_mesh)
+{
+    s.idx = 1.0f / guard_dir(d.x); s.idy = 1.0f / guard_dir(d.y); s.idz = 1.0f / guard_dir(d.z);
+    s.oodx = o.x * s.idx; s.oody = o.y * s.idy; s.oodz = o.z * s.idz;
+    s.t = GPT_F32_MAX; s.tri = -1;
+    s.sp = 0; stack[0] = GPT_SENTINEL;
+    s.node = has_mesh ? 0 : GPT_SENTINEL;    // root = float4 index 0
+    s.leaf = 0; s.tri_cur = 0;
+}
+
+__device__ __forceinline__ bool trav_wants_node(const TravState& s) { return (unsigned)s.node < (unsigned)GPT_SENTINEL; }
+__device__ __forceinline__ bool trav_wants_tri(const TravState& s) { return s.leaf < 0; }
+__device__ __forceinline__ bool trav_finished(const TravState& s) { return s.node == GPT_SENTINEL && s.leaf >= 0; }
+
+// One inner-node visit: cudaUtils.h:305-369.  Requires trav_wants_node(s).
+__device__ __forceinline__ void node_step(const float4* __restrict__ nodes, TravState& s, int* stack)
+{
+    const int node = s.node;
+    const float4 n0 = __ldg(nodes + node);
+    const float4 n1 = __ldg(nodes + node + 1);
+    const float4 nz = __ldg(nodes + node + 2);
+    const int4 ch = __ldg(reinterpret_cast<const int4*>(nodes + node + 3));
+    const float c0lox = fmaf(n0.x, s.idx, -s.oodx), c0hix = fmaf(n0.y, s.idx, -s.oodx);
+    const float c0loy = fmaf(n0.z, s.idy, -s.oody), c0hiy = fmaf(n0.w, s.idy, -s.oody);
+    const float c1lox = fmaf(n1.x, s.idx, -s.oodx), c1hix = fmaf(n1.y, s.idx, -s.oodx);
+    const float c1loy = fmaf(n1.z, s.idy, -s.oody), c1hiy = fmaf(n1.w, s.idy, -s.oody);
+    const float c0loz = fmaf(nz.x, s.idz, -s.oodz), c0hiz = fmaf(nz.y, s.idz, -s.oodz);
+    const float c1loz = fmaf(nz.z, s.idz, -s.oodz), c1hiz = fmaf(nz.w, s.idz, -s.oodz);
+    // tmin = 0 (tracer.cu:94): max(...,0) ; tmax = current hitT
+    const float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), 0.0f));
+    const float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), s.t));
+    const float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), 0.0f));
+    const float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), s.t));
+    // cudaUtils.h:333-334: (min<=max) && (min>=tmin) && (min<=F32_MAX)
+    const bool t0 = (c0min <= c0max) && (c0min <= GPT_F32_MAX);
+    const bool t1 = (c1min <= c1max) && (c1min <= GPT_F32_MAX);
+    int next;
+    if (!t0 && !t1) {
+        next = stack[s.sp]; --s.sp;
+    } else {
+        next = t0 ? ch.x : ch.y;
+        if (t0 && t1) {
+            int far_child = ch.y;
+            if (c1min < c0min) { far_child = next; next = ch.y; }
+            ++s.sp; stack[s.sp] = far_child;
+        }
+    }
+    if (next < 0 && s.leaf >= 0) {           // first leaf: postpone it and keep descending (:362-369)
+        s.leaf = next; s.tri_cur = ~next;
+        next = stack[s.sp]; --s.sp;
+    }
+    s.node = next;
+}
+
+// One triangle of the postponed leaf: cudaUtils.h:405-446.  Requires trav_wants_tri(s).
+__device__ __forceinline__ void tri_step(const float4* __restrict__ tris, TravState& s, int* stack,
+                                         const f3 o, const f3 d, const bool cull)
+{
+    const int ti = s.tri_cur;
+    const float4 a = __ldg(tris + 3 * ti);
+    const float4 b = __ldg(tris + 3 * ti + 1);
+    const float4 c = __ldg(tris + 3 * ti + 2);
+    const float t = tri_test(a, b, c, o, d, cull);
+    if (t > 0.0f && t < s.t) { s.t = t; s.tri = ti; }        // :428, strict: first visited wins ties
+    if (__float_as_int(c.w) != 0) {                          // last triangle of the leaf
+        s.leaf = s.node;                                     // :440 another leaf was reached meanwhile?
+        if (s.node < 0) { s.tri_cur = ~s.node; s.node = stack[s.sp]; --s.sp; }
+    } else {
+        s.tri_cur = ti + 1;
+    }
+}
+
 __device__ __forceinline__ TriHit traverse_bvh(const float4* __restrict__ nodes, const float4* __restrict__ tris,
                                                const f3 o, const f3 d, const bool cull)
 {
     int stack[GPT_STACK_SIZE];
-    TriHit hit; hit.t = GPT_F32_MAX; hit.tri = -1;
-    const float idx = 1.0f / guard_dir(d.x), idy = 1.0f / guard_dir(d.y), idz = 1.0f / guard_dir(d.z);
-    const float oodx = o.x * idx, oody = o.y * idy, oodz = o.z * idz;
-    int sp = 0;
-    stack[0] = GPT_SENTINEL;
-    int node = 0;      // float4 index of the current inner node (root = 0); <0 = leaf; SENTINEL = done
-    int leaf = 0;      // postponed leaf (<0) or none (>=0)
-
-    while (node != GPT_SENTINEL) {
-        // ---- inner nodes until every converged lane holds a leaf ----
-        while ((unsigned)node < (unsigned)GPT_SENTINEL) {
-            const float4 n0 = __ldg(nodes + node);
-            const float4 n1 = __ldg(nodes + node + 1);
-            const float4 nz = __ldg(nodes + node + 2);
-            const int4 ch = __ldg(reinterpret_cast<const int4*>(nodes + node + 3));
-            const float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
-            const float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
-            const float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
-            const float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
-            const float c0loz = fmaf(nz.x, idz, -oodz), c0hiz = fmaf(nz.y, idz, -oodz);
-            const float c1loz = fmaf(nz.z, idz, -oodz), c1hiz = fmaf(nz.w, idz, -oodz);
-            // tmin = 0 (tracer.cu:94): max(...,0) ; tmax = current hitT
-            const float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), 0.0f));
-            const float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), hit.t));
-            const float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), 0.0f));
-            const float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), hit.t));
-            // cudaUtils.h:333-334: (min<=max) && (min>=tmin) && (min<=F32_MAX)
-            const bool t0 = (c0min <= c0max) && (c0min <= GPT_F32_MAX);
-            const bool t1 = (c1min <= c1max) && (c1min <= GPT_F32_MAX);
-            if (!t0 && !t1) {
-                node = stack[sp]; --sp;
-            } else {
-                node = t0 ? ch.x : ch.y;
-                if (t0 && t1) {
-                    int far_child = ch.y;
-                    if (c1min < c0min) { far_child = node; node = ch.y; }
-                    ++sp; stack[sp] = far_child;
-                }
-            }
-            if (node < 0 && leaf >= 0) {         // first leaf: postpone, keep descending
-                leaf = node;
-                node = stack[sp]; --sp;
-            }
-            if (!__any_sync(__activemask(), leaf >= 0)) break;
+    TravState s;
+    trav_init(s, stack, o, d, true);
+    while (!trav_finished(s)) {
+        // inner nodes until every converged lane holds a leaf (or ran out of nodes)
+        while (trav_wants_node(s)) {
+            node_step(nodes, s, stack);
+            if (!__any_sync(__activemask(), s.leaf >= 0)) break;
         }
-        // ---- leaves ----
-        while (leaf < 0) {
-            for (int ti = ~leaf;; ++ti) {
-                const float4 a = __ldg(tris + 3 * ti);
-                const float4 b = __ldg(tris + 3 * ti + 1);
-                const float4 c = __ldg(tris + 3 * ti + 2);
-                const float t = tri_test(a, b, c, o, d, cull);
-                if (t > 0.0f && t < hit.t) { hit.t = t; hit.tri = ti; }   // cudaUtils.h:428, strict
-                if (__float_as_int(c.w) != 0) break;                      // last triangle of the leaf
-            }
-            leaf = node;
-            if (node < 0) { node = stack[sp]; --sp; }
-        }
+        while (trav_wants_tri(s)) tri_step(tris, s, stack, o, d, cull);
     }
+    TriHit hit; hit.t = s.t; hit.tri = s.tri;
     return hit;
 }
 
@@ -139,15 +181,12 @@ __device__ __forceinline__ float box_test(const float* bx, const f3 o, const f3 
 // replaces the triangle hit only if strictly closer and > 0.01), then boxes.
 struct SceneHit { float t; int geom; int prim; };   // prim = packed tri / sphere / box index
 
-__device__ __forceinline__ SceneHit intersect_scene(const DevScene& sc, const float* s_spheres, const float* s_boxes,
-                                                    const f3 o, const f3 d, const bool cull)
+// sphere sweep (cudaUtils.h:221-236) + boxes on top of a finished BVH result
+__device__ __forceinline__ SceneHit finish_scene_hit(const DevScene& sc, const float* s_spheres, const float* s_boxes,
+                                                     const float tri_t, const int tri, const f3 o, const f3 d)
 {
-    SceneHit h; h.t = GPT_F32_MAX; h.geom = GEO_NONE; h.prim = -1;
-    if (sc.n_nodes > 0) {
-        const TriHit th = traverse_bvh(sc.nodes, sc.tris, o, d, cull);
-        h.t = th.t;
-        if (th.tri >= 0) { h.geom = GEO_TRI; h.prim = th.tri; }
-    }
+    SceneHit h; h.t = tri_t; h.geom = GEO_NONE; h.prim = -1;
+    if (tri >= 0) { h.geom = GEO_TRI; h.prim = tri; }
     for (int i = 0; i < sc.n_spheres; ++i) {
         const float t = sphere_test(s_spheres + 11 * i, o, d);
         if (t != 0.0f && t < h.t && t > 0.01f) { h.t = t; h.geom = GEO_SPHERE; h.prim = i; }
@@ -157,4 +196,12 @@ __device__ __forceinline__ SceneHit intersect_scene(const DevScene& sc, const fl
         if (t != 0.0f && t < h.t) { h.t = t; h.geom = GEO_BOX; h.prim = i; }
     }
     return h;
+}
+
+__device__ __forceinline__ SceneHit intersect_scene(const DevScene& sc, const float* s_spheres, const float* s_boxes,
+                                                    const f3 o, const f3 d, const bool cull)
+{
+    TriHit th; th.t = GPT_F32_MAX; th.tri = -1;
+    if (sc.n_nodes > 0) th = traverse_bvh(sc.nodes, sc.tris, o, d, cull);
+    return finish_scene_hit(sc, s_spheres, s_boxes, th.t, th.tri, o, d);
 }

@@ -1,0 +1,322 @@
+// gpt_wavefront.cu -- wavefront form of the render pass (north_star item 2: "wavefront pipeline with compacted
+// ray queues").  Same per-sample arithmetic as the megakernel (gpt_shade.cuh / gpt_traverse.cuh), so both
+// produce bit-identical images; what changes is the schedule:
+//
+//   wave = every pixel of the frame x ONE global sample index          (path id == pixel index)
+//   k_wf_generate : camera ray + path state for the whole wave                       (tracer.cu:61-69)
+//   per bounce    : k_wf_extend  persistent warps pull rays from the queue and traverse the BVH; a lane
+//                                whose ray ends is re-armed with the next queued ray (a 32-byte load), so
+//                                short rays never wait for long ones                  (cudaUtils.h:256-460)
+//                   k_wf_shade   one thread per surviving path: sphere sweep, shading, next ray, and
+//                                compaction of the survivors into the next queue      (tracer.cu:98-296)
+//   k_wf_accumulate : launch sums -> caller's accumulation buffer                    (tracer.cu:386-398)
+//
+// ncu evidence for this choice over the megakernel is in profiles/ (r01_mega_*): with secondary rays the
+// per-ray traversal length is heavy tailed (mean 10.8 node+triangle steps, ~41 for the slowest lane of a
+// warp), and in a megakernel re-arming a finished lane costs a whole shading step.
+#include "gpt_shade.cuh"
+#include "gpt_kernels.h"
+#include <cstdlib>
+
+#define WF_THREADS 128
+
+struct SmemPrims {
+    float spheres[GPT_MAX_SMEM_SPHERES * 11];
+    float boxes[GPT_MAX_SMEM_BOXES * 13];
+};
+
+__device__ __forceinline__ void stage_prims(const DevScene& sc, SmemPrims& sm, const float*& s_spheres, const float*& s_boxes)
+{
+    s_spheres = sc.spheres; s_boxes = sc.boxes;
+    if (sc.n_spheres <= GPT_MAX_SMEM_SPHERES) {
+        for (int i = threadIdx.x; i < sc.n_spheres * 11; i += blockDim.x) sm.spheres[i] = sc.spheres[i];
+        s_spheres = sm.spheres;
+    }
+    if (sc.n_boxes <= GPT_MAX_SMEM_BOXES) {
+        for (int i = threadIdx.x; i < sc.n_boxes * 13; i += blockDim.x) sm.boxes[i] = sc.boxes[i];
+        s_boxes = sm.boxes;
+    }
+    __syncthreads();
+}
+
+// counters layout (unsigned int): [0 .. depth]        n_q[b]   = paths alive at the start of bounce b
+//                                 [depth+1 .. 2depth+1] fetch[b] = extend's work-fetch cursor of bounce b
+__global__ void __launch_bounds__(256)
+k_wf_generate(const RenderParams p, const unsigned long long sample, const int n_pix,
+              float4* __restrict__ ray_o, float4* __restrict__ ray_d, float4* __restrict__ mask, float4* __restrict__ accu,
+              unsigned int* __restrict__ counters, unsigned long long* __restrict__ stats)
+{
+    for (int pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < n_pix; pixel += gridDim.x * blockDim.x) {
+        PathState ps;
+        start_path(p, pixel % p.width, pixel / p.width, (uint32_t)pixel, sample, ps);
+        ray_o[pixel] = make_float4(ps.o.x, ps.o.y, ps.o.z, 0.0f);
+        ray_d[pixel] = make_float4(ps.d.x, ps.d.y, ps.d.z, 0.0f);
+        mask[pixel] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        accu[pixel] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { counters[0] = (unsigned)n_pix; atomicAdd(&stats[1], (unsigned long long)n_pix); }
+}
+
+// Persistent traversal kernel.  Each trip the whole warp either re-arms its idle lanes from the queue, tests
+// one triangle per lane, or visits one inner node per lane -- chosen by vote, so the three code paths are
+// never serialised against each other inside a warp.
+__global__ void __launch_bounds__(WF_THREADS, 8)
+k_wf_extend(const DevScene sc, const int cull, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
+            unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
+            int2* __restrict__ hit, const int refill_min, const int tri_min)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned n = *n_ptr;
+    const bool do_cull = cull != 0;
+    int stack[GPT_STACK_SIZE];
+    TravState ts;
+    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+    uint32_t pid = 0;
+    bool active = false;        // lane holds a ray that is still traversing
+    bool exhausted = false;     // the queue has no more rays for this warp (warp-uniform)
+    ts.node = GPT_SENTINEL; ts.leaf = 0; ts.sp = 0; ts.t = GPT_F32_MAX; ts.tri = -1; ts.tri_cur = 0;
+
+    while (true) {
+        const unsigned m_idle = __ballot_sync(GPT_FULL_MASK, !active);
+        if (m_idle != 0u && !exhausted && (__popc(m_idle) >= refill_min || m_idle == GPT_FULL_MASK)) {
+            // ---- re-arm idle lanes: one atomic per warp ----
+            unsigned base = 0;
+            const int leader = __ffs(m_idle) - 1;
+            if ((int)lane == leader) base = atomicAdd(fetch, (unsigned)__popc(m_idle));
+            base = __shfl_sync(GPT_FULL_MASK, base, leader);
+            if (base + (unsigned)__popc(m_idle) >= n) exhausted = true;      // uniform: this grab reached the end
+            if (!active) {
+                const unsigned j = base + (unsigned)__popc(m_idle & lt_mask);
+                if (j < n) {
+                    pid = queue ? queue[j] : j;
+                    const float4 ro = ray_o[pid], rd = ray_d[pid];
+                    o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
+                    trav_init(ts, stack, o, d, true);
+                    active = true;
+                }
+            }
+            continue;
+        }
+        const unsigned m_node = __ballot_sync(GPT_FULL_MASK, active && trav_wants_node(ts));
+        const unsigned m_tri = __ballot_sync(GPT_FULL_MASK, active && trav_wants_tri(ts));
+        if (m_tri != 0u && (__popc(m_tri) >= tri_min || m_node == 0u)) {
+            if (active && trav_wants_tri(ts)) tri_step(sc.tris, ts, stack, o, d, do_cull);
+        } else if (m_node != 0u) {
+            if (active && trav_wants_node(ts)) node_step(sc.nodes, ts, stack);
+        } else {
+            break;          // nothing traversing; the refill branch above did not fire => queue exhausted
+        }
+        if (active && trav_finished(ts)) {
+            hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
+            active = false;
+        }
+    }
+}
+
+// Alternative schedule of the same traversal (A/B kept for the ncu comparison in profiles/): the classic
+// persistent while-while loop.  All lanes meet at the top of the outer loop once per "descend to the next leaf +
+// test that leaf" round; idle lanes are re-armed there.  Tighter inner loops than the voted steps above, but
+// lanes wait for the slowest descent / largest leaf of the round.
+__global__ void __launch_bounds__(WF_THREADS, 8)
+k_wf_extend_ww(const DevScene sc, const int cull, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
+               unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
+               int2* __restrict__ hit, const int refill_min)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned n = *n_ptr;
+    const bool do_cull = cull != 0;
+    int stack[GPT_STACK_SIZE];
+    TravState ts;
+    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+    uint32_t pid = 0;
+    bool active = false, exhausted = false;
+    ts.node = GPT_SENTINEL; ts.leaf = 0; ts.sp = 0; ts.t = GPT_F32_MAX; ts.tri = -1; ts.tri_cur = 0;
+
+    while (true) {
+        const unsigned m_idle = __ballot_sync(GPT_FULL_MASK, !active);
+        if (m_idle != 0u && !exhausted && (__popc(m_idle) >= refill_min || m_idle == GPT_FULL_MASK)) {
+            unsigned base = 0;
+            const int leader = __ffs(m_idle) - 1;
+            if ((int)lane == leader) base = atomicAdd(fetch, (unsigned)__popc(m_idle));
+            base = __shfl_sync(GPT_FULL_MASK, base, leader);
+            if (base + (unsigned)__popc(m_idle) >= n) exhausted = true;
+            if (!active) {
+                const unsigned j = base + (unsigned)__popc(m_idle & lt_mask);
+                if (j < n) {
+                    pid = queue ? queue[j] : j;
+                    const float4 ro = ray_o[pid], rd = ray_d[pid];
+                    o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
+                    trav_init(ts, stack, o, d, true);
+                    active = true;
+                }
+            }
+        }
+        if (__ballot_sync(GPT_FULL_MASK, active) == 0u) break;      // nothing armed: queue exhausted
+        if (active) {
+            while (trav_wants_node(ts)) {
+                node_step(sc.nodes, ts, stack);
+                if (!__any_sync(__activemask(), ts.leaf >= 0)) break;
+            }
+            while (trav_wants_tri(ts)) {
+                tri_step(sc.tris, ts, stack, o, d, do_cull);
+                // a second leaf was postponed while this one waited: leave it for the next round (measured
+                // faster than draining it here: the round ends sooner for the rest of the warp)
+                if (ts.leaf < 0 && ts.tri_cur == ~ts.leaf) break;
+            }
+            if (trav_finished(ts)) {
+                hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
+                active = false;
+            }
+        }
+    }
+}
+
+// One thread per path alive at bounce `bounce`: the rest of the bounce-loop body (tracer.cu:98-296), the
+// per-pixel launch sum when the path ends (tracer.cu:305 / :141), and compaction of the survivors.
+__global__ void __launch_bounds__(256)
+k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sample, const uint32_t bounce,
+           const uint32_t* __restrict__ queue_in, unsigned int* __restrict__ counters,
+           uint32_t* __restrict__ queue_out, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
+           const int2* __restrict__ hit, float4* __restrict__ mask, float4* __restrict__ accu,
+           float4* __restrict__ lsum, unsigned long long* __restrict__ stats)
+{
+    __shared__ SmemPrims sm;
+    const float* s_spheres; const float* s_boxes;
+    stage_prims(sc, sm, s_spheres, s_boxes);
+    const unsigned n = counters[bounce];
+    unsigned int* n_out = counters + bounce + 1;
+    const unsigned lane = threadIdx.x & 31u;
+    const bool has_mesh = sc.n_nodes > 0;
+    const bool last_bounce = bounce + 1u >= p.depth;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(&stats[0], (unsigned long long)n);
+        if ((p.flags & RP_COUNT_BOUNCES) && bounce < 16) atomicAdd(&stats[2 + bounce], (unsigned long long)n);
+    }
+    // whole warps iterate together so the compaction ballot below is warp-uniform
+    const unsigned n_round = (n + 31u) & ~31u;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+        bool survive = false;
+        uint32_t pid = 0;
+        if (i < n) {
+            pid = queue_in ? queue_in[i] : i;
+            const float4 ro = ray_o[pid], rd = ray_d[pid];
+            const float4 mk = mask[pid], ac = accu[pid];
+            PathState ps;
+            ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
+            ps.mask = mk3(mk.x, mk.y, mk.z); ps.accu = mk3(ac.x, ac.y, ac.z);
+            float tri_t = GPT_F32_MAX; int tri = -1;
+            if (has_mesh) { const int2 h = hit[pid]; tri_t = __int_as_float(h.x); tri = h.y; }
+            const SceneHit h = finish_scene_hit(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
+            const bool cont = shade_bounce(sc, p, s_spheres, s_boxes, h, pid, sample, bounce, ps);
+            survive = cont && !last_bounce;
+            if (survive) {
+                ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, 0.0f);
+                ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, 0.0f);
+                mask[pid] = make_float4(ps.mask.x, ps.mask.y, ps.mask.z, 0.0f);
+                accu[pid] = make_float4(ps.accu.x, ps.accu.y, ps.accu.z, 0.0f);
+            } else {
+                // path over: one path per pixel per wave, waves are stream-ordered => plain read-modify-write,
+                // summed in increasing sample order exactly like the megakernel's register sum
+                float4 s = lsum[pid];
+                s.x += ps.accu.x; s.y += ps.accu.y; s.z += ps.accu.z;
+                lsum[pid] = s;
+            }
+        }
+        // ---- compaction: one atomic per warp ----
+        const unsigned m = __ballot_sync(GPT_FULL_MASK, survive);
+        if (m) {
+            unsigned base = 0;
+            const int leader = __ffs(m) - 1;
+            if ((int)lane == leader) base = atomicAdd(n_out, (unsigned)__popc(m));
+            base = __shfl_sync(GPT_FULL_MASK, base, leader);
+            if (survive) queue_out[base + (unsigned)__popc(m & ((1u << lane) - 1u))] = pid;
+        }
+    }
+}
+
+// depth == 0: every path returns accucolor = 0 (tracer.cu:72,305); nothing to add to lsum.
+// launch sums -> caller's buffer.  LEGACY: running mean + clamp + pack (tracer.cu:386-398).
+template <bool LEGACY>
+__global__ void __launch_bounds__(256)
+k_wf_accumulate(const float4* __restrict__ lsum, const int n_pix, const uint32_t sample_count, float4* __restrict__ accum_f4,
+                float* __restrict__ accum_v3, uint32_t* __restrict__ draw, const unsigned long long constant_pdf)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pix; i += gridDim.x * blockDim.x) {
+        const float4 s = lsum[i];
+        if (LEGACY) {
+            const float nm1 = (float)(constant_pdf - 1ull), inv = 1.0f / (float)constant_pdf;
+            float* a = accum_v3 + 3 * (size_t)i;
+            const float ax = fminf(fmaxf((a[0] * nm1 + s.x) * inv, 0.0f), 1.0f);
+            const float ay = fminf(fmaxf((a[1] * nm1 + s.y) * inv, 0.0f), 1.0f);
+            const float az = fminf(fmaxf((a[2] * nm1 + s.z) * inv, 0.0f), 1.0f);
+            a[0] = ax; a[1] = ay; a[2] = az;
+            if (draw) {
+                const unsigned char cx = (unsigned char)(int)(255.0f * ax), cy = (unsigned char)(int)(255.0f * ay), cz = (unsigned char)(int)(255.0f * az);
+                draw[i] = ((uint32_t)cz << 16) | ((uint32_t)cy << 8) | (uint32_t)cx;
+            }
+        } else {
+            float4 a = accum_f4[i];
+            a.x += s.x; a.y += s.y; a.z += s.z; a.w += (float)sample_count;
+            accum_f4[i] = a;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- launcher
+static int wf_knob(const char* name, int dflt)
+{
+    const char* e = getenv(name);
+    int v = e ? atoi(e) : dflt;
+    return v < 1 ? 1 : (v > 32 ? 32 : v);
+}
+
+size_t gptk_wave_counter_count(unsigned int depth) { return 2 * ((size_t)depth + 1); }
+
+cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,
+                                  float4* accum_f4, float* accum_v3, uint32_t* draw, unsigned long long constant_pdf,
+                                  unsigned long long sample_begin, uint32_t sample_count,
+                                  unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches)
+{
+    static int ext_grid = 0;
+    if (!ext_grid) {
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        ext_grid = sm_count * per_sm;
+    }
+    static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
+    static const bool use_ww = getenv("GPT_WF_VOTED") == nullptr;     // default: while-while extend
+    const int n_pix = p.width * p.height;
+    int grid = (n_pix + 255) / 256; if (grid > sm_count * 8) grid = sm_count * 8; if (grid < 1) grid = 1;
+    const bool legacy = accum_v3 != nullptr;
+    const bool has_mesh = sc.n_nodes > 0;
+    cudaError_t e;
+    if ((e = cudaMemsetAsync(wb.lsum, 0, sizeof(float4) * (size_t)n_pix, st)) != cudaSuccess) return e;
+    for (uint32_t s = 0; s < sample_count && p.depth > 0; ++s) {
+        const unsigned long long sample = sample_begin + s;
+        if ((e = cudaMemsetAsync(wb.counters, 0, sizeof(unsigned int) * gptk_wave_counter_count(p.depth), st)) != cudaSuccess) return e;
+        k_wf_generate<<<grid, 256, 0, st>>>(p, sample, n_pix, wb.ray_o, wb.ray_d, wb.mask, wb.accu, wb.counters, stats);
+        *launches += 1;
+        for (uint32_t b = 0; b < p.depth; ++b) {
+            const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
+            if (has_mesh) {
+                if (use_ww)
+                    k_wf_extend_ww<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
+                                                                    wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                else
+                    k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
+                                                                 wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);
+                *launches += 1;
+            }
+            k_wf_shade<<<grid, 256, 0, st>>>(sc, p, sample, b, q_in, wb.counters, wb.queue[(b + 1u) & 1u], wb.ray_o, wb.ray_d,
+                                             wb.hit, wb.mask, wb.accu, wb.lsum, stats);
+            *launches += 1;
+        }
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    if (legacy) k_wf_accumulate<true><<<grid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, nullptr, accum_v3, draw, constant_pdf);
+    else k_wf_accumulate<false><<<grid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, accum_f4, nullptr, nullptr, 1ull);
+    *launches += 1;
+    return cudaGetLastError();
+}

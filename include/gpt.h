@@ -96,7 +96,7 @@ typedef struct {
 enum {
     GPT_FLAG_NO_JITTER   = 1u << 0,  /* camera jitter off (hit-ID parity runs) */
     GPT_FLAG_METAL_FIXED = 1u << 1,  /* use the reflection vector w1 instead of the reference's int `w` */
-    GPT_FLAG_WAVEFRONT   = 1u << 2,  /* gpt_render uses the wavefront pipeline instead of the megakernel */
+    GPT_FLAG_MEGAKERNEL  = 1u << 2,  /* single persistent megakernel instead of the (default) wavefront pipeline */
     GPT_FLAG_COUNT_BOUNCES = 1u << 3 /* fill gpt_stats.rays_by_bounce (slower) */
 };
 

@@ -116,7 +116,7 @@ def test_primary_hits_exact(gpt, torch_cuda, ctxs, name, w, h, jitter):
     ctx, sc, sph = ctxs(name, flags=flags)
     info = gpt.default_kernel_info(w, h)
     if name == "sphere_mesh":
-        gpt.set_camera(info, (0.0, 0.0, 4.0), 0.0, 0.0)            # sphere.obj sits at the origin
+        gpt.set_camera(info, (0.0, 0.0, 30.0), 0.0, 0.0)           # sphere.obj: radius 9.35 at the origin
     geom_o, tri_o, prim_o, t_o, _ = scenes.oracle_primary(sc, sph, info, 99, 3, flags=0 if jitter else reflib.ORC_FLAG_NO_JITTER)
     n = w * h
     geom = torch.empty(n, dtype=torch.int32, device="cuda"); tri = torch.empty_like(geom); prim = torch.empty_like(geom)
@@ -385,3 +385,47 @@ def test_full_size_properties(gpt, torch_cuda, ctxs):
             s = (s + np.array(rgb[:], np.float32)).astype(np.float32)
         bad += int(not np.array_equal(s, a[py, px, :3]))
     assert bad <= 1, bad
+
+
+# ------------------------------------------------------------------ wavefront pipeline == megakernel == oracle
+@pytest.mark.parametrize("name,tri_mat,depth,w,h", [("bunny_cornell", 0, 8, 160, 90), ("bunny_cornell", 1, 5, 160, 90),
+                                                    ("bunny_cornell", 3, 6, 131, 67), ("cornell", 2, 1, 64, 36),
+                                                    ("sphere_mesh", 0, 4, 96, 54), (None, 0, 5, 96, 54)])
+def test_wavefront_pipeline_bit_identical(gpt, torch_cuda, ctxs, name, tri_mat, depth, w, h):
+    """Both schedules evaluate the same per-sample arithmetic: images must be IDENTICAL, and equal to the oracle."""
+    torch = torch_cuda
+    ctx_m, sc, sph = ctxs(name, flags=gpt.FLAG_MEGAKERNEL)
+    ctx_w, _, _ = ctxs(name)
+    info = small_info(gpt, w, h, depth=depth)
+    info.triCurrentMat = tri_mat
+    a = gpu_render(torch, ctx_m, info, 21, 1, 3)
+    ctx_w.reset_stats()
+    b = gpu_render(torch, ctx_w, info, 21, 1, 3)
+    st = ctx_w.stats()
+    np.testing.assert_array_equal(a, b)
+    assert st.paths == 3 * w * h and st.rays >= 3 * w * h
+    want = scenes.oracle_render(sc, sph, info, 21, 1, 3)
+    assert_radiance_close(b[..., :3], want[..., :3])
+    # depth 0 and an early-terminating scene (no spheres: misses end paths, queues shrink)
+    if name == "cornell":
+        empty = (gpt.Sphere * 0)()
+        ctx_e, _, _ = ctxs("cornell", spheres=empty)
+        info2 = small_info(gpt, 128, 72, depth=6)
+        got = gpu_render(torch, ctx_e, info2, 2, 0, 2)
+        want = scenes.oracle_render(sc, None, info2, 2, 0, 2)
+        assert_radiance_close(got[..., :3], want[..., :3])
+        info2.depth = 0
+        assert (gpu_render(torch, ctx_e, info2, 2, 0, 2)[..., :3] == 0).all()
+
+
+def test_both_pipelines_legacy_launch(gpt, torch_cuda):
+    torch = torch_cuda
+    sc = scenes.load_scene("bunny_cornell")
+    w, h = 160, 90
+    outs = []
+    for flags in (gpt.FLAG_MEGAKERNEL, 0):
+        bs = gpt.BasicScene(w, h, sc["nodes"], sc["tris"], sc["indices"], flags=flags)
+        acc, draw = bs.run(3)
+        outs.append((acc.cpu().numpy().copy(), draw.cpu().numpy().copy()))
+    np.testing.assert_array_equal(outs[0][0], outs[1][0])
+    np.testing.assert_array_equal(outs[0][1], outs[1][1])
