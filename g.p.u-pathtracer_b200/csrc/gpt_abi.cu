@@ -93,19 +93,26 @@ static void free_wave(gpt_ctx* c)
     w = WaveBuffers{}; c->wave_pixels = 0; c->wave_counters = 0;
 }
 
-// wavefront scratch: one entry per pixel (72 B + 2 queue slots), grown on demand
-static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth)
+// wavefront scratch: per-path state for one wave (80 B/path) + one launch sum per pixel.  A wave holds as many
+// samples of the frame as fit GPT_WAVE_MAX_PATHS (5 GB of the 180 GB HBM at the cap); grown on demand.
+#define GPT_WAVE_MAX_PATHS ((size_t)64 << 20)
+static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sample_count)
 {
     const size_t nc = gptk_wave_counter_count(depth);
-    if (c->wave_pixels >= n_pix && c->wave_counters >= nc) return GPT_OK;
+    size_t want = n_pix * (size_t)(sample_count ? sample_count : 1);
+    if (want > GPT_WAVE_MAX_PATHS) want = n_pix > GPT_WAVE_MAX_PATHS ? GPT_WAVE_MAX_PATHS : (GPT_WAVE_MAX_PATHS / n_pix) * n_pix;
+    if (c->wave_pixels >= n_pix && c->wave_counters >= nc && c->wave.capacity >= want) return GPT_OK;
     CU(c, cudaDeviceSynchronize());
+    if (want < c->wave.capacity) want = c->wave.capacity;
     free_wave(c);
     WaveBuffers& w = c->wave;
-    CU(c, cudaMalloc(&w.ray_o, n_pix * sizeof(float4))); CU(c, cudaMalloc(&w.ray_d, n_pix * sizeof(float4)));
-    CU(c, cudaMalloc(&w.mask, n_pix * sizeof(float4)));  CU(c, cudaMalloc(&w.accu, n_pix * sizeof(float4)));
-    CU(c, cudaMalloc(&w.lsum, n_pix * sizeof(float4)));  CU(c, cudaMalloc(&w.hit, n_pix * sizeof(int2)));
-    CU(c, cudaMalloc(&w.queue[0], n_pix * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], n_pix * sizeof(uint32_t)));
+    CU(c, cudaMalloc(&w.ray_o, want * sizeof(float4))); CU(c, cudaMalloc(&w.ray_d, want * sizeof(float4)));
+    CU(c, cudaMalloc(&w.mask, want * sizeof(float4)));  CU(c, cudaMalloc(&w.accu, want * sizeof(float4)));
+    CU(c, cudaMalloc(&w.hit, want * sizeof(int2)));
+    CU(c, cudaMalloc(&w.queue[0], want * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], want * sizeof(uint32_t)));
+    CU(c, cudaMalloc(&w.lsum, n_pix * sizeof(float4)));
     CU(c, cudaMalloc(&w.counters, nc * sizeof(unsigned int)));
+    w.capacity = want;
     c->wave_pixels = n_pix; c->wave_counters = nc;
     return GPT_OK;
 }
@@ -265,7 +272,7 @@ int gpt_launch(gpt_ctx* c, const gpt_kernel_info* info, gpt_stream stream)
     rc = launch_scene(c, info, &sc); if (rc) return rc;
     cudaError_t e;
     if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
-        rc = ensure_wave(c, (size_t)p.width * p.height, p.depth); if (rc) return rc;
+        rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, 1u); if (rc) return rc;
         e = gptk_render_wavefront(sc, p, c->wave, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u,
                                   c->stats, c->sm_count, (cudaStream_t)stream, &c->launches);
     } else {
@@ -288,7 +295,7 @@ int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_
     rc = launch_scene(c, info, &sc); if (rc) return rc;
     cudaError_t e;
     if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
-        rc = ensure_wave(c, (size_t)p.width * p.height, p.depth); if (rc) return rc;
+        rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, sample_count); if (rc) return rc;
         e = gptk_render_wavefront(sc, p, c->wave, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count,
                                   c->stats, c->sm_count, (cudaStream_t)stream, &c->launches);
     } else {

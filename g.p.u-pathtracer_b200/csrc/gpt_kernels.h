@@ -22,12 +22,13 @@ struct RepackResult { float4* nodes; float4* tris; int n_nodes; int n_tris; int 
 cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float4* ref_tris, size_t n_tri_vec4,
                         const int* ref_indices, size_t n_indices, RepackResult* out, cudaStream_t st);
 
-// wavefront pipeline (gpt_wavefront.cu).  All buffers hold one entry per pixel of the frame.
+// wavefront pipeline (gpt_wavefront.cu).  Per-path arrays hold `capacity` entries, lsum one per pixel.
 struct WaveBuffers {
     float4 *ray_o, *ray_d, *mask, *accu, *lsum;
     int2* hit;
     uint32_t* queue[2];
     unsigned int* counters;     // gptk_wave_counter_count(depth) entries
+    size_t capacity;            // paths the per-path arrays hold (lsum: one per pixel of the frame)
 };
 size_t gptk_wave_counter_count(unsigned int depth);
 cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,

@@ -156,13 +156,13 @@ __device__ __forceinline__ float sphere_test(const float* s, const f3 o, const f
 {
     const f3 op = sub3(mk3(s[0], s[1], s[2]), o);
     const float b = dot3(op, d);
-    float disc = fmaf(b, b, -dot3(op, op)) + s[3] * s[3];
-    if (disc < 0.0f) return 0.0f;
-    disc = sqrtf(disc);
-    float t = b - disc;
-    if (t > 0.01f) return t;
-    t = b + disc;
-    return t > 0.01f ? t : 0.0f;
+    const float disc = fmaf(b, b, -dot3(op, op)) + s[3] * s[3];
+    // branch-free: the warp pays for the square root whenever any lane needs it, so every lane may as well
+    // take it; the selected values are the same as in the early-out form
+    const float sq = sqrtf(fmaxf(disc, 0.0f));
+    const float t0 = b - sq, t1 = b + sq;
+    const float t = t0 > 0.01f ? t0 : (t1 > 0.01f ? t1 : 0.0f);
+    return disc < 0.0f ? 0.0f : t;
 }
 
 // Box spec, cudaUtils.h:43-58; bx = 13 floats (min, max, emi, col, mat)

@@ -42,19 +42,24 @@ __device__ __forceinline__ void stage_prims(const DevScene& sc, SmemPrims& sm, c
 // counters layout (unsigned int): [0 .. depth]        n_q[b]   = paths alive at the start of bounce b
 //                                 [depth+1 .. 2depth+1] fetch[b] = extend's work-fetch cursor of bounce b
 __global__ void __launch_bounds__(256)
-k_wf_generate(const RenderParams p, const unsigned long long sample, const int n_pix,
+k_wf_generate(const RenderParams p, const unsigned long long sample0, const int n_samples, const int pix0, const int n_wave,
               float4* __restrict__ ray_o, float4* __restrict__ ray_d, float4* __restrict__ mask, float4* __restrict__ accu,
               unsigned int* __restrict__ counters, unsigned long long* __restrict__ stats)
 {
-    for (int pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < n_pix; pixel += gridDim.x * blockDim.x) {
+    // path id = s_local * n_wave + i  <->  (global sample sample0 + s_local, pixel pix0 + i): sample-major, so the
+    // lanes of a warp hold neighbouring pixels of the same sample
+    const int n_paths = n_samples * n_wave;
+    for (int pid = blockIdx.x * blockDim.x + threadIdx.x; pid < n_paths; pid += gridDim.x * blockDim.x) {
+        const int s_local = pid / n_wave;
+        const int pixel = pix0 + (pid - s_local * n_wave);
         PathState ps;
-        start_path(p, pixel % p.width, pixel / p.width, (uint32_t)pixel, sample, ps);
-        ray_o[pixel] = make_float4(ps.o.x, ps.o.y, ps.o.z, 0.0f);
-        ray_d[pixel] = make_float4(ps.d.x, ps.d.y, ps.d.z, 0.0f);
-        mask[pixel] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-        accu[pixel] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        start_path(p, pixel % p.width, pixel / p.width, (uint32_t)pixel, sample0 + (unsigned long long)s_local, ps);
+        ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, 0.0f);
+        ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, 0.0f);
+        mask[pid] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        accu[pid] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) { counters[0] = (unsigned)n_pix; atomicAdd(&stats[1], (unsigned long long)n_pix); }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { counters[0] = (unsigned)n_paths; atomicAdd(&stats[1], (unsigned long long)n_paths); }
 }
 
 // Persistent traversal kernel.  Each trip the whole warp either re-arms its idle lanes from the queue, tests
@@ -176,11 +181,11 @@ k_wf_extend_ww(const DevScene sc, const int cull, const uint32_t* __restrict__ q
 // One thread per path alive at bounce `bounce`: the rest of the bounce-loop body (tracer.cu:98-296), the
 // per-pixel launch sum when the path ends (tracer.cu:305 / :141), and compaction of the survivors.
 __global__ void __launch_bounds__(256)
-k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sample, const uint32_t bounce,
+k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sample0, const uint32_t bounce, const uint32_t pix0, const uint32_t n_wave,
            const uint32_t* __restrict__ queue_in, unsigned int* __restrict__ counters,
            uint32_t* __restrict__ queue_out, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
            const int2* __restrict__ hit, float4* __restrict__ mask, float4* __restrict__ accu,
-           float4* __restrict__ lsum, unsigned long long* __restrict__ stats)
+           unsigned long long* __restrict__ stats)
 {
     __shared__ SmemPrims sm;
     const float* s_spheres; const float* s_boxes;
@@ -209,7 +214,8 @@ k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sam
             float tri_t = GPT_F32_MAX; int tri = -1;
             if (has_mesh) { const int2 h = hit[pid]; tri_t = __int_as_float(h.x); tri = h.y; }
             const SceneHit h = finish_scene_hit(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
-            const bool cont = shade_bounce(sc, p, s_spheres, s_boxes, h, pid, sample, bounce, ps);
+            const uint32_t s_local = pid / n_wave;
+            const bool cont = shade_bounce(sc, p, s_spheres, s_boxes, h, pix0 + (pid - s_local * n_wave), sample0 + s_local, bounce, ps);
             survive = cont && !last_bounce;
             if (survive) {
                 ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, 0.0f);
@@ -217,11 +223,9 @@ k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sam
                 mask[pid] = make_float4(ps.mask.x, ps.mask.y, ps.mask.z, 0.0f);
                 accu[pid] = make_float4(ps.accu.x, ps.accu.y, ps.accu.z, 0.0f);
             } else {
-                // path over: one path per pixel per wave, waves are stream-ordered => plain read-modify-write,
-                // summed in increasing sample order exactly like the megakernel's register sum
-                float4 s = lsum[pid];
-                s.x += ps.accu.x; s.y += ps.accu.y; s.z += ps.accu.z;
-                lsum[pid] = s;
+                // path over: its radiance (tracer.cu:305, or bkColor on a miss :141) stays in accu[pid] until
+                // k_wf_collect adds the wave's samples to the per-pixel launch sum in sample order
+                accu[pid] = make_float4(ps.accu.x, ps.accu.y, ps.accu.z, 0.0f);
             }
         }
         // ---- compaction: one atomic per warp ----
@@ -233,6 +237,21 @@ k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sam
             base = __shfl_sync(GPT_FULL_MASK, base, leader);
             if (survive) queue_out[base + (unsigned)__popc(m & ((1u << lane) - 1u))] = pid;
         }
+    }
+}
+
+// Adds the finished paths of a wave to the per-pixel launch sums, samples in increasing global index: the same
+// left-to-right float sum the megakernel keeps in a register, so both pipelines round identically.
+__global__ void __launch_bounds__(256)
+k_wf_collect(const float4* __restrict__ accu, const int n_samples, const int pix0, const int n_wave, float4* __restrict__ lsum)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_wave; i += gridDim.x * blockDim.x) {
+        float4 s = lsum[pix0 + i];
+        for (int k = 0; k < n_samples; ++k) {
+            const float4 a = accu[(size_t)k * n_wave + i];
+            s.x += a.x; s.y += a.y; s.z += a.z;
+        }
+        lsum[pix0 + i] = s;
     }
 }
 
@@ -288,33 +307,51 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
     static const bool use_ww = getenv("GPT_WF_VOTED") == nullptr;     // default: while-while extend
     const int n_pix = p.width * p.height;
-    int grid = (n_pix + 255) / 256; if (grid > sm_count * 8) grid = sm_count * 8; if (grid < 1) grid = 1;
+    // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays
+    // hold (88 B/path).  Big waves matter: every launch has a fixed cost (launch gap + the tail where the
+    // persistent extend kernel drains), measured at ~19 us, and a 1080p x 1 spp wave needs 17 launches.
+    static const size_t wave_cap_env = []{ const char* e = getenv("GPT_WF_WAVE_PATHS"); long long v = e ? atoll(e) : 0; return (size_t)(v < 0 ? 0 : v); }();
+    size_t cap = wb.capacity;
+    if (wave_cap_env && wave_cap_env < cap) cap = wave_cap_env < 1024 ? 1024 : wave_cap_env;
+    const int wave_pix = (int)((size_t)n_pix < cap ? (size_t)n_pix : cap);
+    const uint32_t wave_spp_max = (uint32_t)(cap / (size_t)wave_pix);      // >= 1
+    int agrid = (n_pix + 255) / 256; if (agrid > sm_count * 8) agrid = sm_count * 8; if (agrid < 1) agrid = 1;
     const bool legacy = accum_v3 != nullptr;
     const bool has_mesh = sc.n_nodes > 0;
     cudaError_t e;
     if ((e = cudaMemsetAsync(wb.lsum, 0, sizeof(float4) * (size_t)n_pix, st)) != cudaSuccess) return e;
-    for (uint32_t s = 0; s < sample_count && p.depth > 0; ++s) {
-        const unsigned long long sample = sample_begin + s;
-        if ((e = cudaMemsetAsync(wb.counters, 0, sizeof(unsigned int) * gptk_wave_counter_count(p.depth), st)) != cudaSuccess) return e;
-        k_wf_generate<<<grid, 256, 0, st>>>(p, sample, n_pix, wb.ray_o, wb.ray_d, wb.mask, wb.accu, wb.counters, stats);
-        *launches += 1;
-        for (uint32_t b = 0; b < p.depth; ++b) {
-            const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
-            if (has_mesh) {
-                if (use_ww)
-                    k_wf_extend_ww<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
-                                                                    wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                else
-                    k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
-                                                                 wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);
+    for (int pix0 = 0; pix0 < n_pix && p.depth > 0; pix0 += wave_pix) {
+        const int n_wave = n_pix - pix0 < wave_pix ? n_pix - pix0 : wave_pix;
+        for (uint32_t s0 = 0; s0 < sample_count; s0 += wave_spp_max) {
+            const uint32_t ns = sample_count - s0 < wave_spp_max ? sample_count - s0 : wave_spp_max;
+            const size_t n_paths = (size_t)ns * n_wave;
+            int grid = (int)((n_paths + 255) / 256); if (grid > sm_count * 8) grid = sm_count * 8; if (grid < 1) grid = 1;
+            int cgrid = (n_wave + 255) / 256; if (cgrid > sm_count * 8) cgrid = sm_count * 8; if (cgrid < 1) cgrid = 1;
+            const unsigned long long sample0 = sample_begin + s0;
+            if ((e = cudaMemsetAsync(wb.counters, 0, sizeof(unsigned int) * gptk_wave_counter_count(p.depth), st)) != cudaSuccess) return e;
+            k_wf_generate<<<grid, 256, 0, st>>>(p, sample0, (int)ns, pix0, n_wave, wb.ray_o, wb.ray_d, wb.mask, wb.accu, wb.counters, stats);
+            *launches += 1;
+            for (uint32_t b = 0; b < p.depth; ++b) {
+                const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
+                if (has_mesh) {
+                    if (use_ww)
+                        k_wf_extend_ww<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
+                                                                        wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                    else
+                        k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
+                                                                     wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);
+                    *launches += 1;
+                }
+                k_wf_shade<<<grid, 256, 0, st>>>(sc, p, sample0, b, (uint32_t)pix0, (uint32_t)n_wave, q_in, wb.counters, wb.queue[(b + 1u) & 1u],
+                                                 wb.ray_o, wb.ray_d, wb.hit, wb.mask, wb.accu, stats);
                 *launches += 1;
             }
-            k_wf_shade<<<grid, 256, 0, st>>>(sc, p, sample, b, q_in, wb.counters, wb.queue[(b + 1u) & 1u], wb.ray_o, wb.ray_d,
-                                             wb.hit, wb.mask, wb.accu, wb.lsum, stats);
+            k_wf_collect<<<cgrid, 256, 0, st>>>(wb.accu, (int)ns, pix0, n_wave, wb.lsum);
             *launches += 1;
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
+    const int grid = agrid;
     if (legacy) k_wf_accumulate<true><<<grid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, nullptr, accum_v3, draw, constant_pdf);
     else k_wf_accumulate<false><<<grid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, accum_f4, nullptr, nullptr, 1ull);
     *launches += 1;

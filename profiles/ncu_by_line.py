@@ -32,7 +32,8 @@ agg = defaultdict(lambda: [0, 0, 0, 0])
 tot = [0, 0, 0]
 base = None
 for r in rows[2:]:
-    if len(r) < len(hdr):
+    if len(r) < len(hdr) or r[ix["Address"]] == "Address":     # section header of a further launch in the report
+        base = None
         continue
     a = int(r[ix["Address"]], 16) if r[ix["Address"]].startswith("0x") else int(r[ix["Address"]])
     if base is None:
