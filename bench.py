@@ -38,9 +38,22 @@ ACCUM_BYTES_PER_PIXEL_PER_LAUNCH = 32
 
 
 def load_algo_bytes():
+    """-> (bytes per ray of the whole bounce-loop iteration, bytes per ray of the BVH traversal alone)"""
     p = os.path.join(ROOT, "profiles", "r01_algorithmic_bytes.json")
     with open(p) as fh:
-        return json.load(fh)[WORKLOAD]["bytes_per_ray"]
+        a = json.load(fh)[WORKLOAD]
+    trav = 64 * a["inner_nodes_per_ray"] + 48 * a["tri_tests_per_ray"] + 16 * a["leaf_terminators_per_ray"] + 4 * a["tri_hits_per_ray"]
+    return a["bytes_per_ray"], trav
+
+
+def load_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_wf_extend_ww launch from the committed `ncu --set full`
+    capture of this same command (profiles/r01_traffic.json), or None."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as fh:
+        return json.load(fh).get("k_wf_extend_ww", {}).get("dram_bytes_per_launch")
 
 
 def load_scene_arrays():
@@ -216,6 +229,41 @@ def cpu_baseline(gpt, sc, args):
     return out, port
 
 
+def reference_gpu_kernel(gpt, torch, sc, sph, args, rays_per_step):
+    """The reference's OWN CUDA kernel (oracle/_ref/reftrace.cubin = GpuPathTracer/tracer.cu compiled in place) on
+    this GPU, same scene / camera / depth, 16x16 blocks, args.spp one-sample frames per step exactly as
+    BasicScene::run drives it (BasicScene.cpp:395-404).  Baseline leg only: nothing of it is on the product path."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from support import refgpu
+    if not refgpu.available():
+        return None
+    k = refgpu.RefGpuKernel(torch.cuda.current_device())
+    info = bench_info(gpt, args)
+    rs = refgpu.RefScene(torch, info, sc, sph, torch.cuda.current_device())
+
+    def step(i):
+        for f in range(args.spp):
+            info.hash = gpt.hash64(i * args.spp + f)
+            info.constantPdf = f + 1
+            k.launch(info)
+    for i in range(2):
+        step(i)
+    torch.cuda.synchronize()
+    n = 3
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(n):
+        step(2 + i)
+    t1.record()
+    torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / n
+    k.close()
+    return {"ms_per_frame_16spp": ms, "value": rays_per_step / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "kind": "reference",
+            "what": "reference __global__ trace (tracer.cu:343-400) built for sm_100a from /root/reference (PTX-level vote.sync fix), "
+                    "%d launches of 1 spp per step, 16x16 blocks; rays per step taken from our counter (same algorithm, same "
+                    "expected ray count; the reference kernel does not count rays)" % args.spp}
+
+
 def run_reference_arm(args):
     """--impl reference: the reference's own CPU implementation on this box's host cores, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
@@ -286,7 +334,7 @@ def run_ours(args):
     sc = load_scene_arrays()
     sph = bench_spheres(gpt)
     info = bench_info(gpt, args)
-    flags = gpt.FLAG_MEGAKERNEL if args.pipeline == "mega" else 0
+    flags = (gpt.FLAG_MEGAKERNEL if args.pipeline == "mega" else 0) | gpt.FLAG_TIME_KERNELS
     ctx = gpt.Context(local, flags)
     ctx.upload_scene(sc["nodes"], sc["tris"], sc["indices"], sph)
     frame = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
@@ -343,6 +391,7 @@ def run_ours(args):
         sampler.start()
     ms = timed(args.steps, args.warmup, False)
     st = ctx.stats()
+    ktimes = ctx.kernel_times()
     kernel_ms = [a.elapsed_time(b) for a, b in k_events]
     rays = torch.tensor([float(st.rays)], dtype=torch.float64, device=dev)
     if dist is not None:
@@ -382,11 +431,18 @@ def run_ours(args):
             peaks = json.load(open(pk))
             hbm = float(peaks.get("hbm_gbs", hbm))
             peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
-        bpr = load_algo_bytes()
-        k_avg_ms = float(np.mean(kernel_ms))
-        rays_per_launch = float(st.rays) / max(1, len(kernel_ms))
-        algo_bytes = bpr * rays_per_launch + ACCUM_BYTES_PER_PIXEL_PER_LAUNCH * W * H
-        achieved = algo_bytes / (k_avg_ms * 1e-3) / 1e9
+        bpr, bpr_trav = load_algo_bytes()
+        pass_avg_ms = float(np.mean(kernel_ms))
+        pass_bytes = bpr * float(st.rays) / max(1, len(kernel_ms)) + ACCUM_BYTES_PER_PIXEL_PER_LAUNCH * W * H
+        pass_achieved = pass_bytes / (pass_avg_ms * 1e-3) / 1e9
+        if args.pipeline == "mega" or ktimes["extend"][1] == 0:
+            kname, k_avg_ms, rays_per_launch, k_bytes_per_ray, k_total_ms = "k_render_mega<false>", pass_avg_ms, float(st.rays) / max(1, len(kernel_ms)), bpr, pass_avg_ms * len(kernel_ms)
+        else:
+            # dominant kernel: the BVH traversal.  Its algorithmic bytes are the traversal terms of SURVEY 8-d's formula
+            # (nodes, triangles, terminators, index remap); the 44 B x spheres term belongs to k_wf_shade.
+            k_total_ms, n_ext = ktimes["extend"]
+            kname, k_avg_ms, rays_per_launch, k_bytes_per_ray = "k_wf_extend_ww", k_total_ms / n_ext, float(st.rays) / n_ext, bpr_trav
+        achieved = k_bytes_per_ray * rays_per_launch / (k_avg_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": total_rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -401,10 +457,16 @@ def run_ours(args):
                     "what": "gpt_render_frame_host: kernelInfo by value in, RGBA8 frame to pinned host memory out, sync per step"
                             if world == 1 else "render + NCCL reduce + resolve + RGBA8 D2H to pinned host on rank 0, sync per step"},
             "gpu_launches": launches,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
-                         "kernel": "k_render_mega<false>" if args.pipeline == "mega" else "k_wf_extend_ww (+ k_wf_shade, k_wf_generate, k_wf_accumulate: whole gpt_render pass timed)", "kernel_ms_avg": k_avg_ms, "kernel_share_of_step": k_avg_ms * len(kernel_ms) / ms,
-                         "algorithmic_bytes_per_ray": bpr, "rays_per_launch": rays_per_launch, "peak_source": peak_src,
-                         "note": "scene is L1/L2 resident, so the HBM fraction is low by construction; see profiles/ for L1/L2/issue-slot counters"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": load_traffic(),
+                         "kernel": kname, "kernel_ms_avg": k_avg_ms, "kernel_share_of_step": k_total_ms / ms,
+                         "algorithmic_bytes_per_ray": k_bytes_per_ray, "rays_per_launch": rays_per_launch,
+                         "algorithmic_bytes_per_launch": k_bytes_per_ray * rays_per_launch, "peak_source": peak_src,
+                         "whole_pass": {"achieved": pass_achieved, "frac": pass_achieved / hbm, "bytes_per_ray": bpr, "ms_avg": pass_avg_ms,
+                                        "what": "all kernels of one gpt_render pass (generate, extend, shade, collect, accumulate)"},
+                         "kernel_class_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]},
+                         "kernel_class_launches_per_step": {k: v[1] / args.steps for k, v in ktimes.items() if v[1]},
+                         "note": "scene (0.4 MB packed) is L1/L2 resident: algorithmic bytes are served by cache, so the fraction can exceed 1 "
+                                 "of HBM peak; the binding resource is issue slots x SIMT efficiency (profiles/)"},
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_cpu_baseline:
@@ -412,6 +474,12 @@ def run_ours(args):
             line["cpu_baseline"] = base
             if port is not None:
                 line["cpu_oracle_port"] = port
+            try:
+                rg = reference_gpu_kernel(gpt, torch, sc, sph, args, total_rays / args.steps)
+            except Exception as ex:      # baseline leg must never take the product line down
+                rg = {"unavailable": repr(ex)}
+            if rg is not None:
+                line["reference_gpu_kernel"] = rg
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()

@@ -25,6 +25,8 @@ FLAG_NO_JITTER = 1 << 0
 FLAG_METAL_FIXED = 1 << 1
 FLAG_MEGAKERNEL = 1 << 2
 FLAG_COUNT_BOUNCES = 1 << 3
+FLAG_TIME_KERNELS = 1 << 4
+K_GENERATE, K_EXTEND, K_SHADE, K_COLLECT, K_ACCUMULATE, K_RESOLVE, K_OTHER = range(7)
 
 
 class GptError(RuntimeError):
@@ -70,13 +72,17 @@ class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("rays_by_bounce", C.c_uint64 * 16), ("paths", C.c_uint64), ("kernel_launches", C.c_uint64)]
 
 
+class KernelTimes(C.Structure):
+    _fields_ = [("ms", C.c_double * 8), ("launches", C.c_uint64 * 8)]
+
+
 assert C.sizeof(Sphere) == 44 and C.sizeof(Box) == 52 and C.sizeof(CamInfo) == 84
 assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 
 # every symbol include/gpt.h declares (tests check the library exports each one)
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
            "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
-           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats",
+           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times",
            "gpt_hash64", "gpt_default_spheres", "gpt_default_kernel_info", "gpt_set_camera"]
 
 _lib = None
@@ -109,6 +115,7 @@ def load_library():
     L.gpt_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gpt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
     L.gpt_reset_stats.argtypes = [C.c_void_p]
+    L.gpt_get_kernel_times.argtypes = [C.c_void_p, C.POINTER(KernelTimes)]
     L.gpt_hash64.argtypes = [C.c_uint64]
     L.gpt_hash64.restype = C.c_uint64
     L.gpt_default_spheres.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -258,6 +265,13 @@ class Context:
         s = Stats()
         self._ck(self._L.gpt_get_stats(self._h, C.byref(s)), "gpt_get_stats")
         return s
+
+    def kernel_times(self):
+        """{class name: (ms, launches)} since the last reset_stats (needs FLAG_TIME_KERNELS)."""
+        t = KernelTimes()
+        self._ck(self._L.gpt_get_kernel_times(self._h, C.byref(t)), "gpt_get_kernel_times")
+        names = ["generate", "extend", "shade", "collect", "accumulate", "resolve", "other"]
+        return {n: (t.ms[i], int(t.launches[i])) for i, n in enumerate(names)}
 
     def reset_stats(self):
         self._ck(self._L.gpt_reset_stats(self._h), "gpt_reset_stats")

@@ -29,6 +29,7 @@ struct gpt_ctx {
     float4* frame_accum = nullptr; uint32_t* frame_rgba = nullptr; size_t frame_pixels = 0;
     WaveBuffers wave = {}; size_t wave_pixels = 0; size_t wave_counters = 0;   // wavefront scratch
     unsigned long long launches = 0;
+    KernelTimer timer; double kt_ms[KT_CLASSES] = {}; unsigned long long kt_n[KT_CLASSES] = {};
     std::string err;
 };
 
@@ -125,6 +126,7 @@ void gpt_destroy(gpt_ctx* c)
     free_scene(c);
     cudaFree(c->work_counter); cudaFree(c->stats); cudaFree(c->frame_accum); cudaFree(c->frame_rgba);
     free_wave(c);
+    c->timer.release();
     delete c;
 }
 
@@ -274,7 +276,8 @@ int gpt_launch(gpt_ctx* c, const gpt_kernel_info* info, gpt_stream stream)
     if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
         rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, 1u); if (rc) return rc;
         e = gptk_render_wavefront(sc, p, c->wave, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u,
-                                  c->stats, c->sm_count, (cudaStream_t)stream, &c->launches);
+                                  c->stats, c->sm_count, (cudaStream_t)stream, &c->launches,
+                                  (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);
     } else {
         e = gptk_render_legacy(sc, p, info->accumBuffer, info->dev_drawRes, info->constantPdf,
                                c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
@@ -297,7 +300,8 @@ int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_
     if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
         rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, sample_count); if (rc) return rc;
         e = gptk_render_wavefront(sc, p, c->wave, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count,
-                                  c->stats, c->sm_count, (cudaStream_t)stream, &c->launches);
+                                  c->stats, c->sm_count, (cudaStream_t)stream, &c->launches,
+                                  (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);
     } else {
         e = gptk_render_mega(sc, p, reinterpret_cast<float4*>(accum_f4), sample_begin, sample_count,
                              c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
@@ -311,7 +315,10 @@ int gpt_resolve(gpt_ctx* c, const float* accum_f4, int width, int height, uint32
 {
     if (!c || !accum_f4 || width <= 0 || height <= 0) return GPT_ERR_INVALID;
     CU(c, cudaSetDevice(c->device));
+    KernelTimer* kt = (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr;
+    if (kt) kt->tick(KT_RESOLVE, (cudaStream_t)stream);
     cudaError_t e = gptk_resolve(reinterpret_cast<const float4*>(accum_f4), width * height, out_rgba8, out_rgb_f32, c->sm_count, (cudaStream_t)stream);
+    if (kt) kt->tick(KT_END, (cudaStream_t)stream);
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "resolve launch", e);
     c->launches += 1;
     return GPT_OK;
@@ -379,6 +386,16 @@ int gpt_get_stats(gpt_ctx* c, gpt_stats* out)
     return GPT_OK;
 }
 
+int gpt_get_kernel_times(gpt_ctx* c, gpt_kernel_times* out)
+{
+    if (!c || !out) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());
+    c->timer.collect(c->kt_ms, c->kt_n);
+    for (int i = 0; i < 8; ++i) { out->ms[i] = c->kt_ms[i]; out->launches[i] = c->kt_n[i]; }
+    return GPT_OK;
+}
+
 int gpt_reset_stats(gpt_ctx* c)
 {
     if (!c) return GPT_ERR_INVALID;
@@ -386,6 +403,8 @@ int gpt_reset_stats(gpt_ctx* c)
     CU(c, cudaDeviceSynchronize());
     CU(c, cudaMemset(c->stats, 0, 32 * sizeof(unsigned long long)));
     c->launches = 0;
+    c->timer.used = 0;
+    for (int i = 0; i < KT_CLASSES; ++i) { c->kt_ms[i] = 0.0; c->kt_n[i] = 0; }
     return GPT_OK;
 }
 

@@ -3,6 +3,39 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "gpt_scene.cuh"
+#include <vector>
+
+// Optional per-kernel-class device timing (GPT_FLAG_TIME_KERNELS): one CUDA event is recorded on the launching
+// stream in front of every launch (and one after the last); the interval that follows an event is attributed to
+// the class of the kernel launched right after it.  Read back with gpt_get_kernel_times after a sync.
+enum { KT_GENERATE = 0, KT_EXTEND = 1, KT_SHADE = 2, KT_COLLECT = 3, KT_ACCUMULATE = 4, KT_RESOLVE = 5, KT_OTHER = 6, KT_END = 7, KT_CLASSES = 8 };
+struct KernelTimer {
+    std::vector<cudaEvent_t> ev;
+    std::vector<int> kind;
+    size_t used = 0;
+    void tick(int k, cudaStream_t st)
+    {
+        if (used == ev.size()) {
+            cudaEvent_t e;
+            if (cudaEventCreate(&e) != cudaSuccess) return;
+            ev.push_back(e); kind.push_back(KT_END);
+        }
+        kind[used] = k;
+        cudaEventRecord(ev[used], st);
+        ++used;
+    }
+    // sums the finished intervals into ms[]/n[] and forgets them; the caller has synchronised
+    void collect(double* ms, unsigned long long* n)
+    {
+        for (size_t i = 0; i + 1 < used; ++i) {
+            if (kind[i] == KT_END) continue;
+            float t = 0.0f;
+            if (cudaEventElapsedTime(&t, ev[i], ev[i + 1]) == cudaSuccess) { ms[kind[i]] += t; n[kind[i]] += 1; }
+        }
+        used = 0;
+    }
+    void release() { for (cudaEvent_t e : ev) cudaEventDestroy(e); ev.clear(); kind.clear(); used = 0; }
+};
 
 cudaError_t gptk_render_mega(const DevScene& sc, const RenderParams& p, float4* accum_f4, unsigned long long sample_begin,
                              uint32_t sample_count, unsigned int* work_counter, unsigned long long* stats,
@@ -34,4 +67,5 @@ size_t gptk_wave_counter_count(unsigned int depth);
 cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,
                                   float4* accum_f4, float* accum_v3, uint32_t* draw, unsigned long long constant_pdf,
                                   unsigned long long sample_begin, uint32_t sample_count,
-                                  unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches);
+                                  unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches,
+                                  KernelTimer* kt);

@@ -296,7 +296,8 @@ size_t gptk_wave_counter_count(unsigned int depth) { return 2 * ((size_t)depth +
 cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,
                                   float4* accum_f4, float* accum_v3, uint32_t* draw, unsigned long long constant_pdf,
                                   unsigned long long sample_begin, uint32_t sample_count,
-                                  unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches)
+                                  unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches,
+                                  KernelTimer* kt)
 {
     static int ext_grid = 0;
     if (!ext_grid) {
@@ -329,11 +330,13 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
             int cgrid = (n_wave + 255) / 256; if (cgrid > sm_count * 8) cgrid = sm_count * 8; if (cgrid < 1) cgrid = 1;
             const unsigned long long sample0 = sample_begin + s0;
             if ((e = cudaMemsetAsync(wb.counters, 0, sizeof(unsigned int) * gptk_wave_counter_count(p.depth), st)) != cudaSuccess) return e;
+            if (kt) kt->tick(KT_GENERATE, st);
             k_wf_generate<<<grid, 256, 0, st>>>(p, sample0, (int)ns, pix0, n_wave, wb.ray_o, wb.ray_d, wb.mask, wb.accu, wb.counters, stats);
             *launches += 1;
             for (uint32_t b = 0; b < p.depth; ++b) {
                 const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
                 if (has_mesh) {
+                    if (kt) kt->tick(KT_EXTEND, st);
                     if (use_ww)
                         k_wf_extend_ww<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                         wb.ray_o, wb.ray_d, wb.hit, refill_min);
@@ -342,18 +345,22 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                                                                      wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);
                     *launches += 1;
                 }
+                if (kt) kt->tick(KT_SHADE, st);
                 k_wf_shade<<<grid, 256, 0, st>>>(sc, p, sample0, b, (uint32_t)pix0, (uint32_t)n_wave, q_in, wb.counters, wb.queue[(b + 1u) & 1u],
                                                  wb.ray_o, wb.ray_d, wb.hit, wb.mask, wb.accu, stats);
                 *launches += 1;
             }
+            if (kt) kt->tick(KT_COLLECT, st);
             k_wf_collect<<<cgrid, 256, 0, st>>>(wb.accu, (int)ns, pix0, n_wave, wb.lsum);
             *launches += 1;
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
     }
     const int grid = agrid;
+    if (kt) kt->tick(KT_ACCUMULATE, st);
     if (legacy) k_wf_accumulate<true><<<grid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, nullptr, accum_v3, draw, constant_pdf);
     else k_wf_accumulate<false><<<grid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, accum_f4, nullptr, nullptr, 1ull);
     *launches += 1;
+    if (kt) kt->tick(KT_END, st);
     return cudaGetLastError();
 }

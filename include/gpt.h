@@ -97,7 +97,8 @@ enum {
     GPT_FLAG_NO_JITTER   = 1u << 0,  /* camera jitter off (hit-ID parity runs) */
     GPT_FLAG_METAL_FIXED = 1u << 1,  /* use the reflection vector w1 instead of the reference's int `w` */
     GPT_FLAG_MEGAKERNEL  = 1u << 2,  /* single persistent megakernel instead of the (default) wavefront pipeline */
-    GPT_FLAG_COUNT_BOUNCES = 1u << 3 /* fill gpt_stats.rays_by_bounce (slower) */
+    GPT_FLAG_COUNT_BOUNCES = 1u << 3, /* fill gpt_stats.rays_by_bounce (slower) */
+    GPT_FLAG_TIME_KERNELS = 1u << 4  /* CUDA-event timing per kernel class, read with gpt_get_kernel_times */
 };
 
 typedef struct {
@@ -106,6 +107,11 @@ typedef struct {
     uint64_t paths;               /* (pixel,sample) paths started */
     uint64_t kernel_launches;     /* library kernels launched */
 } gpt_stats;
+
+/* Device time per kernel class since the last gpt_reset_stats (GPT_FLAG_TIME_KERNELS): CUDA events recorded on the
+ * launching stream around every launch (replaces the reference's commented-out uf::GpuTimer, BasicScene.cpp:402-418). */
+enum { GPT_K_GENERATE = 0, GPT_K_EXTEND = 1, GPT_K_SHADE = 2, GPT_K_COLLECT = 3, GPT_K_ACCUMULATE = 4, GPT_K_RESOLVE = 5, GPT_K_OTHER = 6 };
+typedef struct { double ms[8]; uint64_t launches[8]; } gpt_kernel_times;
 
 typedef struct gpt_ctx gpt_ctx;
 typedef void* gpt_stream;   /* cudaStream_t */
@@ -166,6 +172,7 @@ GPT_API int gpt_trace_rays(gpt_ctx* ctx, const float* o, const float* d, size_t 
                            int32_t* tri_idx, int32_t* tri_addr, float* t, gpt_stream stream);
 GPT_API int gpt_get_stats(gpt_ctx* ctx, gpt_stats* out);      /* synchronises the context's streams */
 GPT_API int gpt_reset_stats(gpt_ctx* ctx);
+GPT_API int gpt_get_kernel_times(gpt_ctx* ctx, gpt_kernel_times* out);  /* synchronises; see GPT_FLAG_TIME_KERNELS */
 
 /* ---- host-side helpers mirroring the reference's scene setup (no GPU needed) ---- */
 GPT_API uint64_t gpt_hash64(uint64_t key);                                   /* uf::hash, utilfun.cpp:380-389 */
