@@ -72,6 +72,11 @@ class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("rays_by_bounce", C.c_uint64 * 16), ("paths", C.c_uint64), ("kernel_launches", C.c_uint64)]
 
 
+class BuiltBVH(C.Structure):  # gpt_built_bvh
+    _fields_ = [("bvh", BVHData), ("n_inner_nodes", C.c_uint32), ("n_leaves", C.c_uint32), ("n_triangles", C.c_uint32),
+                ("depth", C.c_uint32), ("build_ms", C.c_float)]
+
+
 class KernelTimes(C.Structure):
     _fields_ = [("ms", C.c_double * 8), ("launches", C.c_uint64 * 8)]
 
@@ -83,6 +88,7 @@ assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
            "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
            "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times",
+           "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_hash64", "gpt_default_spheres", "gpt_default_kernel_info", "gpt_set_camera"]
 
 _lib = None
@@ -116,6 +122,9 @@ def load_library():
     L.gpt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
     L.gpt_reset_stats.argtypes = [C.c_void_p]
     L.gpt_get_kernel_times.argtypes = [C.c_void_p, C.POINTER(KernelTimes)]
+    L.gpt_build_bvh.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.POINTER(BuiltBVH)]
+    L.gpt_free_bvh.argtypes = [C.c_void_p, C.POINTER(BuiltBVH)]
+    L.gpt_copy_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
     L.gpt_hash64.argtypes = [C.c_uint64]
     L.gpt_hash64.restype = C.c_uint64
     L.gpt_default_spheres.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -265,6 +274,38 @@ class Context:
         s = Stats()
         self._ck(self._L.gpt_get_stats(self._h, C.byref(s)), "gpt_get_stats")
         return s
+
+    def build_bvh(self, verts, faces, on_device=False, max_leaf=8):
+        """Device-side LBVH build (gpt_build_bvh): verts (n,3) float32, faces (m,3) int32 -> BuiltBVH whose .bvh holds
+        DEVICE arrays in CudaBVH's compact layout.  Free with free_bvh()."""
+        def cnt(a):
+            return int(a.numel() if hasattr(a, "numel") else a.size) // 3
+        b = BuiltBVH()
+        self._ck(self._L.gpt_build_bvh(self._h, _ptr(verts), cnt(verts), _ptr(faces), cnt(faces), 1 if on_device else 0,
+                                       C.c_uint32(max_leaf), C.byref(b)), "gpt_build_bvh")
+        return b
+
+    def free_bvh(self, b):
+        self._ck(self._L.gpt_free_bvh(self._h, C.byref(b)), "gpt_free_bvh")
+
+    def built_to_host(self, b):
+        """numpy copies of a BuiltBVH's arrays: dict(nodes (n,4) f32, tris (n,4) f32, indices i32)."""
+        out = {}
+        for key, ptr, n, dt, w in (("nodes", b.bvh.dev_triNode, b.bvh.triNodeSize, np.float32, 4),
+                                   ("tris", b.bvh.dev_triPtr, b.bvh.triSize, np.float32, 4),
+                                   ("indices", b.bvh.dev_triIndicesPtr, b.bvh.triIndicesSize, np.int32, 1)):
+            a = np.empty((int(n), w) if w > 1 else (int(n),), dtype=dt)
+            self._ck(self._L.gpt_copy_to_host(self._h, a.ctypes.data, ptr, a.nbytes), "gpt_copy_to_host")
+            out[key] = a
+        return out
+
+    def upload_built(self, b, spheres=None, boxes=None):
+        """gpt_upload_scene(on_device=1) with a BuiltBVH's arrays."""
+        ns = len(spheres) if spheres is not None else 0
+        nb = len(boxes) if boxes is not None else 0
+        self._ck(self._L.gpt_upload_scene(self._h, b.bvh.dev_triNode, b.bvh.triNodeSize, b.bvh.dev_triPtr, b.bvh.triSize,
+                                          b.bvh.dev_triIndicesPtr, b.bvh.triIndicesSize, _ptr(spheres) if ns else None, ns,
+                                          _ptr(boxes) if nb else None, nb, 1), "gpt_upload_scene")
 
     def kernel_times(self):
         """{class name: (ms, launches)} since the last reset_stats (needs FLAG_TIME_KERNELS)."""

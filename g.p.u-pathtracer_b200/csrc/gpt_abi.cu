@@ -174,7 +174,8 @@ int gpt_upload_scene(gpt_ctx* c, const void* nodes, size_t n_node_vec4, const vo
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaDeviceSynchronize());
     free_scene(c);
-    const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    // spheres / boxes may live on either side regardless of `on_device` (which describes the BVH arrays): UVA sorts it out
+    const cudaMemcpyKind kind = cudaMemcpyDefault;
     int rc = GPT_OK;
     if (n_node_vec4 && nodes) {
         if (on_device) {
@@ -207,6 +208,69 @@ int gpt_upload_scene(gpt_ctx* c, const void* nodes, size_t n_node_vec4, const vo
         c->n_boxes = (int)n_boxes;
     }
     c->has_scene = true;
+    return GPT_OK;
+}
+
+int gpt_build_bvh(gpt_ctx* c, const float* verts, size_t n_verts, const int32_t* tris, size_t n_tris, int on_device,
+                  uint32_t max_leaf_size, gpt_built_bvh* out)
+{
+    if (!c || !out) return GPT_ERR_INVALID;
+    memset(out, 0, sizeof(*out));
+    if (n_tris == 0) return fail(c, GPT_ERR_INVALID, "gpt_build_bvh: empty mesh");
+    if (!verts || !tris || n_verts == 0) return fail(c, GPT_ERR_INVALID, "gpt_build_bvh: NULL vertex / triangle array");
+    CU(c, cudaSetDevice(c->device));
+    cudaEvent_t e0, e1;
+    CU(c, cudaEventCreate(&e0)); CU(c, cudaEventCreate(&e1));
+    cudaEventRecord(e0, 0);
+    float* dv = nullptr; int* dt = nullptr;
+    cudaError_t e = cudaSuccess;
+    if (!on_device) {
+        if ((e = cudaMalloc(&dv, n_verts * 12)) != cudaSuccess || (e = cudaMalloc(&dt, n_tris * 12)) != cudaSuccess ||
+            (e = cudaMemcpy(dv, verts, n_verts * 12, cudaMemcpyHostToDevice)) != cudaSuccess ||
+            (e = cudaMemcpy(dt, tris, n_tris * 12, cudaMemcpyHostToDevice)) != cudaSuccess) {
+            cudaFree(dv); cudaFree(dt); cudaEventDestroy(e0); cudaEventDestroy(e1);
+            return fail(c, GPT_ERR_CUDA, "gpt_build_bvh: staging copy", e);
+        }
+    }
+    BuildResult r;
+    e = gptk_build_lbvh(on_device ? verts : dv, n_verts, on_device ? tris : dt, n_tris, max_leaf_size ? (int)max_leaf_size : 8, &r, 0);
+    cudaEventRecord(e1, 0);
+    cudaEventSynchronize(e1);
+    float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(dv); cudaFree(dt);
+    c->launches += (unsigned long long)r.launches;
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "gpt_build_bvh", e);
+    if (r.status == 0 && r.depth > GPT_STACK_SIZE) { cudaFree(r.nodes); cudaFree(r.tris); cudaFree(r.indices); r.status = 4; }
+    if (r.status) {
+        static const char* why[] = {"", "vertex index out of range", "non-finite vertex", "mesh too large for 32-bit offsets", "tree deeper than the 64-entry traversal stack"};
+        char buf[128]; snprintf(buf, sizeof(buf), "gpt_build_bvh: %s", why[r.status < 5 ? r.status : 0]);
+        return fail(c, r.status == 3 || r.status == 4 ? GPT_ERR_LAYOUT : GPT_ERR_INVALID, buf);
+    }
+    out->bvh.dev_triNode = r.nodes; out->bvh.triNodeSize = r.n_node_vec4;
+    out->bvh.dev_triPtr = r.tris; out->bvh.triSize = r.n_tri_vec4;
+    out->bvh.dev_triIndicesPtr = r.indices; out->bvh.triIndicesSize = r.n_indices;
+    out->n_inner_nodes = (uint32_t)(r.n_node_vec4 / 4); out->n_leaves = (uint32_t)r.n_leaves;
+    out->n_triangles = (uint32_t)n_tris; out->depth = (uint32_t)r.depth; out->build_ms = ms;
+    return GPT_OK;
+}
+
+int gpt_free_bvh(gpt_ctx* c, gpt_built_bvh* b)
+{
+    if (!c || !b) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());
+    if (c->src_nodes == b->bvh.dev_triNode) c->src_nodes = nullptr;      // the packed copy stays valid; force a re-pack if the address is reused
+    cudaFree(b->bvh.dev_triNode); cudaFree(b->bvh.dev_triPtr); cudaFree(b->bvh.dev_triIndicesPtr);
+    memset(b, 0, sizeof(*b));
+    return GPT_OK;
+}
+
+int gpt_copy_to_host(gpt_ctx* c, void* dst, const void* src, size_t bytes)
+{
+    if (!c || (bytes && (!dst || !src))) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
     return GPT_OK;
 }
 

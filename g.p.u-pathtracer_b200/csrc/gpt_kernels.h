@@ -55,6 +55,13 @@ struct RepackResult { float4* nodes; float4* tris; int n_nodes; int n_tris; int 
 cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float4* ref_tris, size_t n_tri_vec4,
                         const int* ref_indices, size_t n_indices, RepackResult* out, cudaStream_t st);
 
+// device-side LBVH builder (gpt_build.cu): indexed mesh (device pointers) -> arrays in CudaBVH's compact layout,
+// cudaMalloc'd by the callee.  status: 0 ok, 1 vertex index out of range, 2 non-finite vertex, 3 too large, 4 too deep
+struct BuildResult { float4* nodes; size_t n_node_vec4; float4* tris; size_t n_tri_vec4; int* indices; size_t n_indices;
+                     int n_leaves; int depth; int status; int launches; };
+cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, size_t n_tris, int max_leaf,
+                            BuildResult* out, cudaStream_t st);
+
 // wavefront pipeline (gpt_wavefront.cu).  Per-path arrays hold `capacity` entries, lsum one per pixel.
 struct WaveBuffers {
     float4 *ray_o, *ray_d, *mask, *accu, *lsum;

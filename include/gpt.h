@@ -137,6 +137,27 @@ GPT_API int gpt_upload_scene(gpt_ctx* ctx,
                              const gpt_box* boxes, size_t n_boxes,
                              int on_device);
 
+/* ---- device-side BVH builder ----
+ * Replaces, for scenes where the single-threaded host build is the bottleneck (2.9 s per 100 k triangles), the
+ * pipeline  BVH myBVH(&scene, Platform(), BuildParams()); new CudaBVH(myBVH, BVHLayout_Compact)  of
+ * BasicScene.cpp:283-292 (SplitBVHBuilder.cpp:32-164, CudaBVH.cpp:121-270).  Input: the indexed mesh
+ * uf::loadIndexedTris returns (utilfun.cpp:454-524; verts = n_verts*3 floats, tris = n_tris*3 ints), host
+ * (on_device=0) or device pointers.  Output: DEVICE arrays in exactly the layout CudaBVH::getGpuNodes /
+ * getDebugTri / getGpuTriIndices hand out, so `out->bvh` can be stored into kernelInfo.bvhData or passed to
+ * gpt_upload_scene(..., on_device=1).  The tree is an LBVH (Morton radix tree + SAH leaf collapse with the
+ * reference's cost model 1/1), not the reference's SBVH: hit distances are identical, tie-breaking between
+ * triangles with bit-equal t may differ.  The arrays belong to the caller until gpt_free_bvh. */
+typedef struct {
+    gpt_bvh_data bvh;
+    uint32_t n_inner_nodes, n_leaves, n_triangles, depth;
+    float build_ms;                 /* device + host time of the call */
+} gpt_built_bvh;
+GPT_API int gpt_build_bvh(gpt_ctx* ctx, const float* verts, size_t n_verts, const int32_t* tris, size_t n_tris,
+                          int on_device, uint32_t max_leaf_size, gpt_built_bvh* out);
+GPT_API int gpt_free_bvh(gpt_ctx* ctx, gpt_built_bvh* bvh);
+/* plain cudaMemcpy device -> host (so C callers and the ctypes tests can inspect built arrays without the runtime) */
+GPT_API int gpt_copy_to_host(gpt_ctx* ctx, void* dst_host, const void* src_device, size_t bytes);
+
 /* ---- render launch ---- */
 /* Drop-in for launchKernel (tracer.cu:405-415): ONE progressive pass (1 spp) with the reference's
  * exact field meanings: vec3 running mean with per-frame clamp into info->accumBuffer, RGBA8 pack into
