@@ -60,3 +60,37 @@ def synthetic_scene(n_tris_target, seed=1234, level=4, box_fraction=0.02):
         verts = np.concatenate([verts, bv])
         faces = np.concatenate([faces, bf])
     return np.ascontiguousarray(verts, dtype=np.float32), np.ascontiguousarray(faces, dtype=np.int32)
+
+
+def subdivide(verts, faces, times=1):
+    """1 -> 4 midpoint subdivision (shared midpoints welded); keeps the surface, multiplies the triangle count by 4."""
+    v, f = verts.astype(np.float32), faces.astype(np.int64)
+    for _ in range(times):
+        e = np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]])
+        uniq, inv = np.unique(np.sort(e, axis=1), axis=0, return_inverse=True)
+        mid = 0.5 * (v[uniq[:, 0]] + v[uniq[:, 1]])
+        m = len(v) + inv.reshape(3, -1).T
+        v = np.concatenate([v, mid.astype(np.float32)])
+        a, b, c = f[:, 0], f[:, 1], f[:, 2]
+        ab, bc, ca = m[:, 0], m[:, 1], m[:, 2]
+        f = np.concatenate([np.stack([a, ab, ca], 1), np.stack([b, bc, ab], 1), np.stack([c, ca, bc], 1), np.stack([ab, bc, ca], 1)])
+    return np.ascontiguousarray(v, np.float32), np.ascontiguousarray(f, np.int32)
+
+
+def instance_grid(verts, faces, nx, nz, scale, x_step, z_first, z_step, floor_y=-15.0):
+    """nx x nz copies of a mesh (vertex duplication before the BVH build, SURVEY cfg4 "multi-instance"): each copy is
+    scaled about its bounding-box centre, put on the room's floor (y = floor_y; the default room is x[-20,20]
+    y[-15,15], BasicScene.cpp:180-202) and placed on a grid in x and depth."""
+    lo, hi = verts.min(0), verts.max(0)
+    c = 0.5 * (lo + hi)
+    base = (verts - c) * scale
+    half_h = 0.5 * (hi[1] - lo[1]) * scale
+    vs, fs = [], []
+    k = 0
+    for j in range(nz):
+        for i in range(nx):
+            off = np.array([(i - (nx - 1) / 2.0) * x_step, floor_y + half_h + 0.01, z_first - j * z_step], np.float32)
+            vs.append((base + off).astype(np.float32))
+            fs.append(faces + k * len(verts))
+            k += 1
+    return np.ascontiguousarray(np.concatenate(vs), np.float32), np.ascontiguousarray(np.concatenate(fs), np.int32)
