@@ -33,8 +33,15 @@ METRIC = "Mrays/s (prim+sec) @1080p 16spp depth 8"
 # Algorithmic bytes per ray of THIS workload, counted by the CPU oracle executing the reference algorithm on
 # the reference BVH2 arrays (64*N_inner + 48*N_tri + 16*N_leaf + 4*[tri hit] + 44*N_sphere), full
 # frame, 1 spp, seed 0 (profiles/r01_algorithmic_bytes.json; re-measured on a sample by the cpu_baseline leg).
+_REAL_STDOUT = None
 ALGO_BYTES_PER_RAY = None   # filled from profiles/r01_algorithmic_bytes.json
 ACCUM_BYTES_PER_PIXEL_PER_LAUNCH = 32
+
+
+def emit_line(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def load_algo_bytes():
@@ -308,7 +315,7 @@ def run_reference_arm(args):
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit_line(line)
     return 0
 
 
@@ -480,7 +487,7 @@ def run_ours(args):
                 rg = {"unavailable": repr(ex)}
             if rg is not None:
                 line["reference_gpu_kernel"] = rg
-        print(json.dumps(line))
+        emit_line(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -504,6 +511,12 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
+    # stdout carries exactly ONE JSON line: anything libraries print to fd 1 meanwhile (NCCL's version banner, the
+    # reference CPU tracer's load messages) is routed to stderr, and the line is written to the real stdout at the end
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_ours(args)

@@ -19,6 +19,9 @@
 #include <cstdlib>
 
 #define WF_THREADS 128
+#ifndef WF_MIN_BLOCKS
+#define WF_MIN_BLOCKS 10   // 51-register cap, no spills; measured +1.5% over 8 (profiles/r01_sweep_extend.log)
+#endif
 
 struct SmemPrims {
     float spheres[GPT_MAX_SMEM_SPHERES * 11];
@@ -123,7 +126,7 @@ k_wf_extend(const DevScene sc, const int cull, const uint32_t* __restrict__ queu
 // persistent while-while loop.  All lanes meet at the top of the outer loop once per "descend to the next leaf +
 // test that leaf" round; idle lanes are re-armed there.  Tighter inner loops than the voted steps above, but
 // lanes wait for the slowest descent / largest leaf of the round.
-__global__ void __launch_bounds__(WF_THREADS, 8)
+__global__ void __launch_bounds__(WF_THREADS, WF_MIN_BLOCKS)
 k_wf_extend_ww(const DevScene sc, const int cull, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
                unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                int2* __restrict__ hit, const int refill_min)
@@ -299,14 +302,14 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                                   unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches,
                                   KernelTimer* kt)
 {
+    static const bool use_ww = getenv("GPT_WF_VOTED") == nullptr;     // default: while-while extend
     static int ext_grid = 0;
     if (!ext_grid) {
         int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, use_ww ? (const void*)k_wf_extend_ww : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
         ext_grid = sm_count * per_sm;
     }
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
-    static const bool use_ww = getenv("GPT_WF_VOTED") == nullptr;     // default: while-while extend
     const int n_pix = p.width * p.height;
     // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays
     // hold (88 B/path).  Big waves matter: every launch has a fixed cost (launch gap + the tail where the
