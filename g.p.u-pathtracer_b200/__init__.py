@@ -89,6 +89,7 @@ EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string"
            "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
            "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
+           "gpt_load_obj", "gpt_free_host", "gpt_write_png", "gpt_write_pfm",
            "gpt_hash64", "gpt_default_spheres", "gpt_default_kernel_info", "gpt_set_camera"]
 
 _lib = None
@@ -132,6 +133,12 @@ def load_library():
     L.gpt_default_kernel_info.restype = None
     L.gpt_set_camera.argtypes = [C.POINTER(CamInfo), C.c_void_p, C.c_float, C.c_float]
     L.gpt_set_camera.restype = None
+    L.gpt_load_obj.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_size_t),
+                               C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_size_t)]
+    L.gpt_free_host.argtypes = [C.c_void_p]
+    L.gpt_free_host.restype = None
+    L.gpt_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+    L.gpt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
     _lib = L
     return L
 
@@ -176,6 +183,38 @@ def spheres_from_list(items):
         s.col[:] = col
         s.mat = int(mat)
     return arr
+
+
+def load_obj(path):
+    """uf::loadIndexedTris (utilfun.cpp:454-524) -> (verts (n,3) float32, faces (m,3) int32)."""
+    L = load_library()
+    v, t = C.POINTER(C.c_float)(), C.POINTER(C.c_int32)()
+    nv, nt = C.c_size_t(0), C.c_size_t(0)
+    rc = L.gpt_load_obj(os.fsencode(path), C.byref(v), C.byref(nv), C.byref(t), C.byref(nt))
+    if rc != 0:
+        raise GptError("gpt_load_obj(%s) failed (%d)" % (path, rc))
+    try:
+        verts = np.ctypeslib.as_array(v, shape=(nv.value * 3,)).copy().reshape(-1, 3) if nv.value else np.zeros((0, 3), np.float32)
+        faces = np.ctypeslib.as_array(t, shape=(nt.value * 3,)).copy().reshape(-1, 3) if nt.value else np.zeros((0, 3), np.int32)
+    finally:
+        L.gpt_free_host(v)
+        L.gpt_free_host(t)
+    return verts, faces
+
+
+def write_png(path, rgba8, width, height):
+    """rgba8: host uint32/int32 array of W*H 0x00BBGGRR pixels, row 0 = bottom (the dev_drawRes layout)."""
+    a = np.ascontiguousarray(rgba8).view(np.uint32)
+    rc = load_library().gpt_write_png(os.fsencode(path), a.ctypes.data, int(width), int(height))
+    if rc != 0:
+        raise GptError("gpt_write_png failed (%d)" % rc)
+
+
+def write_pfm(path, rgb, width, height):
+    a = np.ascontiguousarray(rgb, dtype=np.float32)
+    rc = load_library().gpt_write_pfm(os.fsencode(path), a.ctypes.data, int(width), int(height))
+    if rc != 0:
+        raise GptError("gpt_write_pfm failed (%d)" % rc)
 
 
 def _ptr(x):

@@ -98,3 +98,175 @@ void gpt_default_kernel_info(gpt_kernel_info* info, int width, int height)
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------- headless scene / image I/O
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+// strtof on the "C" locale subset OBJ files use; returns false at end of line
+bool next_float(const char*& p, float* out)
+{
+    while (*p == ' ' || *p == '\t') ++p;
+    if (*p == '\0' || *p == '\n' || *p == '\r' || *p == '#') return false;
+    char* end = nullptr;
+    *out = strtof(p, &end);
+    if (end == p) return false;
+    p = end;
+    return true;
+}
+
+uint32_t crc_table[256];
+bool crc_ready = false;
+uint32_t crc32_update(uint32_t c, const unsigned char* buf, size_t n)
+{
+    if (!crc_ready) {
+        for (uint32_t i = 0; i < 256; ++i) { uint32_t k = i; for (int j = 0; j < 8; ++j) k = (k & 1u) ? 0xEDB88320u ^ (k >> 1) : k >> 1; crc_table[i] = k; }
+        crc_ready = true;
+    }
+    for (size_t i = 0; i < n; ++i) c = crc_table[(c ^ buf[i]) & 0xffu] ^ (c >> 8);
+    return c;
+}
+
+void put_be32(std::vector<unsigned char>& v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }
+
+bool write_chunk(FILE* f, const char* tag, const std::vector<unsigned char>& data)
+{
+    std::vector<unsigned char> hdr; put_be32(hdr, (uint32_t)data.size());
+    unsigned char t[4] = {(unsigned char)tag[0], (unsigned char)tag[1], (unsigned char)tag[2], (unsigned char)tag[3]};
+    uint32_t c = crc32_update(0xffffffffu, t, 4);
+    if (!data.empty()) c = crc32_update(c, data.data(), data.size());
+    c ^= 0xffffffffu;
+    std::vector<unsigned char> tail; put_be32(tail, c);
+    return fwrite(hdr.data(), 1, 4, f) == 4 && fwrite(t, 1, 4, f) == 4 &&
+           (data.empty() || fwrite(data.data(), 1, data.size(), f) == data.size()) && fwrite(tail.data(), 1, 4, f) == 4;
+}
+
+} // namespace
+
+extern "C" {
+
+// uf::loadIndexedTris (utilfun.cpp:454-524): every `v` in file order, per face the 0-based vertex index of each
+// corner, polygons fan-triangulated (v0, v[k], v[k+1]) like tinyobjloader; normals / uvs / materials dropped
+// (SURVEY F5).  Unlike the reference (assert(shapes.size()==1), :474) several o/g shapes are merged into one mesh.
+int gpt_load_obj(const char* path, float** verts_out, size_t* n_verts, int32_t** tris_out, size_t* n_tris)
+{
+    if (!path || !verts_out || !n_verts || !tris_out || !n_tris) return GPT_ERR_INVALID;
+    *verts_out = nullptr; *tris_out = nullptr; *n_verts = 0; *n_tris = 0;
+    FILE* f = fopen(path, "rb");
+    if (!f) return GPT_ERR_IO;
+    std::vector<float> v;
+    std::vector<int32_t> t;
+    std::vector<long long> corner;
+    std::string line;
+    char buf[4096];
+    bool bad = false;
+    while (fgets(buf, sizeof(buf), f)) {
+        line.assign(buf);
+        while (!line.empty() && line.back() != '\n' && fgets(buf, sizeof(buf), f)) line.append(buf);   // long lines
+        const char* p = line.c_str();
+        while (*p == ' ' || *p == '\t') ++p;
+        if (p[0] == 'v' && (p[1] == ' ' || p[1] == '\t')) {
+            p += 2;
+            float x[3] = {0.0f, 0.0f, 0.0f};
+            for (int k = 0; k < 3; ++k) if (!next_float(p, &x[k])) { bad = true; break; }
+            v.push_back(x[0]); v.push_back(x[1]); v.push_back(x[2]);
+        } else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
+            p += 2;
+            corner.clear();
+            const long long nv = (long long)(v.size() / 3);
+            while (true) {
+                while (*p == ' ' || *p == '\t') ++p;
+                if (*p == '\0' || *p == '\n' || *p == '\r' || *p == '#') break;
+                char* end = nullptr;
+                const long long i = strtoll(p, &end, 10);
+                if (end == p) { bad = true; break; }
+                p = end;
+                while (*p != '\0' && *p != ' ' && *p != '\t' && *p != '\n' && *p != '\r') ++p;   // skip /vt/vn
+                const long long idx = i > 0 ? i - 1 : nv + i;
+                if (idx < 0 || idx >= nv) { bad = true; break; }
+                corner.push_back(idx);
+            }
+            for (size_t k = 1; k + 1 < corner.size(); ++k) { t.push_back((int32_t)corner[0]); t.push_back((int32_t)corner[k]); t.push_back((int32_t)corner[k + 1]); }
+        }
+        if (bad) break;
+    }
+    fclose(f);
+    if (bad) return GPT_ERR_IO;
+    float* vo = (float*)malloc(v.size() * sizeof(float) + 4);
+    int32_t* to = (int32_t*)malloc(t.size() * sizeof(int32_t) + 4);
+    if (!vo || !to) { free(vo); free(to); return GPT_ERR_INVALID; }
+    if (!v.empty()) memcpy(vo, v.data(), v.size() * sizeof(float));
+    if (!t.empty()) memcpy(to, t.data(), t.size() * sizeof(int32_t));
+    *verts_out = vo; *n_verts = v.size() / 3; *tris_out = to; *n_tris = t.size() / 3;
+    return GPT_OK;
+}
+
+void gpt_free_host(void* p) { free(p); }
+
+// dev_drawRes layout (tracer.cu:394-398): W*H uint32 0x00BBGGRR, row 0 = BOTTOM of the image (getCamRayDir,
+// cudaUtils.h:111-134) -> 8-bit RGB PNG, top row first.  Replaces the GL texture blit + quad draw
+// (BasicScene.cpp:424-432,468) and lodepng in the CPU tracer (renderer.cpp:224-245).  Stored (uncompressed)
+// deflate blocks: no zlib dependency.
+int gpt_write_png(const char* path, const uint32_t* rgba8, int width, int height)
+{
+    if (!path || !rgba8 || width <= 0 || height <= 0) return GPT_ERR_INVALID;
+    FILE* f = fopen(path, "wb");
+    if (!f) return GPT_ERR_IO;
+    static const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    bool ok = fwrite(sig, 1, 8, f) == 8;
+    std::vector<unsigned char> ihdr;
+    put_be32(ihdr, (uint32_t)width); put_be32(ihdr, (uint32_t)height);
+    ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);   // 8-bit RGB
+    ok = ok && write_chunk(f, "IHDR", ihdr);
+    const size_t stride = 1 + 3 * (size_t)width;
+    std::vector<unsigned char> raw(stride * (size_t)height);
+    for (int y = 0; y < height; ++y) {
+        const uint32_t* src = rgba8 + (size_t)(height - 1 - y) * width;      // vertical flip
+        unsigned char* dst = raw.data() + stride * (size_t)y;
+        dst[0] = 0;                                                           // filter: none
+        for (int x = 0; x < width; ++x) { const uint32_t c = src[x]; dst[1 + 3 * x] = c & 0xff; dst[2 + 3 * x] = (c >> 8) & 0xff; dst[3 + 3 * x] = (c >> 16) & 0xff; }
+    }
+    std::vector<unsigned char> z;
+    z.reserve(raw.size() + raw.size() / 65535 * 5 + 16);
+    z.push_back(0x78); z.push_back(0x01);
+    uint32_t a = 1, b = 0;
+    size_t pos = 0;
+    while (pos < raw.size() || raw.empty()) {
+        const size_t n = raw.size() - pos < 65535 ? raw.size() - pos : 65535;
+        z.push_back(pos + n == raw.size() ? 1 : 0);
+        z.push_back(n & 0xff); z.push_back(n >> 8); z.push_back(~n & 0xff); z.push_back((~n >> 8) & 0xff);
+        z.insert(z.end(), raw.begin() + pos, raw.begin() + pos + n);
+        pos += n;
+        if (pos >= raw.size()) break;
+    }
+    for (size_t i = 0; i < raw.size();) {                                     // adler32, modulo deferred per 5552 bytes
+        const size_t n = raw.size() - i < 5552 ? raw.size() - i : 5552;
+        for (size_t k = 0; k < n; ++k) { a += raw[i + k]; b += a; }
+        a %= 65521u; b %= 65521u; i += n;
+    }
+    put_be32(z, (b << 16) | a);
+    ok = ok && write_chunk(f, "IDAT", z) && write_chunk(f, "IEND", std::vector<unsigned char>());
+    ok = (fclose(f) == 0) && ok;
+    return ok ? GPT_OK : GPT_ERR_IO;
+}
+
+// Linear float image (PFM "PF", little endian, bottom row first -- the accumulation buffer's own row order):
+// rgb = W*H*3 floats as gpt_resolve's out_rgb_f32 writes them.
+int gpt_write_pfm(const char* path, const float* rgb, int width, int height)
+{
+    if (!path || !rgb || width <= 0 || height <= 0) return GPT_ERR_INVALID;
+    FILE* f = fopen(path, "wb");
+    if (!f) return GPT_ERR_IO;
+    bool ok = fprintf(f, "PF\n%d %d\n-1.0\n", width, height) > 0;
+    const size_t n = 3 * (size_t)width * (size_t)height;
+    ok = ok && fwrite(rgb, sizeof(float), n, f) == n;
+    ok = (fclose(f) == 0) && ok;
+    return ok ? GPT_OK : GPT_ERR_IO;
+}
+
+} // extern "C"

@@ -201,6 +201,18 @@ GPT_API int  gpt_default_spheres(gpt_sphere* out, size_t cap, size_t* n);   /* B
 GPT_API void gpt_default_kernel_info(gpt_kernel_info* info, int width, int height); /* BasicScene.cpp:220-259 */
 GPT_API void gpt_set_camera(gpt_cam_info* cam, const float pos[3], float yaw_deg, float pitch_deg); /* BasicScene.cpp:42-64 */
 
+/* ---- headless scene / image I/O (no GPU needed) ---- */
+/* uf::loadIndexedTris (utilfun.cpp:454-524): indexed triangle mesh of an OBJ file (fan-triangulated, 0-based,
+ * materials dropped); several shapes are merged (the reference asserts exactly one, :474).  The arrays are
+ * malloc'd by the library; release with gpt_free_host. */
+GPT_API int  gpt_load_obj(const char* path, float** verts, size_t* n_verts, int32_t** tris, size_t* n_tris);
+GPT_API void gpt_free_host(void* p);
+/* RGBA8 frame as dev_drawRes holds it (0x00BBGGRR, row 0 = bottom; copied to the host by the caller) -> PNG, top
+ * row first: replaces the GL texture blit + quad (BasicScene.cpp:424-432,468; renderer.cpp:224-245). */
+GPT_API int  gpt_write_png(const char* path, const uint32_t* host_rgba8, int width, int height);
+/* linear float RGB (gpt_resolve's out_rgb_f32, copied to the host) -> PFM, bottom row first */
+GPT_API int  gpt_write_pfm(const char* path, const float* host_rgb, int width, int height);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,6 +5,8 @@ the GPU built: (t, triangle slot, OBJ face index) must match bit for bit.  Again
 (SplitBVHBuilder, committed fixtures) the nearest-hit distances must be bit-identical too -- the tree only decides
 which triangles are tested, not the per-triangle arithmetic -- and face indices may differ only on exact t ties.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -192,3 +194,45 @@ def test_large_procedural_scene_builds_fast_and_traces_exactly(gpt, torch_cuda):
         np.testing.assert_array_equal(tri.cpu().numpy(), tri_o)
         print("1M-triangle LBVH: %.1f ms, %d inner nodes, %d leaves, depth %d" % (b.build_ms, b.n_inner_nodes, b.n_leaves, b.depth))
         ctx.free_bvh(b)
+
+
+def test_headless_cli_renders_an_obj_like_the_library(gpt, torch_cuda, tmp_path):
+    """N1: the C++ driver (OBJ -> device BVH -> progressive passes -> PNG/PFM) against the same steps through the
+    Python mirror: identical float image; PNG = clamped, truncated 8-bit pack (tracer.cu:394-398), top row first."""
+    import subprocess
+    from support import objio
+    torch = torch_cuda
+    exe = os.path.join(os.path.dirname(gpt.LIB_PATH), "gpt_headless")
+    if not os.path.exists(exe):
+        pytest.fail("gpt_headless not built (make -C g.p.u-pathtracer_b200/host)")
+    sc = scenes.load_scene("bunny_cornell")
+    obj = str(tmp_path / "scene.obj")
+    objio.write_obj(obj, sc["verts"], sc["faces"])
+    W, H, SPP = 160, 90, 12
+    png, pfm = str(tmp_path / "o.png"), str(tmp_path / "o.pfm")
+    out = subprocess.run([exe, "--obj", obj, "--width", str(W), "--height", str(H), "--spp", str(SPP), "--frames-per-pass", "5", "--depth", "5",
+                          "--mat", "spec", "--seed", "3", "--png", png, "--pfm", pfm], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "built on the device" in out.stdout
+    blob = open(pfm, "rb").read()
+    hdr = ("PF\n%d %d\n-1.0\n" % (W, H)).encode()
+    got = np.frombuffer(blob[len(hdr):], np.float32).reshape(H, W, 3)
+    v, f = gpt.load_obj(obj)
+    info = gpt.default_kernel_info(W, H)
+    info.depth, info.triCurrentMat = 5, gpt.SPEC
+    with gpt.Context(0) as ctx:
+        b = ctx.build_bvh(v, f)
+        ctx.upload_built(b, gpt.default_spheres())
+        total = np.zeros((H, W, 4), np.float32)
+        for begin, n in ((0, 5), (5, 5), (10, 2)):                   # the CLI's pass structure: host-side sum of per-pass sums
+            acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
+            ctx.render(info, acc, 3, begin, n)
+            torch.cuda.synchronize()
+            total += acc.cpu().numpy()
+        ctx.free_bvh(b)
+    want = total[..., :3] * (np.float32(1.0) / total[..., 3:4])
+    np.testing.assert_array_equal(got, want)
+    from PIL import Image
+    im = np.array(Image.open(png))
+    pack = (np.float32(255.0) * np.clip(want, 0, 1)).astype(np.int32).astype(np.uint8)[::-1]
+    np.testing.assert_array_equal(im, pack)

@@ -1,0 +1,82 @@
+"""Host-side I/O of the headless layer: OBJ loader, PNG / PFM writers.  No GPU needed."""
+import os
+import struct
+import zlib
+
+import numpy as np
+
+from support import objio, scenes
+
+
+def test_load_obj_matches_reference_loader_semantics(gpt, tmp_path):
+    """uf::loadIndexedTris keeps every `v` in file order and fan-triangulates polygons (utilfun.cpp:454-524)."""
+    p = tmp_path / "m.obj"
+    p.write_text("# comment\no a\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nvn 0 0 1\nvt 0 0\n"
+                 "f 1/1/1 2/1/1 3/1/1 4/1/1\n"                     # quad -> 2 triangles
+                 "g b\nv 0 0 -1\nv 1 0 -1.5e0\nv 1 1 -1\n"
+                 "f -3 -2 -1\n"                                    # negative (relative) indices
+                 "f 1//1 5//1 6//1 7//1 2//1\n")                   # pentagon -> 3 triangles
+    v, f = gpt.load_obj(str(p))
+    v2, f2 = objio.load_obj(str(p))
+    assert v.shape == (7, 3) and f.shape == (6, 3)
+    np.testing.assert_array_equal(v, v2)
+    np.testing.assert_array_equal(f, f2)
+    assert f.tolist()[:3] == [[0, 1, 2], [0, 2, 3], [4, 5, 6]]
+
+
+def test_load_obj_roundtrip_of_a_fixture_and_errors(gpt, tmp_path):
+    sc = scenes.load_scene("bunny_cornell")
+    p = tmp_path / "bunny.obj"
+    objio.write_obj(str(p), sc["verts"], sc["faces"])
+    v, f = gpt.load_obj(str(p))
+    np.testing.assert_array_equal(f, sc["faces"])
+    np.testing.assert_allclose(v, sc["verts"], rtol=0, atol=0)       # %.9g round-trips float32
+    import pytest
+    with pytest.raises(gpt.GptError):
+        gpt.load_obj(str(tmp_path / "missing.obj"))
+    bad = tmp_path / "bad.obj"
+    bad.write_text("v 0 0 0\nf 1 2 3\n")                              # index beyond the vertices read so far
+    with pytest.raises(gpt.GptError):
+        gpt.load_obj(str(bad))
+
+
+def _png_pixels(path):
+    """independent decoder: chunks, CRCs, zlib stream, filter type 0 rows"""
+    data = open(path, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w, h = 8, b"", 0, 0
+    while pos < len(data):
+        n, tag = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        crc, = struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])
+        assert zlib.crc32(tag + body) & 0xffffffff == crc
+        if tag == b"IHDR":
+            w, h, bits, ctype = struct.unpack(">IIBB", body[:10])
+            assert bits == 8 and ctype == 2
+        elif tag == b"IDAT":
+            idat += body
+        pos += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + 3 * w)
+    assert (raw[:, 0] == 0).all()
+    return raw[:, 1:].reshape(h, w, 3)
+
+
+def test_png_and_pfm_writers(gpt, tmp_path):
+    rng = np.random.default_rng(0)
+    for w, h in [(7, 5), (301, 230)]:                                # second one needs several stored-deflate blocks
+        px = rng.integers(0, 1 << 24, size=(h, w), dtype=np.uint32)
+        p = str(tmp_path / ("t%d.png" % w))
+        gpt.write_png(p, px, w, h)
+        want = np.stack([px & 0xff, (px >> 8) & 0xff, (px >> 16) & 0xff], -1).astype(np.uint8)[::-1]    # 0x00BBGGRR, row 0 = bottom
+        np.testing.assert_array_equal(_png_pixels(p), want)
+        try:
+            from PIL import Image
+            np.testing.assert_array_equal(np.array(Image.open(p)), want)
+        except ImportError:
+            pass
+    rgb = rng.random((5, 7, 3)).astype(np.float32)
+    p = str(tmp_path / "t.pfm")
+    gpt.write_pfm(p, rgb, 7, 5)
+    blob = open(p, "rb").read()
+    assert blob.startswith(b"PF\n7 5\n-1.0\n")
+    np.testing.assert_array_equal(np.frombuffer(blob[len(b"PF\n7 5\n-1.0\n"):], np.float32).reshape(5, 7, 3), rgb)
