@@ -72,6 +72,10 @@ class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("rays_by_bounce", C.c_uint64 * 16), ("paths", C.c_uint64), ("kernel_launches", C.c_uint64)]
 
 
+class TriMaterial(C.Structure):  # gpt_tri_material (N4)
+    _fields_ = [("col", C.c_float * 3), ("emi", C.c_float * 3), ("mat", C.c_int32)]
+
+
 class BuiltBVH(C.Structure):  # gpt_built_bvh
     _fields_ = [("bvh", BVHData), ("n_inner_nodes", C.c_uint32), ("n_leaves", C.c_uint32), ("n_triangles", C.c_uint32),
                 ("depth", C.c_uint32), ("build_ms", C.c_float)]
@@ -89,7 +93,7 @@ EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string"
            "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
            "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
-           "gpt_load_obj", "gpt_free_host", "gpt_write_png", "gpt_write_pfm",
+           "gpt_set_triangle_materials", "gpt_load_obj", "gpt_load_obj_materials", "gpt_free_host", "gpt_write_png", "gpt_write_pfm", "gpt_save_accum", "gpt_load_accum",
            "gpt_hash64", "gpt_default_spheres", "gpt_default_kernel_info", "gpt_set_camera"]
 
 _lib = None
@@ -133,12 +137,18 @@ def load_library():
     L.gpt_default_kernel_info.restype = None
     L.gpt_set_camera.argtypes = [C.POINTER(CamInfo), C.c_void_p, C.c_float, C.c_float]
     L.gpt_set_camera.restype = None
+    L.gpt_set_triangle_materials.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.gpt_load_obj.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_size_t),
                                C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_size_t)]
+    L.gpt_load_obj_materials.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_size_t),
+                                         C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_size_t),
+                                         C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.POINTER(TriMaterial)), C.POINTER(C.c_size_t)]
     L.gpt_free_host.argtypes = [C.c_void_p]
     L.gpt_free_host.restype = None
     L.gpt_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
     L.gpt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+    L.gpt_save_accum.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64]
+    L.gpt_load_accum.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     _lib = L
     return L
 
@@ -202,6 +212,27 @@ def load_obj(path):
     return verts, faces
 
 
+def load_obj_materials(path):
+    """OBJ + .mtl -> (verts, faces, face_material int32 (m,), materials (TriMaterial * n))."""
+    L = load_library()
+    v, t, fm, mt = C.POINTER(C.c_float)(), C.POINTER(C.c_int32)(), C.POINTER(C.c_int32)(), C.POINTER(TriMaterial)()
+    nv, nt, nm = C.c_size_t(0), C.c_size_t(0), C.c_size_t(0)
+    rc = L.gpt_load_obj_materials(os.fsencode(path), C.byref(v), C.byref(nv), C.byref(t), C.byref(nt), C.byref(fm), C.byref(mt), C.byref(nm))
+    if rc != 0:
+        raise GptError("gpt_load_obj_materials(%s) failed (%d)" % (path, rc))
+    try:
+        verts = np.ctypeslib.as_array(v, shape=(nv.value * 3,)).copy().reshape(-1, 3) if nv.value else np.zeros((0, 3), np.float32)
+        faces = np.ctypeslib.as_array(t, shape=(nt.value * 3,)).copy().reshape(-1, 3) if nt.value else np.zeros((0, 3), np.int32)
+        face_mat = np.ctypeslib.as_array(fm, shape=(nt.value,)).copy() if nt.value else np.zeros((0,), np.int32)
+        mats = (TriMaterial * nm.value)()
+        if nm.value:
+            C.memmove(mats, mt, nm.value * C.sizeof(TriMaterial))
+    finally:
+        for q in (v, t, fm, mt):
+            L.gpt_free_host(q)
+    return verts, faces, face_mat, mats
+
+
 def write_png(path, rgba8, width, height):
     """rgba8: host uint32/int32 array of W*H 0x00BBGGRR pixels, row 0 = bottom (the dev_drawRes layout)."""
     a = np.ascontiguousarray(rgba8).view(np.uint32)
@@ -215,6 +246,24 @@ def write_pfm(path, rgb, width, height):
     rc = load_library().gpt_write_pfm(os.fsencode(path), a.ctypes.data, int(width), int(height))
     if rc != 0:
         raise GptError("gpt_write_pfm failed (%d)" % rc)
+
+
+def save_accum(path, accum_f4, samples_done, seed):
+    a = np.ascontiguousarray(accum_f4, dtype=np.float32)
+    h, w = a.shape[0], a.shape[1]
+    rc = load_library().gpt_save_accum(os.fsencode(path), a.ctypes.data, w, h, C.c_uint64(samples_done), C.c_uint64(seed))
+    if rc != 0:
+        raise GptError("gpt_save_accum failed (%d)" % rc)
+
+
+def load_accum(path, width, height):
+    """-> (accum (H,W,4) float32, samples_done, seed)"""
+    a = np.empty((height, width, 4), np.float32)
+    n, s = C.c_uint64(0), C.c_uint64(0)
+    rc = load_library().gpt_load_accum(os.fsencode(path), a.ctypes.data, int(width), int(height), C.byref(n), C.byref(s))
+    if rc != 0:
+        raise GptError("gpt_load_accum failed (%d)" % rc)
+    return a, n.value, s.value
 
 
 def _ptr(x):
@@ -345,6 +394,15 @@ class Context:
         self._ck(self._L.gpt_upload_scene(self._h, b.bvh.dev_triNode, b.bvh.triNodeSize, b.bvh.dev_triPtr, b.bvh.triSize,
                                           b.bvh.dev_triIndicesPtr, b.bvh.triIndicesSize, _ptr(spheres) if ns else None, ns,
                                           _ptr(boxes) if nb else None, nb, 1), "gpt_upload_scene")
+
+    def set_triangle_materials(self, materials, face_material):
+        """materials: (TriMaterial * n) array; face_material: int32 array indexed by OBJ face index (None clears)."""
+        if face_material is None:
+            self._ck(self._L.gpt_set_triangle_materials(self._h, None, 0, None, 0), "gpt_set_triangle_materials")
+            return
+        fm = np.ascontiguousarray(face_material, dtype=np.int32)
+        self._ck(self._L.gpt_set_triangle_materials(self._h, C.addressof(materials), len(materials), fm.ctypes.data, fm.size),
+                 "gpt_set_triangle_materials")
 
     def kernel_times(self):
         """{class name: (ms, launches)} since the last reset_stats (needs FLAG_TIME_KERNELS)."""

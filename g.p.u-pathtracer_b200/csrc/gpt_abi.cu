@@ -19,6 +19,7 @@ struct gpt_ctx {
     float4* nodes = nullptr; float4* tris = nullptr; int n_nodes = 0; int n_tris = 0;
     float* spheres = nullptr; int n_spheres = 0;
     float* boxes = nullptr; int n_boxes = 0;
+    float* tri_mats = nullptr; int* face_mat = nullptr; int n_tri_mats = 0, n_faces = 0;   // N4, survive scene re-uploads
     bool has_scene = false;
     // identity of the reference arrays the packed BVH was built from (gpt_launch re-packs on change)
     const void* src_nodes = nullptr; const void* src_tris = nullptr; const void* src_idx = nullptr;
@@ -125,6 +126,7 @@ void gpt_destroy(gpt_ctx* c)
     cudaDeviceSynchronize();
     free_scene(c);
     cudaFree(c->work_counter); cudaFree(c->stats); cudaFree(c->frame_accum); cudaFree(c->frame_rgba);
+    cudaFree(c->tri_mats); cudaFree(c->face_mat);
     free_wave(c);
     c->timer.release();
     delete c;
@@ -274,6 +276,24 @@ int gpt_copy_to_host(gpt_ctx* c, void* dst, const void* src, size_t bytes)
     return GPT_OK;
 }
 
+int gpt_set_triangle_materials(gpt_ctx* c, const gpt_tri_material* mats, size_t n_mats, const int32_t* face_material, size_t n_faces)
+{
+    if (!c) return GPT_ERR_INVALID;
+    if ((n_faces && (!mats || !face_material || n_mats == 0)) || n_mats > 0x7fffffffull || n_faces > 0x7fffffffull)
+        return fail(c, GPT_ERR_INVALID, "gpt_set_triangle_materials: bad arguments");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());
+    cudaFree(c->tri_mats); cudaFree(c->face_mat);
+    c->tri_mats = nullptr; c->face_mat = nullptr; c->n_tri_mats = 0; c->n_faces = 0;
+    if (n_faces == 0) return GPT_OK;
+    CU(c, cudaMalloc(&c->tri_mats, n_mats * sizeof(gpt_tri_material)));
+    CU(c, cudaMalloc(&c->face_mat, n_faces * sizeof(int32_t)));
+    CU(c, cudaMemcpy(c->tri_mats, mats, n_mats * sizeof(gpt_tri_material), cudaMemcpyDefault));
+    CU(c, cudaMemcpy(c->face_mat, face_material, n_faces * sizeof(int32_t), cudaMemcpyDefault));
+    c->n_tri_mats = (int)n_mats; c->n_faces = (int)n_faces;
+    return GPT_OK;
+}
+
 static int make_params(gpt_ctx* c, const gpt_kernel_info* info, uint64_t seed, RenderParams* p)
 {
     if (info->width < 2 || info->height < 2 || (long long)info->width * info->height > 0x7fffffffLL / 4)
@@ -300,6 +320,7 @@ static void uploaded_scene(const gpt_ctx* c, DevScene* sc)
     sc->nodes = c->nodes; sc->tris = c->tris; sc->n_nodes = c->n_nodes; sc->n_tris = c->n_tris;
     sc->spheres = c->spheres; sc->n_spheres = c->n_spheres;
     sc->boxes = c->boxes; sc->n_boxes = c->n_boxes;
+    sc->tri_mats = c->tri_mats; sc->face_mat = c->face_mat; sc->n_tri_mats = c->n_tri_mats; sc->n_faces = c->n_faces;
 }
 
 // scene for a launch: pointers carried by kernelInfo win (drop-in use), else the uploaded scene

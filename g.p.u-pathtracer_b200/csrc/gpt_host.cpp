@@ -153,7 +153,8 @@ extern "C" {
 // uf::loadIndexedTris (utilfun.cpp:454-524): every `v` in file order, per face the 0-based vertex index of each
 // corner, polygons fan-triangulated (v0, v[k], v[k+1]) like tinyobjloader; normals / uvs / materials dropped
 // (SURVEY F5).  Unlike the reference (assert(shapes.size()==1), :474) several o/g shapes are merged into one mesh.
-int gpt_load_obj(const char* path, float** verts_out, size_t* n_verts, int32_t** tris_out, size_t* n_tris)
+static int load_obj_impl(const char* path, float** verts_out, size_t* n_verts, int32_t** tris_out, size_t* n_tris,
+                         std::vector<int32_t>* face_mat, std::vector<std::string>* mat_names, std::string* mtllib)
 {
     if (!path || !verts_out || !n_verts || !tris_out || !n_tris) return GPT_ERR_INVALID;
     *verts_out = nullptr; *tris_out = nullptr; *n_verts = 0; *n_tris = 0;
@@ -161,6 +162,7 @@ int gpt_load_obj(const char* path, float** verts_out, size_t* n_verts, int32_t**
     if (!f) return GPT_ERR_IO;
     std::vector<float> v;
     std::vector<int32_t> t;
+    int32_t cur_mat = -1;
     std::vector<long long> corner;
     std::string line;
     char buf[4096];
@@ -191,7 +193,22 @@ int gpt_load_obj(const char* path, float** verts_out, size_t* n_verts, int32_t**
                 if (idx < 0 || idx >= nv) { bad = true; break; }
                 corner.push_back(idx);
             }
-            for (size_t k = 1; k + 1 < corner.size(); ++k) { t.push_back((int32_t)corner[0]); t.push_back((int32_t)corner[k]); t.push_back((int32_t)corner[k + 1]); }
+            for (size_t k = 1; k + 1 < corner.size(); ++k) {
+                t.push_back((int32_t)corner[0]); t.push_back((int32_t)corner[k]); t.push_back((int32_t)corner[k + 1]);
+                if (face_mat) face_mat->push_back(cur_mat);
+            }
+        } else if (mat_names && (strncmp(p, "usemtl", 6) == 0 || strncmp(p, "mtllib", 6) == 0) && (p[6] == ' ' || p[6] == '\t')) {
+            const bool lib = p[0] == 'm';
+            p += 7;
+            while (*p == ' ' || *p == '\t') ++p;
+            std::string name(p);
+            while (!name.empty() && (name.back() == '\n' || name.back() == '\r' || name.back() == ' ' || name.back() == '\t')) name.pop_back();
+            if (lib) { if (mtllib) *mtllib = name; }
+            else {
+                cur_mat = -1;
+                for (size_t k = 0; k < mat_names->size(); ++k) if ((*mat_names)[k] == name) cur_mat = (int32_t)k;
+                if (cur_mat < 0) { mat_names->push_back(name); cur_mat = (int32_t)mat_names->size() - 1; }
+            }
         }
         if (bad) break;
     }
@@ -203,6 +220,65 @@ int gpt_load_obj(const char* path, float** verts_out, size_t* n_verts, int32_t**
     if (!v.empty()) memcpy(vo, v.data(), v.size() * sizeof(float));
     if (!t.empty()) memcpy(to, t.data(), t.size() * sizeof(int32_t));
     *verts_out = vo; *n_verts = v.size() / 3; *tris_out = to; *n_tris = t.size() / 3;
+    return GPT_OK;
+}
+
+int gpt_load_obj(const char* path, float** verts_out, size_t* n_verts, int32_t** tris_out, size_t* n_tris)
+{
+    return load_obj_impl(path, verts_out, n_verts, tris_out, n_tris, nullptr, nullptr, nullptr);
+}
+
+// OBJ + its .mtl (what tinyobj parses and the reference then drops, utilfun.cpp:457-497): per
+// triangle the index of its `usemtl` material (-1 = none), and one gpt_tri_material per material name:
+// col = Kd, emi = Ke, Mat from illum (0-2 DIFF, 3 METAL, 5 SPEC mirror, 4/6/7/9 REFR glass).  Materials used in the
+// OBJ but missing from the .mtl (or no mtllib at all) get the reference's default triangle colour
+// (BasicScene.cpp:234-236) and DIFF.
+int gpt_load_obj_materials(const char* path, float** verts_out, size_t* n_verts, int32_t** tris_out, size_t* n_tris,
+                           int32_t** face_material_out, gpt_tri_material** materials_out, size_t* n_materials)
+{
+    if (!face_material_out || !materials_out || !n_materials) return GPT_ERR_INVALID;
+    *face_material_out = nullptr; *materials_out = nullptr; *n_materials = 0;
+    std::vector<int32_t> face_mat; std::vector<std::string> names; std::string mtllib;
+    int rc = load_obj_impl(path, verts_out, n_verts, tris_out, n_tris, &face_mat, &names, &mtllib);
+    if (rc != GPT_OK) return rc;
+    std::vector<gpt_tri_material> mats(names.size());
+    for (gpt_tri_material& m : mats) { m.col[0] = 246.0f / 256.0f; m.col[1] = 246.0f / 255.0f; m.col[2] = 70.0f / 255.0f; m.emi[0] = m.emi[1] = m.emi[2] = 0.0f; m.mat = GPT_MAT_DIFF; }
+    if (!mtllib.empty()) {
+        std::string dir(path);
+        const size_t slash = dir.find_last_of('/');
+        dir = slash == std::string::npos ? std::string() : dir.substr(0, slash + 1);
+        FILE* f = fopen((dir + mtllib).c_str(), "rb");
+        if (f) {
+            char buf[1024];
+            int cur = -1;
+            while (fgets(buf, sizeof(buf), f)) {
+                const char* p = buf;
+                while (*p == ' ' || *p == '\t') ++p;
+                if (strncmp(p, "newmtl", 6) == 0 && (p[6] == ' ' || p[6] == '\t')) {
+                    p += 7; while (*p == ' ' || *p == '\t') ++p;
+                    std::string name(p);
+                    while (!name.empty() && (name.back() == '\n' || name.back() == '\r' || name.back() == ' ' || name.back() == '\t')) name.pop_back();
+                    cur = -1;
+                    for (size_t k = 0; k < names.size(); ++k) if (names[k] == name) cur = (int)k;
+                } else if (cur >= 0 && p[0] == 'K' && (p[1] == 'd' || p[1] == 'e') && (p[2] == ' ' || p[2] == '\t')) {
+                    float* dst = p[1] == 'd' ? mats[cur].col : mats[cur].emi;
+                    p += 3;
+                    float x[3];
+                    if (next_float(p, &x[0]) && next_float(p, &x[1]) && next_float(p, &x[2])) { dst[0] = x[0]; dst[1] = x[1]; dst[2] = x[2]; }
+                } else if (cur >= 0 && strncmp(p, "illum", 5) == 0) {
+                    const int il = atoi(p + 5);
+                    mats[cur].mat = il == 3 ? GPT_MAT_METAL : il == 5 ? GPT_MAT_SPEC : (il == 4 || il == 6 || il == 7 || il == 9) ? GPT_MAT_REFR : GPT_MAT_DIFF;
+                }
+            }
+            fclose(f);
+        }
+    }
+    int32_t* fm = (int32_t*)malloc(face_mat.size() * sizeof(int32_t) + 4);
+    gpt_tri_material* mo = (gpt_tri_material*)malloc(mats.size() * sizeof(gpt_tri_material) + 4);
+    if (!fm || !mo) { free(fm); free(mo); free(*verts_out); free(*tris_out); *verts_out = nullptr; *tris_out = nullptr; return GPT_ERR_INVALID; }
+    if (!face_mat.empty()) memcpy(fm, face_mat.data(), face_mat.size() * sizeof(int32_t));
+    if (!mats.empty()) memcpy(mo, mats.data(), mats.size() * sizeof(gpt_tri_material));
+    *face_material_out = fm; *materials_out = mo; *n_materials = mats.size();
     return GPT_OK;
 }
 
@@ -267,6 +343,39 @@ int gpt_write_pfm(const char* path, const float* rgb, int width, int height)
     ok = ok && fwrite(rgb, sizeof(float), n, f) == n;
     ok = (fclose(f) == 0) && ok;
     return ok ? GPT_OK : GPT_ERR_IO;
+}
+
+// Accumulation checkpoint / resume: the reference keeps accumBuffer + constantPdf in process memory
+// only (BasicScene.cpp:399).  File = "GPTACC1\0", int32 width, height, uint64 samples done, uint64 seed, then W*H
+// float4 (sum r, g, b, sample count) as gpt_render accumulates them.
+int gpt_save_accum(const char* path, const float* accum_f4, int width, int height, uint64_t samples_done, uint64_t seed)
+{
+    if (!path || !accum_f4 || width <= 0 || height <= 0) return GPT_ERR_INVALID;
+    FILE* f = fopen(path, "wb");
+    if (!f) return GPT_ERR_IO;
+    const int32_t wh[2] = {width, height};
+    const uint64_t meta[2] = {samples_done, seed};
+    const size_t n = 4 * (size_t)width * (size_t)height;
+    bool ok = fwrite("GPTACC1", 1, 8, f) == 8 && fwrite(wh, 4, 2, f) == 2 && fwrite(meta, 8, 2, f) == 2 && fwrite(accum_f4, sizeof(float), n, f) == n;
+    ok = (fclose(f) == 0) && ok;
+    return ok ? GPT_OK : GPT_ERR_IO;
+}
+
+int gpt_load_accum(const char* path, float* accum_f4, int width, int height, uint64_t* samples_done, uint64_t* seed)
+{
+    if (!path || !accum_f4 || width <= 0 || height <= 0) return GPT_ERR_INVALID;
+    FILE* f = fopen(path, "rb");
+    if (!f) return GPT_ERR_IO;
+    char magic[8]; int32_t wh[2]; uint64_t meta[2];
+    const size_t n = 4 * (size_t)width * (size_t)height;
+    bool ok = fread(magic, 1, 8, f) == 8 && memcmp(magic, "GPTACC1", 8) == 0 && fread(wh, 4, 2, f) == 2 && fread(meta, 8, 2, f) == 2;
+    if (ok && (wh[0] != width || wh[1] != height)) { fclose(f); return GPT_ERR_INVALID; }
+    ok = ok && fread(accum_f4, sizeof(float), n, f) == n;
+    fclose(f);
+    if (!ok) return GPT_ERR_IO;
+    if (samples_done) *samples_done = meta[0];
+    if (seed) *seed = meta[1];
+    return GPT_OK;
 }
 
 } // extern "C"

@@ -34,6 +34,11 @@ struct DevScene {
     int n_tris;
     int n_spheres;
     int n_boxes;
+    // N4: per-face materials (nullptr / 0 = the reference's single global triangle material, tracer.cu:131-135)
+    const float* tri_mats;   // n_tri_mats * 7 floats: col rgb, emi rgb, bits(Mat)
+    const int*   face_mat;   // n_faces entries, indexed by the remapped OBJ face index (cudaUtils.h:452-456)
+    int n_tri_mats;
+    int n_faces;
 };
 
 // the kernelInfo fields the device code reads (CpuStructs.hpp:45-72), flattened

@@ -78,6 +78,17 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         n = normalize3(cross3(mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z)));
         nl = n;                                                          // Q4: not face-forwarded
         emit = ld3(p.emi); objcol = ld3(p.col); mat = p.tri_mat;
+        if (sc.n_faces) {                                                // N4: per-face material table
+            const int face = __float_as_int(__ldg(sc.tris + 3 * h.prim).w);
+            if ((unsigned)face < (unsigned)sc.n_faces) {
+                const int m = __ldg(sc.face_mat + face);
+                if ((unsigned)m < (unsigned)sc.n_tri_mats) {
+                    const float* tm = sc.tri_mats + 7 * (size_t)m;
+                    objcol = mk3(__ldg(tm), __ldg(tm + 1), __ldg(tm + 2)); emit = mk3(__ldg(tm + 3), __ldg(tm + 4), __ldg(tm + 5));
+                    mat = __float_as_int(__ldg(tm + 6));
+                }
+            }
+        }
     } else {                                                             // BOX (commented branch :143-152)
         const float* bx = s_boxes + 13 * h.prim;
         n = box_normal(bx, hitpos);

@@ -10,7 +10,7 @@
 //
 //   gpt_headless --obj scene.obj [--width 1280 --height 720 --spp 64 --depth 4 --mat diff|metal|spec|refr]
 //                [--col r g b --emi r g b --bk r g b --phong 30 --air 1.0 --glass 1.4 --no-cull]
-//                [--cam x y z yaw pitch] [--seed 0] [--legacy] [--frames-per-pass 16] [--png out.png] [--pfm out.pfm]
+//                [--cam x y z yaw pitch] [--dist d] [--seed 0] [--mtl] [--checkpoint f] [--resume f] [--legacy] [--frames-per-pass 16] [--png out.png] [--pfm out.pfm]
 #include "../../include/gpt.h"
 #include <chrono>
 #include <cstdio>
@@ -30,14 +30,15 @@ static int die(gpt_ctx* ctx, const char* what, int rc)
 
 int main(int argc, char** argv)
 {
-    std::string obj, png = "render.png", pfm;
+    std::string obj, png = "render.png", pfm, checkpoint, resume;
+    bool use_mtl = false;
     int width = 1280, height = 720, device = 0;              // App/main.cpp:12
     unsigned spp = 16, depth = 4, per_pass = 16;
     unsigned long long seed = 0;
     int mat = GPT_MAT_DIFF, cull = 1;
     float col[3] = {246.0f / 256.0f, 246.0f / 255.0f, 70.0f / 255.0f}, emi[3] = {0, 0, 0}, bk[3] = {1, 1, 1};   // BasicScene.cpp:230-236
     float phong = 30.0f, air = 1.0f, glass = 1.4f;
-    float cam_pos[3] = {0, 0, 0}, yaw = 0.0f, pitch = 0.0f;
+    float cam_pos[3] = {0, 0, 0}, yaw = 0.0f, pitch = 0.0f, dist = -1.0f;
     bool have_cam = false;
     auto need = [&](int i, int n) { if (i + n >= argc) { fprintf(stderr, "gpt_headless: %s needs %d value(s)\n", argv[i], n); exit(2); } };
     for (int i = 1; i < argc; ++i) {
@@ -45,6 +46,9 @@ int main(int argc, char** argv)
         if (a == "--obj") { need(i, 1); obj = argv[++i]; }
         else if (a == "--png") { need(i, 1); png = argv[++i]; }
         else if (a == "--pfm") { need(i, 1); pfm = argv[++i]; }
+        else if (a == "--checkpoint") { need(i, 1); checkpoint = argv[++i]; }   // write float4 sums + sample count at the end
+        else if (a == "--resume") { need(i, 1); resume = argv[++i]; }           // continue a checkpoint (same size and seed)
+        else if (a == "--mtl") use_mtl = true;                                  // per-triangle materials from the OBJ's mtllib (N4)
         else if (a == "--width") { need(i, 1); width = atoi(argv[++i]); }
         else if (a == "--height") { need(i, 1); height = atoi(argv[++i]); }
         else if (a == "--device") { need(i, 1); device = atoi(argv[++i]); }
@@ -55,6 +59,7 @@ int main(int argc, char** argv)
         else if (a == "--phong") { need(i, 1); phong = (float)atof(argv[++i]); }
         else if (a == "--air") { need(i, 1); air = (float)atof(argv[++i]); }
         else if (a == "--glass") { need(i, 1); glass = (float)atof(argv[++i]); }
+        else if (a == "--dist") { need(i, 1); dist = (float)atof(argv[++i]); }     // cam.dist; default height/60 (INT division, BasicScene.cpp:241)
         else if (a == "--no-cull") cull = 0;
         else if (a == "--mat") {
             need(i, 1); const std::string m = argv[++i];
@@ -82,17 +87,26 @@ int main(int argc, char** argv)
     info.phongExpo = phong; info.air_ref_index = air; info.glass_ref_index = glass;
     for (int k = 0; k < 3; ++k) { info.col[k] = col[k]; info.emi[k] = emi[k]; info.bkColor[k] = bk[k]; }
     if (have_cam) gpt_set_camera(&info.cam, cam_pos, yaw, pitch);
+    if (dist > 0.0f) info.cam.dist = dist;
 
     gpt_built_bvh bvh; memset(&bvh, 0, sizeof(bvh));
     if (!obj.empty()) {
         float* verts = nullptr; int32_t* tris = nullptr; size_t nv = 0, nt = 0;
+        int32_t* face_mat = nullptr; gpt_tri_material* mats = nullptr; size_t n_mats = 0;
         const auto t0 = std::chrono::steady_clock::now();
-        rc = gpt_load_obj(obj.c_str(), &verts, &nv, &tris, &nt);
+        rc = use_mtl ? gpt_load_obj_materials(obj.c_str(), &verts, &nv, &tris, &nt, &face_mat, &mats, &n_mats)
+                     : gpt_load_obj(obj.c_str(), &verts, &nv, &tris, &nt);
         if (rc) { fprintf(stderr, "gpt_headless: cannot read %s\n", obj.c_str()); gpt_destroy(ctx); return 1; }
         const double load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         rc = gpt_build_bvh(ctx, verts, nv, tris, nt, 0, 8, &bvh);
         gpt_free_host(verts); gpt_free_host(tris);
         if (rc) return die(ctx, "gpt_build_bvh", rc);
+        if (use_mtl && n_mats) {
+            rc = gpt_set_triangle_materials(ctx, mats, n_mats, face_mat, nt);
+            if (rc) return die(ctx, "gpt_set_triangle_materials", rc);
+            printf("materials: %zu from the mtllib\n", n_mats);
+        }
+        gpt_free_host(face_mat); gpt_free_host(mats);
         printf("mesh: %zu vertices, %zu triangles (OBJ read %.2f s); BVH: %u inner nodes, %u leaves, depth %u, built on the device in %.2f ms\n",
                nv, nt, load_s, bvh.n_inner_nodes, bvh.n_leaves, bvh.depth, bvh.build_ms);
         rc = gpt_upload_scene(ctx, bvh.bvh.dev_triNode, bvh.bvh.triNodeSize, bvh.bvh.dev_triPtr, bvh.bvh.triSize,
@@ -106,8 +120,16 @@ int main(int argc, char** argv)
     //      indices [done, done+n) into the library's float4 sum and returns the resolved frame to the host ----
     std::vector<uint32_t> rgba((size_t)width * height);
     std::vector<float> accum((size_t)width * height * 4), sum((size_t)width * height * 4, 0.0f);
-    const auto t0 = std::chrono::steady_clock::now();
     unsigned done = 0;
+    if (!resume.empty()) {
+        uint64_t n0 = 0, s0 = 0;
+        rc = gpt_load_accum(resume.c_str(), sum.data(), width, height, &n0, &s0);
+        if (rc || s0 != seed) { fprintf(stderr, "gpt_headless: cannot resume from %s (rc %d; size or seed mismatch?)\n", resume.c_str(), rc); gpt_destroy(ctx); return 1; }
+        done = (unsigned)n0;
+        spp += done;                      // --spp counts the samples to ADD; global indices continue at `done`
+        printf("resumed %s at %u samples\n", resume.c_str(), done);
+    }
+    const auto t0 = std::chrono::steady_clock::now();
     while (done < spp) {
         const unsigned n = spp - done < per_pass ? spp - done : per_pass;
         rc = gpt_render_frame_host(ctx, &info, seed, done, n, rgba.data(), accum.data());
@@ -120,6 +142,11 @@ int main(int argc, char** argv)
     printf("%ux%u, %u spp, depth %u: %.3f s, %.1f Mrays/s (%llu rays, %llu kernel launches)\n", width, height, spp, depth, secs,
            (double)st.rays / secs / 1e6, (unsigned long long)st.rays, (unsigned long long)st.kernel_launches);
 
+    if (!checkpoint.empty()) {
+        rc = gpt_save_accum(checkpoint.c_str(), sum.data(), width, height, spp, seed);
+        if (rc) { fprintf(stderr, "gpt_headless: cannot write %s\n", checkpoint.c_str()); gpt_destroy(ctx); return 1; }
+        printf("wrote %s (%u samples)\n", checkpoint.c_str(), spp);
+    }
     // ---- resolve on the host from the summed float4 buffer: mean, clamp, pack (tracer.cu:386-398 semantics) ----
     std::vector<float> rgb((size_t)width * height * 3);
     for (size_t i = 0; i < (size_t)width * height; ++i) {

@@ -137,6 +137,16 @@ GPT_API int gpt_upload_scene(gpt_ctx* ctx,
                              const gpt_box* boxes, size_t n_boxes,
                              int on_device);
 
+/* ---- per-triangle materials ----
+ * The reference shades every triangle with ONE global material (info.col / emi / triCurrentMat, tracer.cu:131-135;
+ * tinyobj's .mtl data is dropped, utilfun.cpp:457-497).  With a table set, a triangle hit takes colour, emission
+ * and Mat from materials[face_material[f]], f = the original OBJ face index the reference's index array maps the
+ * hit to (gpuTriIndices[hitIndex], cudaUtils.h:452-456); faces outside the table keep the global material.
+ * Host or device pointers; copied.  n_faces = 0 restores the reference behaviour. */
+typedef struct { float col[3]; float emi[3]; int32_t mat; } gpt_tri_material;   /* 28 B */
+GPT_API int gpt_set_triangle_materials(gpt_ctx* ctx, const gpt_tri_material* materials, size_t n_materials,
+                                       const int32_t* face_material, size_t n_faces);
+
 /* ---- device-side BVH builder ----
  * Replaces, for scenes where the single-threaded host build is the bottleneck (2.9 s per 100 k triangles), the
  * pipeline  BVH myBVH(&scene, Platform(), BuildParams()); new CudaBVH(myBVH, BVHLayout_Compact)  of
@@ -206,10 +216,19 @@ GPT_API void gpt_set_camera(gpt_cam_info* cam, const float pos[3], float yaw_deg
  * materials dropped); several shapes are merged (the reference asserts exactly one, :474).  The arrays are
  * malloc'd by the library; release with gpt_free_host. */
 GPT_API int  gpt_load_obj(const char* path, float** verts, size_t* n_verts, int32_t** tris, size_t* n_tris);
+/* OBJ plus its mtllib: additionally one material index per triangle (usemtl; -1 = none) and one
+ * gpt_tri_material per material name (col = Kd, emi = Ke, Mat from illum: 0-2 DIFF, 3 METAL, 5 SPEC, 4/6/7/9 REFR),
+ * ready for gpt_set_triangle_materials.  All four arrays are released with gpt_free_host. */
+GPT_API int  gpt_load_obj_materials(const char* path, float** verts, size_t* n_verts, int32_t** tris, size_t* n_tris,
+                                    int32_t** face_material, gpt_tri_material** materials, size_t* n_materials);
 GPT_API void gpt_free_host(void* p);
 /* RGBA8 frame as dev_drawRes holds it (0x00BBGGRR, row 0 = bottom; copied to the host by the caller) -> PNG, top
  * row first: replaces the GL texture blit + quad (BasicScene.cpp:424-432,468; renderer.cpp:224-245). */
 GPT_API int  gpt_write_png(const char* path, const uint32_t* host_rgba8, int width, int height);
+/* accumulation checkpoint / resume: host float4 sums + samples done + seed; because sample indices
+ * are global, rendering [0,a) , saving, loading and rendering [a,b) equals rendering [0,b) in one go */
+GPT_API int  gpt_save_accum(const char* path, const float* host_accum_f4, int width, int height, uint64_t samples_done, uint64_t seed);
+GPT_API int  gpt_load_accum(const char* path, float* host_accum_f4, int width, int height, uint64_t* samples_done, uint64_t* seed);
 /* linear float RGB (gpt_resolve's out_rgb_f32, copied to the host) -> PFM, bottom row first */
 GPT_API int  gpt_write_pfm(const char* path, const float* host_rgb, int width, int height);
 
@@ -220,6 +239,7 @@ GPT_API int  gpt_write_pfm(const char* path, const float* host_rgb, int width, i
 #ifdef __cplusplus
 #include <cstddef>
 static_assert(sizeof(gpt_sphere) == 44, "Sphere ABI");
+static_assert(sizeof(gpt_tri_material) == 28, "gpt_tri_material");
 static_assert(sizeof(gpt_box) == 52, "Box ABI");
 static_assert(sizeof(gpt_cam_info) == 84, "CamInfo ABI");
 static_assert(sizeof(gpt_bvh_data) == 48, "BVHData ABI");

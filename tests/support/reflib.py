@@ -32,7 +32,9 @@ class OrcScene(C.Structure):
                 ("tris", C.c_void_p), ("n_tri_vec4", C.c_size_t),
                 ("indices", C.c_void_p), ("n_indices", C.c_size_t),
                 ("spheres", C.c_void_p), ("n_spheres", C.c_size_t),
-                ("boxes", C.c_void_p), ("n_boxes", C.c_size_t)]
+                ("boxes", C.c_void_p), ("n_boxes", C.c_size_t),
+                ("tri_materials", C.c_void_p), ("n_tri_materials", C.c_size_t),
+                ("face_material", C.c_void_p), ("n_faces", C.c_size_t)]
 
 
 class OrcParams(C.Structure):

@@ -211,7 +211,7 @@ def test_headless_cli_renders_an_obj_like_the_library(gpt, torch_cuda, tmp_path)
     W, H, SPP = 160, 90, 12
     png, pfm = str(tmp_path / "o.png"), str(tmp_path / "o.pfm")
     out = subprocess.run([exe, "--obj", obj, "--width", str(W), "--height", str(H), "--spp", str(SPP), "--frames-per-pass", "5", "--depth", "5",
-                          "--mat", "spec", "--seed", "3", "--png", png, "--pfm", pfm], capture_output=True, text=True, timeout=300)
+                          "--mat", "spec", "--seed", "3", "--dist", "1.5", "--png", png, "--pfm", pfm], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "built on the device" in out.stdout
     blob = open(pfm, "rb").read()
@@ -220,6 +220,7 @@ def test_headless_cli_renders_an_obj_like_the_library(gpt, torch_cuda, tmp_path)
     v, f = gpt.load_obj(obj)
     info = gpt.default_kernel_info(W, H)
     info.depth, info.triCurrentMat = 5, gpt.SPEC
+    info.cam.dist = 1.5
     with gpt.Context(0) as ctx:
         b = ctx.build_bvh(v, f)
         ctx.upload_built(b, gpt.default_spheres())
@@ -236,3 +237,43 @@ def test_headless_cli_renders_an_obj_like_the_library(gpt, torch_cuda, tmp_path)
     im = np.array(Image.open(png))
     pack = (np.float32(255.0) * np.clip(want, 0, 1)).astype(np.int32).astype(np.uint8)[::-1]
     np.testing.assert_array_equal(im, pack)
+
+
+def test_headless_cli_checkpoint_resume_and_mtl(gpt, torch_cuda, tmp_path):
+    """N4: 6 spp + checkpoint, then resume + 6 spp == 12 spp in one go (global sample indices continue); --mtl takes
+    per-triangle materials from the OBJ's mtllib."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(gpt.LIB_PATH), "gpt_headless")
+    sc = scenes.load_scene("cornell")
+    obj = tmp_path / "c.obj"
+    lines = ["mtllib c.mtl"] + ["v %.9g %.9g %.9g" % tuple(v) for v in sc["verts"]]
+    for i, f in enumerate(sc["faces"]):
+        lines.append("usemtl %s" % ("lamp" if i % 5 == 0 else "wall"))
+        lines.append("f %d %d %d" % (f[0] + 1, f[1] + 1, f[2] + 1))
+    obj.write_text("\n".join(lines) + "\n")
+    (tmp_path / "c.mtl").write_text("newmtl wall\nKd 0.2 0.7 0.3\nillum 2\nnewmtl lamp\nKd 1 1 1\nKe 2 2 2\nillum 2\n")
+
+    def run(*extra):
+        out = subprocess.run([exe, "--obj", str(obj), "--width", "96", "--height", "54", "--frames-per-pass", "6", "--depth", "4", "--seed", "9", "--dist", "0.9",
+                              "--png", str(tmp_path / "x.png")] + list(extra), capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stdout + out.stderr
+        return out.stdout
+
+    def pfm(path):
+        blob = open(path, "rb").read()
+        return np.frombuffer(blob[len(b"PF\n96 54\n-1.0\n"):], np.float32).reshape(54, 96, 3)
+    run("--spp", "12", "--pfm", str(tmp_path / "full.pfm"))
+    run("--spp", "6", "--checkpoint", str(tmp_path / "half.acc"))
+    assert "resumed" in run("--spp", "6", "--resume", str(tmp_path / "half.acc"), "--pfm", str(tmp_path / "two.pfm"))
+    np.testing.assert_array_equal(pfm(tmp_path / "two.pfm"), pfm(tmp_path / "full.pfm"))
+    assert "materials: 2" in run("--spp", "12", "--mtl", "--pfm", str(tmp_path / "mtl.pfm"))
+    a, b = pfm(tmp_path / "mtl.pfm"), pfm(tmp_path / "full.pfm")
+    assert np.mean(np.any(a != b, axis=-1)) > 0.2
+    # the same materials through the library + oracle (reference-built tree: the radiance of a pixel does not depend on the tree except on exact t ties)
+    v, f, fm, mats = gpt.load_obj_materials(str(obj))
+    info = gpt.default_kernel_info(96, 54)
+    info.depth = 4
+    info.cam.dist = 0.9
+    want = scenes.oracle_render(sc, gpt.default_spheres(), info, 9, 0, 12, tri_materials=mats, face_material=fm)
+    mean = want[..., :3] / want[..., 3:4]
+    assert np.mean(np.any(np.abs(a - mean) > 1e-5, axis=-1)) <= 5e-3

@@ -429,3 +429,33 @@ def test_both_pipelines_legacy_launch(gpt, torch_cuda):
         outs.append((acc.cpu().numpy().copy(), draw.cpu().numpy().copy()))
     np.testing.assert_array_equal(outs[0][0], outs[1][0])
     np.testing.assert_array_equal(outs[0][1], outs[1][1])
+
+
+def test_per_triangle_materials_match_oracle(gpt, torch_cuda):
+    """N4: a material table indexed by the remapped OBJ face index replaces the single global triangle material
+    (tracer.cu:131-135); faces outside the table and a cleared table fall back to info.col/emi/triCurrentMat."""
+    torch = torch_cuda
+    sc = scenes.load_scene("bunny_cornell")
+    n_faces = len(sc["faces"])
+    mats = (gpt.TriMaterial * 5)()
+    for m, (col, emi, mat) in zip(mats, [((0.8, 0.2, 0.2), (0, 0, 0), gpt.DIFF), ((1, 1, 1), (3, 3, 2.5), gpt.DIFF), ((0.9, 0.9, 0.9), (0, 0, 0), gpt.SPEC),
+                                         ((0.7, 0.8, 0.9), (0, 0, 0), gpt.METAL), ((1, 1, 1), (0, 0, 0), gpt.REFR)]):
+        m.col[:] = col; m.emi[:] = emi; m.mat = mat
+    rng = np.random.default_rng(4)
+    face_mat = rng.integers(0, 5, n_faces).astype(np.int32)
+    face_mat[::7] = -1                                              # "no usemtl": global material
+    face_mat = face_mat[: n_faces - 100]                            # table shorter than the mesh: tail uses the global material
+    sph = gpt.default_spheres()
+    info = small_info(gpt, 160, 90, depth=7)
+    info.triCurrentMat = gpt.DIFF
+    for flags in (0, gpt.FLAG_MEGAKERNEL):
+        with gpt.Context(0, flags) as ctx:
+            ctx.upload_scene(sc["nodes"], sc["tris"], sc["indices"], sph)
+            ctx.set_triangle_materials(mats, face_mat)
+            got = gpu_render(torch, ctx, info, 21, 0, 3)
+            want = scenes.oracle_render(sc, sph, info, 21, 0, 3, tri_materials=mats, face_material=face_mat)
+            assert_radiance_close(got[..., :3], want[..., :3])
+            plain = scenes.oracle_render(sc, sph, info, 21, 0, 3)
+            assert np.mean(np.any(want != plain, axis=-1)) > 0.2    # the table really changes the image
+            ctx.set_triangle_materials(None, None)
+            assert_radiance_close(gpu_render(torch, ctx, info, 21, 0, 3)[..., :3], plain[..., :3])

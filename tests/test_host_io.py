@@ -80,3 +80,29 @@ def test_png_and_pfm_writers(gpt, tmp_path):
     blob = open(p, "rb").read()
     assert blob.startswith(b"PF\n7 5\n-1.0\n")
     np.testing.assert_array_equal(np.frombuffer(blob[len(b"PF\n7 5\n-1.0\n"):], np.float32).reshape(5, 7, 3), rgb)
+
+
+def test_load_obj_with_mtl(gpt, tmp_path):
+    """N4: usemtl per face + Kd / Ke / illum from the .mtl the reference's loader parses and drops."""
+    (tmp_path / "m.mtl").write_text("newmtl red\nKd 0.8 0.1 0.1\nKe 0 0 0\nillum 2\n\nnewmtl lamp\nKd 1 1 1\nKe 4 4 3\nillum 2\n"
+                                    "newmtl mirror\nKd 0.9 0.9 0.9\nillum 5\nnewmtl glass\nillum 7\nnewmtl unused\nKd 0 0 0\n")
+    (tmp_path / "m.obj").write_text("mtllib m.mtl\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nf 1 2 3\nusemtl red\nf 1 2 3 4\nusemtl lamp\nf 1 3 4\n"
+                                    "usemtl mirror\nf 1 2 4\nusemtl glass\nf 2 3 4\nusemtl red\nf 1 2 3\nusemtl notinmtl\nf 1 2 3\n")
+    v, f, fm, mats = gpt.load_obj_materials(str(tmp_path / "m.obj"))
+    assert f.shape == (8, 3) and fm.tolist() == [-1, 0, 0, 1, 2, 3, 0, 4] and len(mats) == 5
+    assert np.allclose(list(mats[0].col), [0.8, 0.1, 0.1]) and mats[0].mat == gpt.DIFF
+    assert np.allclose(list(mats[1].emi), [4, 4, 3]) and mats[2].mat == gpt.SPEC and mats[3].mat == gpt.REFR
+    assert np.allclose(list(mats[4].col), [246 / 256, 246 / 255, 70 / 255]) and mats[4].mat == gpt.DIFF     # BasicScene.cpp:234-236 default
+
+
+def test_accum_checkpoint_roundtrip(gpt, tmp_path):
+    import pytest
+    rng = np.random.default_rng(1)
+    acc = rng.random((5, 7, 4)).astype(np.float32)
+    p = str(tmp_path / "a.gptacc")
+    gpt.save_accum(p, acc, 12345678901, 0xDEADBEEFCAFE)
+    back, n, seed = gpt.load_accum(p, 7, 5)
+    np.testing.assert_array_equal(back, acc)
+    assert n == 12345678901 and seed == 0xDEADBEEFCAFE
+    with pytest.raises(gpt.GptError):
+        gpt.load_accum(p, 8, 5)                                       # size mismatch is an error, not a reinterpretation
