@@ -359,15 +359,30 @@ def run_ours(args):
         e1.record(stream)
         k_events.append((e0, e1))
 
+    peer = None
+    if world > 1 and args.reduce == "peer":
+        peer = mg.PeerFrames(ctx, W, H, dist=dist, device=dev)
+
+    def render_ptr(ptr, begin, count):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        ctx.render(info, ptr, args.seed, begin, count, stream.cuda_stream)
+        e1.record(stream)
+        k_events.append((e0, e1))
+
     def step(i, e2e=False):
         flush.zero_()                                                  # L2 flush between timed iterations
         # weak scaling: every rank renders SPP samples of a SPP*world-sample progressive frame
-        mg.render_progressive_frame(render_fn, frame, total, i * SPP * world, SPP * world, dist=dist)
-        if rank == 0:
-            ctx.resolve(total, W, H, rgba, None, stream.cuda_stream)
-            if e2e:
-                host_rgba.copy_(rgba, non_blocking=True)
-                stream.synchronize()
+        if peer is not None:
+            # fused path: root P2P-reads the peers' frames inside ONE reduce + accumulate + resolve kernel
+            peer.frame(render_ptr, i * SPP * world, SPP * world, total, rgba if rank == 0 else None, None, stream.cuda_stream)
+        else:
+            mg.render_progressive_frame(render_fn, frame, total, i * SPP * world, SPP * world, dist=dist)
+            if rank == 0:
+                ctx.resolve(total, W, H, rgba, None, stream.cuda_stream)
+        if rank == 0 and e2e:
+            host_rgba.copy_(rgba, non_blocking=True)
+            stream.synchronize()
 
     def sync_all():
         torch.cuda.synchronize(dev)
@@ -456,7 +471,10 @@ def run_ours(args):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "scene": "Assets/cornell.obj + Assets/bunny_low.obj (5000 tris, reference SBVH) + 9 spheres",
                        "width": W, "height": H, "spp_per_gpu_per_step": SPP, "frame_spp": SPP * world, "depth": args.depth,
-                       "pipeline": args.pipeline, "collective": "1 NCCL reduce(float4 accum) per step" if world > 1 else "none",
+                       "pipeline": args.pipeline,
+                       "collective": "none" if world == 1 else ("none on the data path: root reads the peers' float4 frames over NVLink inside the fused "
+                                     "reduce+accumulate+resolve kernel (CUDA IPC); one 4-byte NCCL all_reduce per step as a stream-ordered barrier"
+                                     if peer is not None else "1 NCCL reduce(float4 accum) per step"),
                        "l2": "256 MiB buffer written between steps (L2 flush); scene itself (0.5 MB) is cache-resident by design",
                        "rays_per_step": total_rays / args.steps, "ms_per_frame_16spp": ms / args.steps},
             "e2e": {"value": e2e_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 296,
@@ -488,6 +506,8 @@ def run_ours(args):
             if rg is not None:
                 line["reference_gpu_kernel"] = rg
         emit_line(line)
+    if peer is not None:
+        peer.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -508,6 +528,7 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--pipeline", default="wavefront", choices=["mega", "wavefront"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"], help="multi-GPU frame reduce: fused P2P kernel (default) or torch.distributed.reduce")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

@@ -93,6 +93,8 @@ EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string"
            "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
            "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
+           "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
+           "gpt_reduce_resolve_ptrs", "gpt_frame_free",
            "gpt_set_triangle_materials", "gpt_load_obj", "gpt_load_obj_materials", "gpt_free_host", "gpt_write_png", "gpt_write_pfm", "gpt_save_accum", "gpt_load_accum",
            "gpt_hash64", "gpt_default_spheres", "gpt_default_kernel_info", "gpt_set_camera"]
 
@@ -137,6 +139,14 @@ def load_library():
     L.gpt_default_kernel_info.restype = None
     L.gpt_set_camera.argtypes = [C.POINTER(CamInfo), C.c_void_p, C.c_float, C.c_float]
     L.gpt_set_camera.restype = None
+    L.gpt_frame_alloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    L.gpt_frame_open_peers.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    L.gpt_frame_ptr.argtypes = [C.c_void_p, C.c_int]
+    L.gpt_frame_ptr.restype = C.c_void_p
+    L.gpt_frame_clear.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    L.gpt_reduce_resolve.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gpt_reduce_resolve_ptrs.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gpt_frame_free.argtypes = [C.c_void_p]
     L.gpt_set_triangle_materials.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.gpt_load_obj.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_size_t),
                                C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_size_t)]
@@ -394,6 +404,39 @@ class Context:
         self._ck(self._L.gpt_upload_scene(self._h, b.bvh.dev_triNode, b.bvh.triNodeSize, b.bvh.dev_triPtr, b.bvh.triSize,
                                           b.bvh.dev_triIndicesPtr, b.bvh.triIndicesSize, _ptr(spheres) if ns else None, ns,
                                           _ptr(boxes) if nb else None, nb, 1), "gpt_upload_scene")
+
+    # ---- multi-GPU peer frames (gpt_frame_* / gpt_reduce_resolve) ----
+    def frame_alloc(self, width, height, n_buffers=2):
+        """-> 64-byte IPC handle (bytes) of this rank's frame allocation"""
+        h = (C.c_ubyte * 64)()
+        self._ck(self._L.gpt_frame_alloc(self._h, int(width), int(height), int(n_buffers), h), "gpt_frame_alloc")
+        return bytes(h)
+
+    def frame_open_peers(self, handles, rank):
+        """handles: list of 64-byte handles, one per rank (this rank's own entry is ignored)"""
+        blob = (C.c_ubyte * (64 * len(handles)))(*b"".join(handles))
+        self._ck(self._L.gpt_frame_open_peers(self._h, blob, len(handles), int(rank)), "gpt_frame_open_peers")
+
+    def frame_ptr(self, index):
+        p = self._L.gpt_frame_ptr(self._h, int(index))
+        if not p:
+            raise GptError("gpt_frame_ptr: no such frame buffer")
+        return p
+
+    def frame_clear(self, index, stream=None):
+        self._ck(self._L.gpt_frame_clear(self._h, int(index), _ptr(stream)), "gpt_frame_clear")
+
+    def reduce_resolve(self, index, total_accum_f4=None, out_rgba8=None, out_rgb_f32=None, stream=None):
+        self._ck(self._L.gpt_reduce_resolve(self._h, int(index), _ptr(total_accum_f4), _ptr(out_rgba8), _ptr(out_rgb_f32), _ptr(stream)),
+                 "gpt_reduce_resolve")
+
+    def reduce_resolve_ptrs(self, frames, width, height, total_accum_f4=None, out_rgba8=None, out_rgb_f32=None, stream=None):
+        arr = (C.c_void_p * len(frames))(*[_ptr(f) for f in frames])
+        self._ck(self._L.gpt_reduce_resolve_ptrs(self._h, arr, len(frames), int(width), int(height), _ptr(total_accum_f4), _ptr(out_rgba8),
+                                                 _ptr(out_rgb_f32), _ptr(stream)), "gpt_reduce_resolve_ptrs")
+
+    def frame_free(self):
+        self._ck(self._L.gpt_frame_free(self._h), "gpt_frame_free")
 
     def set_triangle_materials(self, materials, face_material):
         """materials: (TriMaterial * n) array; face_material: int32 array indexed by OBJ face index (None clears)."""

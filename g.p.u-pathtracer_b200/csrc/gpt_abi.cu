@@ -30,6 +30,9 @@ struct gpt_ctx {
     float4* frame_accum = nullptr; uint32_t* frame_rgba = nullptr; size_t frame_pixels = 0;
     WaveBuffers wave = {}; size_t wave_pixels = 0; size_t wave_counters = 0;   // wavefront scratch
     unsigned long long launches = 0;
+    // multi-GPU peer frames
+    float4* frames = nullptr; int frame_w = 0, frame_h = 0, frame_n = 0;
+    void* peer_base[16] = {}; int peer_world = 0, peer_rank = 0;
     KernelTimer timer; double kt_ms[KT_CLASSES] = {}; unsigned long long kt_n[KT_CLASSES] = {};
     std::string err;
 };
@@ -128,6 +131,7 @@ void gpt_destroy(gpt_ctx* c)
     cudaFree(c->work_counter); cudaFree(c->stats); cudaFree(c->frame_accum); cudaFree(c->frame_rgba);
     cudaFree(c->tri_mats); cudaFree(c->face_mat);
     free_wave(c);
+    gpt_frame_free(c);
     c->timer.release();
     delete c;
 }
@@ -469,6 +473,92 @@ int gpt_get_stats(gpt_ctx* c, gpt_stats* out)
     for (int i = 0; i < 16; ++i) out->rays_by_bounce[i] = h[2 + i];
     out->kernel_launches = c->launches;
     return GPT_OK;
+}
+
+int gpt_frame_free(gpt_ctx* c)
+{
+    if (!c) return GPT_ERR_INVALID;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (int r = 0; r < 16; ++r) { if (c->peer_base[r]) cudaIpcCloseMemHandle(c->peer_base[r]); c->peer_base[r] = nullptr; }
+    c->peer_world = 0;
+    cudaFree(c->frames); c->frames = nullptr; c->frame_w = c->frame_h = c->frame_n = 0;
+    return GPT_OK;
+}
+
+int gpt_frame_alloc(gpt_ctx* c, int width, int height, int n_buffers, gpt_ipc_mem_handle* handle_out)
+{
+    if (!c || width <= 0 || height <= 0 || n_buffers < 1 || n_buffers > 8) return GPT_ERR_INVALID;
+    gpt_frame_free(c);
+    CU(c, cudaSetDevice(c->device));
+    const size_t bytes = sizeof(float4) * (size_t)width * height * n_buffers;
+    CU(c, cudaMalloc(&c->frames, bytes));
+    CU(c, cudaMemset(c->frames, 0, bytes));
+    c->frame_w = width; c->frame_h = height; c->frame_n = n_buffers;
+    if (handle_out) {
+        static_assert(sizeof(cudaIpcMemHandle_t) == sizeof(gpt_ipc_mem_handle), "IPC handle size");
+        CU(c, cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle_out), c->frames));
+    }
+    return GPT_OK;
+}
+
+int gpt_frame_open_peers(gpt_ctx* c, const gpt_ipc_mem_handle* handles, int world, int rank)
+{
+    if (!c || !handles || world < 1 || world > 16 || rank < 0 || rank >= world) return GPT_ERR_INVALID;
+    if (!c->frames) return fail(c, GPT_ERR_INVALID, "gpt_frame_open_peers: call gpt_frame_alloc first");
+    CU(c, cudaSetDevice(c->device));
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) continue;
+        cudaIpcMemHandle_t h; memcpy(&h, handles + r, sizeof(h));
+        CU(c, cudaIpcOpenMemHandle(&c->peer_base[r], h, cudaIpcMemLazyEnablePeerAccess));
+    }
+    c->peer_world = world; c->peer_rank = rank;
+    return GPT_OK;
+}
+
+float* gpt_frame_ptr(gpt_ctx* c, int index)
+{
+    if (!c || !c->frames || index < 0 || index >= c->frame_n) return nullptr;
+    return reinterpret_cast<float*>(c->frames + (size_t)index * c->frame_w * c->frame_h);
+}
+
+int gpt_frame_clear(gpt_ctx* c, int index, gpt_stream stream)
+{
+    float* p = gpt_frame_ptr(c, index);
+    if (!p) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemsetAsync(p, 0, sizeof(float4) * (size_t)c->frame_w * c->frame_h, (cudaStream_t)stream));
+    return GPT_OK;
+}
+
+int gpt_reduce_resolve_ptrs(gpt_ctx* c, const float* const* frames, int n_frames, int width, int height,
+                            float* total, uint32_t* out_rgba8, float* out_rgb, gpt_stream stream)
+{
+    if (!c || !frames || n_frames < 1 || n_frames > 16 || width <= 0 || height <= 0) return GPT_ERR_INVALID;
+    for (int r = 0; r < n_frames; ++r) if (!frames[r]) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    KernelTimer* kt = (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr;
+    if (kt) kt->tick(KT_RESOLVE, (cudaStream_t)stream);
+    cudaError_t e = gptk_reduce_resolve(reinterpret_cast<const float4* const*>(frames), n_frames, width * height, reinterpret_cast<float4*>(total),
+                                        out_rgba8, out_rgb, c->sm_count, (cudaStream_t)stream);
+    if (kt) kt->tick(KT_END, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "reduce_resolve launch", e);
+    c->launches += 1;
+    return GPT_OK;
+}
+
+int gpt_reduce_resolve(gpt_ctx* c, int index, float* total, uint32_t* out_rgba8, float* out_rgb, gpt_stream stream)
+{
+    if (!c || !c->frames || index < 0 || index >= c->frame_n) return GPT_ERR_INVALID;
+    const int world = c->peer_world ? c->peer_world : 1;
+    const size_t off = (size_t)index * c->frame_w * c->frame_h;
+    const float* ptrs[16];
+    for (int r = 0; r < world; ++r) {
+        const float4* base = (world == 1 || r == c->peer_rank) ? c->frames : reinterpret_cast<const float4*>(c->peer_base[r]);
+        if (!base) return fail(c, GPT_ERR_INVALID, "gpt_reduce_resolve: peer not opened");
+        ptrs[r] = reinterpret_cast<const float*>(base + off);
+    }
+    return gpt_reduce_resolve_ptrs(c, ptrs, world, c->frame_w, c->frame_h, total, out_rgba8, out_rgb, stream);
 }
 
 int gpt_get_kernel_times(gpt_ctx* c, gpt_kernel_times* out)

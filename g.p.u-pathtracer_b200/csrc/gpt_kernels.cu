@@ -213,6 +213,47 @@ k_resolve(const float4* __restrict__ accum, const int n, uint32_t* __restrict__ 
     }
 }
 
+// ---- multi-GPU frame reduce fused with the running-sum update and the resolve ----
+// Runs on the ROOT GPU.  frames[r] is rank r's per-frame float4 buffer: the root's own memory for r == root, a
+// peer GPU's memory mapped through CUDA IPC otherwise, read with plain 16-byte loads over NVLink/NVSwitch.  Ranks
+// are summed in rank order (deterministic, unlike a ring/tree reduce), added into the running sum, and the same
+// thread resolves the pixel: one kernel replaces ncclReduce + accumulate + resolve (three passes over the frame).
+#define GPT_MAX_RANKS 16
+struct PeerFrames { const float4* f[GPT_MAX_RANKS]; int n; };
+
+__global__ void __launch_bounds__(256)
+k_reduce_resolve(const PeerFrames fr, const int n_pix, float4* __restrict__ total, uint32_t* __restrict__ rgba8, float* __restrict__ rgb)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pix; i += gridDim.x * blockDim.x) {
+        float4 v[GPT_MAX_RANKS];
+#pragma unroll
+        for (int r = 0; r < GPT_MAX_RANKS; ++r)
+            if (r < fr.n) v[r] = __ldcs(fr.f[r] + i);          // all peer loads in flight before the first add
+        float4 s = v[0];
+#pragma unroll
+        for (int r = 1; r < GPT_MAX_RANKS; ++r)
+            if (r < fr.n) { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+        float4 a = s;
+        if (total) { a = total[i]; a.x += s.x; a.y += s.y; a.z += s.z; a.w += s.w; total[i] = a; }
+        const float inv = a.w > 0.0f ? 1.0f / a.w : 0.0f;
+        const float mx = a.x * inv, my = a.y * inv, mz = a.z * inv;
+        if (rgb) { rgb[3 * i] = mx; rgb[3 * i + 1] = my; rgb[3 * i + 2] = mz; }
+        if (rgba8) rgba8[i] = pack_rgb(clamp01(mx), clamp01(my), clamp01(mz));
+    }
+}
+
+cudaError_t gptk_reduce_resolve(const float4* const* frames, int n_frames, int n_pix, float4* total, uint32_t* rgba8, float* rgb,
+                                int sm_count, cudaStream_t st)
+{
+    if (n_pix <= 0 || n_frames <= 0) return cudaSuccess;
+    if (n_frames > GPT_MAX_RANKS) return cudaErrorInvalidValue;
+    PeerFrames fr; fr.n = n_frames;
+    for (int r = 0; r < GPT_MAX_RANKS; ++r) fr.f[r] = r < n_frames ? frames[r] : nullptr;
+    int grid = (n_pix + 255) / 256; if (grid > sm_count * 8) grid = sm_count * 8;
+    k_reduce_resolve<<<grid, 256, 0, st>>>(fr, n_pix, total, rgba8, rgb);
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------- launchers
 static int persistent_grid(const void* kernel, int threads, int sm_count)
 {

@@ -49,6 +49,10 @@ cudaError_t gptk_trace_rays(const DevScene& sc, const float* o, const float* d, 
                             int* tri_idx, int* tri_addr, float* t, int sm_count, cudaStream_t st);
 cudaError_t gptk_resolve(const float4* accum, int n, uint32_t* rgba8, float* rgb, int sm_count, cudaStream_t st);
 
+// root-side fused peer reduce + running-sum update + resolve; frames[] = device-accessible pointers (own or IPC-mapped)
+cudaError_t gptk_reduce_resolve(const float4* const* frames, int n_frames, int n_pix, float4* total, uint32_t* rgba8, float* rgb,
+                                int sm_count, cudaStream_t st);
+
 // device re-pack (gpt_repack.cu): reference arrays (device pointers) -> packed nodes / triangles.
 // *out_nodes / *out_tris are cudaMalloc'd by the callee; returns the packed triangle count.
 struct RepackResult { float4* nodes; float4* tris; int n_nodes; int n_tris; int bad_layout; };

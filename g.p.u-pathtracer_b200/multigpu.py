@@ -46,3 +46,51 @@ def render_progressive_frame(render_fn, frame_accum, total_accum, frame_begin, f
     if total_accum is not None and (all_ranks or rank == root):
         total_accum.add_(frame_accum)
     return off, cnt
+
+
+class PeerFrames:
+    """Fused alternative to render_progressive_frame's NCCL reduce (SURVEY 8-e "later" row): every rank renders into a
+    library-owned, IPC-exported frame buffer; the root reads all peers' buffers over NVLink inside ONE kernel that
+    sums the ranks in rank order, adds the frame into the running sum and resolves it (gpt_reduce_resolve).  The only
+    collective left per frame is a one-element all_reduce used as a stream-ordered barrier ("the peers' renders are
+    done"); double buffering makes the next frame's clear safe while the root may still be reading.
+
+    ctx: gpt_b200.Context; dist: an initialised torch.distributed (NCCL) or None for a single rank."""
+
+    def __init__(self, ctx, width, height, dist=None, device=None, root=0):
+        import torch
+        self.ctx, self.dist, self.root = ctx, dist, root
+        self.world = dist.get_world_size() if dist is not None else 1
+        self.rank = dist.get_rank() if dist is not None else 0
+        self.width, self.height = int(width), int(height)
+        self.frame_index = 0
+        handle = ctx.frame_alloc(width, height, 2)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+        if self.world > 1:
+            mine = torch.tensor(list(handle), dtype=torch.uint8, device=device)
+            gathered = [torch.empty_like(mine) for _ in range(self.world)]
+            dist.all_gather(gathered, mine)
+            ctx.frame_open_peers([bytes(g.cpu().tolist()) for g in gathered], self.rank)
+            dist.barrier()
+
+    def frame(self, render_fn, frame_begin, frame_spp, total_accum=None, out_rgba8=None, out_rgb_f32=None, stream=None):
+        """render_fn(accum_ptr, sample_begin, sample_count) must ADD the slice into the float4 buffer at accum_ptr on
+        `stream`.  Returns this rank's (offset, count)."""
+        buf = self.frame_index & 1
+        self.frame_index += 1
+        off, cnt = sample_slice(frame_spp, self.world, self.rank)
+        self.ctx.frame_clear(buf, stream)
+        if cnt:
+            render_fn(self.ctx.frame_ptr(buf), frame_begin + off, cnt)
+        if self.world > 1:
+            self.dist.all_reduce(self._flag)               # stream-ordered barrier: every rank's render precedes it
+        if self.rank == self.root:
+            self.ctx.reduce_resolve(buf, total_accum, out_rgba8, out_rgb_f32, stream)
+        return off, cnt
+
+    def close(self):
+        if self.world > 1:
+            import torch
+            torch.cuda.synchronize()
+            self.dist.barrier()                            # nobody unmaps while the root may still be reading
+        self.ctx.frame_free()

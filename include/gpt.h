@@ -192,6 +192,30 @@ GPT_API int gpt_render_frame_host(gpt_ctx* ctx, const gpt_kernel_info* info, uin
                                   uint64_t sample_begin, uint32_t spp,
                                   uint32_t* host_rgba8, float* host_accum_f4);
 
+/* ---- multi-GPU: one process per GPU, peer-memory frame reduce fused with accumulate + resolve ----
+ * The reference is single-GPU (utilfun.cpp:73,95).  Here every rank renders a disjoint slice of a progressive frame's
+ * global sample indices into its own per-frame float4 buffer; instead of ncclReduce + add + resolve, the ROOT reads the
+ * peers' buffers directly over NVLink (CUDA IPC mappings) inside ONE kernel that sums the ranks in rank order, adds
+ * the frame into the running sum and resolves the pixel.
+ *   gpt_frame_alloc      library-owned frame buffers (n_buffers x W*H float4, one allocation) + the IPC handle of the
+ *                        allocation; the caller exchanges handles between ranks (torch.distributed all_gather, MPI ...)
+ *   gpt_frame_open_peers maps every other rank's allocation (handles[r], r != rank); world <= 16
+ *   gpt_frame_ptr        this rank's buffer `index` (render target for gpt_render after gpt_frame_clear)
+ *   gpt_reduce_resolve   root only: total += sum_r frame_r[index]; resolve into out_rgba8 / out_rgb_f32 (either NULL)
+ * Ordering between ranks is the caller's: the peers' renders must have completed (a stream-ordered collective such
+ * as a 4-byte all-reduce, or a host barrier after a sync) before the root launches gpt_reduce_resolve, and a buffer
+ * must not be cleared again before the root has read it -- alternate between n_buffers >= 2. */
+typedef struct { unsigned char reserved[64]; } gpt_ipc_mem_handle;      /* cudaIpcMemHandle_t */
+GPT_API int gpt_frame_alloc(gpt_ctx* ctx, int width, int height, int n_buffers, gpt_ipc_mem_handle* handle_out);
+GPT_API int gpt_frame_open_peers(gpt_ctx* ctx, const gpt_ipc_mem_handle* handles, int world, int rank);
+GPT_API float* gpt_frame_ptr(gpt_ctx* ctx, int index);
+GPT_API int gpt_frame_clear(gpt_ctx* ctx, int index, gpt_stream stream);
+GPT_API int gpt_reduce_resolve(gpt_ctx* ctx, int index, float* total_accum_f4, uint32_t* out_rgba8, float* out_rgb_f32, gpt_stream stream);
+/* the same kernel over explicit device pointers (frames[r], r = 0..n-1, all W*H float4): single-process use and tests */
+GPT_API int gpt_reduce_resolve_ptrs(gpt_ctx* ctx, const float* const* frames, int n_frames, int width, int height,
+                                    float* total_accum_f4, uint32_t* out_rgba8, float* out_rgb_f32, gpt_stream stream);
+GPT_API int gpt_frame_free(gpt_ctx* ctx);
+
 /* ---- test hooks / diagnostics ---- */
 /* first bounce of every pixel: geometry type, remapped triangle index (or -1), sphere/box index
  * (or -1) and hit distance; device or NULL outputs of W*H elements. */
