@@ -6,7 +6,7 @@
 //   1. count : a leaf child (~slot, CudaBVH.cpp:177) is walked exactly the way the reference kernel reads
 //              it (v0 first; bits(v0.x)==0x80000000 ends the leaf, cudaUtils.h:405-416) -> triangles per leaf
 //   2. scan  : exclusive prefix sum (CUB) -> first packed triangle of each leaf
-//   3. write : packed triangles (v0, e1, e2 + index / slot / last flag) and patched child pointers
+//   3. write : packed triangles (v0, e1, e2 + index / slot / triangles left in the leaf) and patched child pointers
 #include "gpt_kernels.h"
 #include <cub/device/device_scan.cuh>
 
@@ -54,14 +54,14 @@ __global__ void k_write_packed(const float4* __restrict__ ref_nodes, int n_inner
         // "-0.0 hazard"); it points at the shared null triangle appended behind the last real one.
         packed_child = (__float_as_uint(ref_tris[~c].x) == LEAF_TERM) ? ~n_total : ~base;
         int slot = ~c, k = 0;
+        const int cnt = offsets[i + 1] - base;                  // triangles in this leaf (pass 1)
         while (__float_as_uint(ref_tris[slot].x) != LEAF_TERM) {
             const float4 v0 = ref_tris[slot], v1 = ref_tris[slot + 1], v2 = ref_tris[slot + 2];
-            const bool last = __float_as_uint(ref_tris[slot + 3].x) == LEAF_TERM;
             const int orig = ((size_t)slot < n_indices) ? ref_indices[slot] : -1;
             float4* dst = tris + 3 * (size_t)(base + k);
             dst[0] = make_float4(v0.x, v0.y, v0.z, __int_as_float(orig));
             dst[1] = make_float4(v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, __int_as_float(slot));
-            dst[2] = make_float4(v2.x - v0.x, v2.y - v0.y, v2.z - v0.z, __int_as_float(last ? 1 : 0));
+            dst[2] = make_float4(v2.x - v0.x, v2.y - v0.y, v2.z - v0.z, __int_as_float(cnt - 1 - k));
             ++k; slot += 3;
         }
     }
@@ -73,10 +73,10 @@ __global__ void k_write_packed(const float4* __restrict__ ref_nodes, int n_inner
     }
     reinterpret_cast<int*>(nodes + 4 * node + 3)[i & 1] = packed_child;
     if ((i & 1) == 0) { reinterpret_cast<int*>(nodes + 4 * node + 3)[2] = 0; reinterpret_cast<int*>(nodes + 4 * node + 3)[3] = 0; }
-    if (i == 0) {   // null triangle: zero area -> det == 0 -> never hit; flagged last-in-leaf
+    if (i == 0) {   // null triangle: zero area -> det == 0 -> never hit; 0 triangles follow it in its leaf
         tris[3 * (size_t)n_total + 0] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
         tris[3 * (size_t)n_total + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-        tris[3 * (size_t)n_total + 2] = make_float4(0.f, 0.f, 0.f, __int_as_float(1));
+        tris[3 * (size_t)n_total + 2] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
     }
 }
 

@@ -11,7 +11,8 @@
 //   tris  : float4[3] per triangle reference (48 B), leaf after leaf, NO terminator slots
 //           [0] = v0.xyz , bits(original OBJ face index)      (the remap gpuTriIndices[hit], cudaUtils.h:452-456)
 //           [1] = (v1-v0).xyz , bits(slot address in the caller's array) (the reference's pre-remap hitIndex)
-//           [2] = (v2-v0).xyz , bits(1 if last triangle of its leaf else 0)  (replaces the 0x80000000 terminator read, :413)
+//           [2] = (v2-v0).xyz , bits(number of triangles that FOLLOW in the same leaf; 0 = last)  (replaces the 0x80000000
+//                 terminator read, :413; the first triangle of a leaf therefore carries leaf size - 1)
 //   spheres / boxes : the caller's 44-B / 52-B structs copied verbatim, staged to shared memory per CTA.
 #pragma once
 #include "gpt_math.cuh"

@@ -125,7 +125,7 @@ __device__ __forceinline__ void tri_step(const float4* __restrict__ tris, TravSt
     const float4 c = __ldg(tris + 3 * ti + 2);
     const float t = tri_test(a, b, c, o, d, cull);
     if (t > 0.0f && t < s.t) { s.t = t; s.tri = ti; }        // :428, strict: first visited wins ties
-    if (__float_as_int(c.w) != 0) {                          // last triangle of the leaf
+    if (__float_as_int(c.w) == 0) {                          // last triangle of the leaf (no triangle follows)
         s.leaf = s.node;                                     // :440 another leaf was reached meanwhile?
         if (s.node < 0) { s.tri_cur = ~s.node; s.node = stack[s.sp]; --s.sp; }
     } else {

@@ -17,6 +17,7 @@
 #include "gpt_shade.cuh"
 #include "gpt_kernels.h"
 #include <cstdlib>
+#include <cstring>
 
 #define WF_THREADS 128
 #ifndef WF_MIN_BLOCKS
@@ -181,6 +182,109 @@ k_wf_extend_ww(const DevScene sc, const int cull, const uint32_t* __restrict__ q
     }
 }
 
+// Third schedule (A/B, GPT_WF_EXTEND=pool; measured 17% slower than k_wf_extend_ww, see profiles/r01_schedules.md):
+// while-while like k_wf_extend_ww for the inner nodes, but the LEAF phase is pooled over
+// the warp.  In the reference's loop (cudaUtils.h:400-446) every lane walks its own leaf, so a round costs
+// max-leaf-size iterations while most lanes idle (ncu on k_wf_extend_ww: 22 lanes enter the triangle loop, 12 reach
+// the division, 5 the last dot product).  Here the warp's pending (ray, triangle) pairs are laid end to end
+// (exclusive scan of the leaf sizes; a leaf's size is carried by its first triangle) and handed out 32 at a time:
+// lane j of pass k tests pair 32k+j with the owner's ray fetched by shuffle, lanes without a leaf -- or without a
+// ray -- work too, and a round costs ceil(sum of leaf sizes / 32) iterations.  The owner's result is the
+// lexicographic minimum of (t, position in leaf) over the pairs with 0 < t < hitT, taken with one 64-bit shared
+// atomicMin per candidate: exactly what the sequential strict `t < hitT` update yields (first visited wins ties).
+#ifndef WF_POOL_MIN_BLOCKS
+#define WF_POOL_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(WF_THREADS, WF_POOL_MIN_BLOCKS)
+k_wf_extend_pool(const DevScene sc, const int cull, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
+                 unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
+                 int2* __restrict__ hit, const int refill_min)
+{
+    __shared__ unsigned long long s_best[WF_THREADS];
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned n = *n_ptr;
+    const bool do_cull = cull != 0;
+    unsigned long long* best = s_best + (threadIdx.x & ~31u);
+    int stack[GPT_STACK_SIZE];
+    TravState ts;
+    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+    uint32_t pid = 0;
+    bool active = false, exhausted = false;
+    ts.node = GPT_SENTINEL; ts.leaf = 0; ts.sp = 0; ts.t = GPT_F32_MAX; ts.tri = -1; ts.tri_cur = 0;
+
+    while (true) {
+        const unsigned m_idle = __ballot_sync(GPT_FULL_MASK, !active);
+        if (m_idle != 0u && !exhausted && (__popc(m_idle) >= refill_min || m_idle == GPT_FULL_MASK)) {
+            unsigned base = 0;
+            const int leader = __ffs(m_idle) - 1;
+            if ((int)lane == leader) base = atomicAdd(fetch, (unsigned)__popc(m_idle));
+            base = __shfl_sync(GPT_FULL_MASK, base, leader);
+            if (base + (unsigned)__popc(m_idle) >= n) exhausted = true;
+            if (!active) {
+                const unsigned j = base + (unsigned)__popc(m_idle & lt_mask);
+                if (j < n) {
+                    pid = queue ? queue[j] : j;
+                    const float4 ro = ray_o[pid], rd = ray_d[pid];
+                    o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
+                    trav_init(ts, stack, o, d, true);
+                    active = true;
+                }
+            }
+        }
+        if (__ballot_sync(GPT_FULL_MASK, active) == 0u) break;      // nothing armed: queue exhausted
+        if (active) {
+            while (trav_wants_node(ts)) {
+                node_step(sc.nodes, ts, stack);
+                if (!__any_sync(__activemask(), ts.leaf >= 0)) break;
+            }
+        }
+        __syncwarp();
+        // ---- pooled leaf phase: every lane of the warp takes part ----
+        const bool has_leaf = active && trav_wants_tri(ts);
+        const int first = ts.tri_cur;
+        int cnt = 0;
+        if (has_leaf) cnt = __float_as_int(__ldg(sc.tris + 3 * first + 2).w) + 1;      // leaf size, carried by its first triangle
+        int incl = cnt;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(GPT_FULL_MASK, incl, off); if ((int)lane >= off) incl += v; }
+        const int total = __shfl_sync(GPT_FULL_MASK, incl, 31);
+        const int excl = incl - cnt;
+        best[lane] = ~0ull;
+        __syncwarp();
+        for (int base = 0; base < total; base += 32) {
+            const int q = base + (int)lane;
+            // owner = number of lanes whose inclusive sum is <= q (the sums are non-decreasing in the lane index)
+            int own = 0;
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) { const int v = __shfl_sync(GPT_FULL_MASK, incl, own + step - 1); if (v <= q) own += step; }
+            own &= 31;
+            const float ox = __shfl_sync(GPT_FULL_MASK, o.x, own), oy = __shfl_sync(GPT_FULL_MASK, o.y, own), oz = __shfl_sync(GPT_FULL_MASK, o.z, own);
+            const float dx = __shfl_sync(GPT_FULL_MASK, d.x, own), dy = __shfl_sync(GPT_FULL_MASK, d.y, own), dz = __shfl_sync(GPT_FULL_MASK, d.z, own);
+            const float ht = __shfl_sync(GPT_FULL_MASK, ts.t, own);
+            const int f0 = __shfl_sync(GPT_FULL_MASK, first, own), e0 = __shfl_sync(GPT_FULL_MASK, excl, own);
+            if (q < total) {
+                const int pos = q - e0, ti = f0 + pos;
+                const float4 a = __ldg(sc.tris + 3 * ti), b = __ldg(sc.tris + 3 * ti + 1), c = __ldg(sc.tris + 3 * ti + 2);
+                const float t = tri_test(a, b, c, mk3(ox, oy, oz), mk3(dx, dy, dz), do_cull);
+                if (t > 0.0f && t < ht)
+                    atomicMin(best + own, ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(unsigned)pos);
+            }
+        }
+        __syncwarp();
+        if (has_leaf) {
+            const unsigned long long k = best[lane];
+            if (k != ~0ull) { ts.t = __uint_as_float((unsigned)(k >> 32)); ts.tri = first + (int)(unsigned)(k & 0xffffffffull); }
+            ts.leaf = ts.node;                                           // cudaUtils.h:440: another leaf reached meanwhile?
+            if (ts.node < 0) { ts.tri_cur = ~ts.node; ts.node = stack[ts.sp]; --ts.sp; }
+        }
+        if (active && trav_finished(ts)) {
+            hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
+            active = false;
+        }
+    }
+}
+
 // One thread per path alive at bounce `bounce`: the rest of the bounce-loop body (tracer.cu:98-296), the
 // per-pixel launch sum when the path ends (tracer.cu:305 / :141), and compaction of the survivors.
 __global__ void __launch_bounds__(256)
@@ -302,11 +406,14 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                                   unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches,
                                   KernelTimer* kt)
 {
-    static const bool use_ww = getenv("GPT_WF_VOTED") == nullptr;     // default: while-while extend
+    // extend schedule: while-while (default); GPT_WF_EXTEND=pool the pooled-leaf variant, =voted the voted steps (both
+    // bit-identical, both measured slower: profiles/r01_schedules.md)
+    static const int ext_kind = []{ const char* e = getenv("GPT_WF_EXTEND"); if (!e) e = getenv("GPT_WF_VOTED") ? "voted" : "ww";
+                                    return !strcmp(e, "pool") ? 0 : (!strcmp(e, "voted") ? 2 : 1); }();
     static int ext_grid = 0;
     if (!ext_grid) {
         int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, use_ww ? (const void*)k_wf_extend_ww : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ext_kind == 0 ? (const void*)k_wf_extend_pool : ext_kind == 1 ? (const void*)k_wf_extend_ww : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
         ext_grid = sm_count * per_sm;
     }
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
@@ -340,7 +447,10 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                 const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
                 if (has_mesh) {
                     if (kt) kt->tick(KT_EXTEND, st);
-                    if (use_ww)
+                    if (ext_kind == 0)
+                        k_wf_extend_pool<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
+                                                                          wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                    else if (ext_kind == 1)
                         k_wf_extend_ww<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                         wb.ray_o, wb.ray_d, wb.hit, refill_min);
                     else
