@@ -127,15 +127,16 @@ k_wf_extend(const DevScene sc, const int cull, const uint32_t* __restrict__ queu
 // persistent while-while loop.  All lanes meet at the top of the outer loop once per "descend to the next leaf +
 // test that leaf" round; idle lanes are re-armed there.  Tighter inner loops than the voted steps above, but
 // lanes wait for the slowest descent / largest leaf of the round.
+template <bool CULL>      // back-face culling resolved at compile time: the flag is tested once per triangle otherwise
 __global__ void __launch_bounds__(WF_THREADS, WF_MIN_BLOCKS)
-k_wf_extend_ww(const DevScene sc, const int cull, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
+k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
                unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                int2* __restrict__ hit, const int refill_min)
 {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     const unsigned n = *n_ptr;
-    const bool do_cull = cull != 0;
+    const bool do_cull = CULL;
     int stack[GPT_STACK_SIZE];
     TravState ts;
     f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
@@ -413,7 +414,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
     static int ext_grid = 0;
     if (!ext_grid) {
         int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ext_kind == 0 ? (const void*)k_wf_extend_pool : ext_kind == 1 ? (const void*)k_wf_extend_ww : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ext_kind == 0 ? (const void*)k_wf_extend_pool : ext_kind == 1 ? (const void*)k_wf_extend_ww<true> : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
         ext_grid = sm_count * per_sm;
     }
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
@@ -450,10 +451,10 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                     if (ext_kind == 0)
                         k_wf_extend_pool<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                           wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                    else if (ext_kind == 1)
-                        k_wf_extend_ww<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
-                                                                        wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                    else
+                    else if (ext_kind == 1) {
+                        if (p.cull) k_wf_extend_ww<true><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        else k_wf_extend_ww<false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                    } else
                         k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                      wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);
                     *launches += 1;
