@@ -23,7 +23,7 @@ __device__ __forceinline__ void camera_ray(const RenderParams& p, int px, int py
     float ys = ((float)py - (float)p.height / 2.0f) + 0.5f;
     ys = ys + jy;
     ys = ys * p.dist; ys = ys * p.fov; ys = ys / (float)(p.height - 1);
-    const f3 dir = mad3(ld3(p.up), ys, mad3(ld3(p.right), xs, scale3(ld3(p.front), p.dist)));
+    const f3 dir = mad3(ld3(p.up), ys, mad3(ld3(p.front), p.dist, scale3(ld3(p.right), xs)));   // FMUL right, FFMA front, FFMA up (reference SASS)
     o = add3(ld3(p.pos), dir);
     d = normalize3(dir);
 }
@@ -95,7 +95,7 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
         emit = mk3(bx[6], bx[7], bx[8]); objcol = mk3(bx[9], bx[10], bx[11]); mat = __float_as_int(bx[12]);
     }
-    ps.accu = add3(ps.accu, mul3(ps.mask, emit));                        // :120/:133
+    ps.accu = mk3(fmaf(ps.mask.x, emit.x, ps.accu.x), fmaf(ps.mask.y, emit.y, ps.accu.y), fmaf(ps.mask.z, emit.z, ps.accu.z));   // :120/:133, contracted
 
     f3 nextdir;
     if (mat == MAT_DIFF) {                                               // :156-186 (Q5)
@@ -112,8 +112,10 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         hitpos = mad3(nl, 0.001f, hitpos);
         ps.mask = mul3(ps.mask, objcol);
     } else if (mat == MAT_SPEC) {                                        // :190-203 (Q6)
-        const float k = dot3(nl, ps.d) * 2.0f;
-        nextdir = normalize3(mad3(nl, -k, ps.d));
+        // :194 'dir - nl * dot * 2.0f' the way nvcc emits it for the reference: pr = rn(nl*k), 2*pr formed as fma(k, nl, pr), plain subtract
+        const float k = dot3(nl, ps.d);
+        const f3 pr = scale3(nl, k);
+        nextdir = normalize3(mk3(ps.d.x - fmaf(k, nl.x, pr.x), ps.d.y - fmaf(k, nl.y, pr.y), ps.d.z - fmaf(k, nl.z, pr.z)));
         hitpos = mad3(nl, 0.001f, hitpos);
         ps.mask = mul3(ps.mask, objcol);
     } else if (mat == MAT_REFR) {                                        // :205-256 (Q7)
@@ -121,7 +123,7 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         const float nc = p.air, ntr = p.glass;
         const float nnt = into ? nc / ntr : ntr / nc;
         const float ddn = dot3(ps.d, nl);
-        const float cos2t = 1.0f - (nnt * nnt) * (1.0f - ddn * ddn);
+        const float cos2t = fmaf(-(nnt * nnt), fmaf(-ddn, ddn, 1.0f), 1.0f);        // :212, contracted as in the reference's SASS
         if (cos2t < 0.0f) {
             const float k = dot3(n, ps.d) * 2.0f;
             nextdir = normalize3(mad3(n, -k, ps.d));
@@ -130,7 +132,7 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
             const f3 tdir = normalize3(mad3(n, -s, scale3(ps.d, nnt)));
             const float R0 = ((ntr - nc) * (ntr - nc)) / (ntr + nc) * (ntr + nc);   // :230 precedence kept
             const float c = 1.0f - (into ? -ddn : dot3(tdir, n));
-            const float Re = R0 + (1.0f - R0) * c * c * c * c * c;
+            const float Re = fmaf((1.0f - R0) * c * c * c * c, c, R0);           // :232, last product fused into the sum
             const float Tr = 1.0f - Re;
             const float P = 0.25f + 0.5f * Re;
             const float RP = Re / P, TP = Tr / (1.0f - P);

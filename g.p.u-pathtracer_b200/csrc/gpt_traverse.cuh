@@ -156,7 +156,7 @@ __device__ __forceinline__ float sphere_test(const float* s, const f3 o, const f
 {
     const f3 op = sub3(mk3(s[0], s[1], s[2]), o);
     const float b = dot3(op, d);
-    const float disc = fmaf(b, b, -dot3(op, op)) + s[3] * s[3];
+    const float disc = fmaf(s[3], s[3], fmaf(b, b, -dot3(op, op)));      // contraction as in the reference's SASS
     // branch-free: the warp pays for the square root whenever any lane needs it, so every lane may as well
     // take it; the selected values are the same as in the early-out form
     const float sq = sqrtf(fmaxf(disc, 0.0f));

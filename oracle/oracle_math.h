@@ -23,8 +23,9 @@ static inline V3 vmul(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); 
 static inline V3 vscale(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
 /* a + b*s with one rounding per component */
 static inline V3 vmad(V3 b, float s, V3 a) { return v3(fmaf(b.x, s, a.x), fmaf(b.y, s, a.y), fmaf(b.z, s, a.z)); }
-/* contract: x term first, then y, then z, each an FMA onto the running sum */
-static inline float vdot(V3 a, V3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+/* glm::dot = (a.x*b.x + a.y*b.y) + a.z*b.z as nvcc contracts it in the reference kernel (read off its SASS, e.g. the
+ * determinant of cudaUtils.h:145: FMUL y, FFMA x, FFMA z): the y product is rounded, x and z are fused */
+static inline float vdot(V3 a, V3 b) { return fmaf(a.z, b.z, fmaf(a.x, b.x, a.y * b.y)); }
 static inline V3 vcross(V3 a, V3 b)
 {
     return v3(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));

@@ -57,6 +57,8 @@ class OrcCounters(C.Structure):
 
 ORC_FLAG_NO_JITTER = 1
 ORC_FLAG_METAL_FIXED = 2
+ORC_FLAG_REF_RNG = 4          # replay the reference's cuRAND XORWOW stream + CUDA sinf/cosf (oracle.h)
+ORC_FLAG_REF_RNG_SWAP = 8     # A/B: other argument order at cudaUtils.h call site tracer.cu:170
 
 _oracle = None
 
