@@ -26,6 +26,8 @@ FLAG_METAL_FIXED = 1 << 1
 FLAG_MEGAKERNEL = 1 << 2
 FLAG_COUNT_BOUNCES = 1 << 3
 FLAG_TIME_KERNELS = 1 << 4
+FLAG_WIDE_BVH = 1 << 5        # always traverse the 4-wide quantised tree
+FLAG_BINARY_BVH = 1 << 6      # always traverse the binary tree as uploaded
 K_GENERATE, K_EXTEND, K_SHADE, K_COLLECT, K_ACCUMULATE, K_RESOLVE, K_OTHER = range(7)
 
 
@@ -91,7 +93,7 @@ assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 # every symbol include/gpt.h declares (tests check the library exports each one)
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
            "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
-           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times",
+           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_wide_info",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
            "gpt_reduce_resolve_ptrs", "gpt_frame_free",
@@ -129,6 +131,7 @@ def load_library():
     L.gpt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
     L.gpt_reset_stats.argtypes = [C.c_void_p]
     L.gpt_get_kernel_times.argtypes = [C.c_void_p, C.POINTER(KernelTimes)]
+    L.gpt_wide_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.gpt_build_bvh.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.POINTER(BuiltBVH)]
     L.gpt_free_bvh.argtypes = [C.c_void_p, C.POINTER(BuiltBVH)]
     L.gpt_copy_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
@@ -446,6 +449,12 @@ class Context:
         fm = np.ascontiguousarray(face_material, dtype=np.int32)
         self._ck(self._L.gpt_set_triangle_materials(self._h, C.addressof(materials), len(materials), fm.ctypes.data, fm.size),
                  "gpt_set_triangle_materials")
+
+    def wide_info(self):
+        """(wide nodes, wide levels) of the 4-wide tree in use; (0, 0) = the binary tree is traversed."""
+        n, lv = C.c_int(0), C.c_int(0)
+        self._ck(self._L.gpt_wide_info(self._h, C.byref(n), C.byref(lv)), "gpt_wide_info")
+        return n.value, lv.value
 
     def kernel_times(self):
         """{class name: (ms, launches)} since the last reset_stats (needs FLAG_TIME_KERNELS)."""

@@ -21,6 +21,8 @@ struct gpt_ctx {
     float* boxes = nullptr; int n_boxes = 0;
     float* tri_mats = nullptr; int* face_mat = nullptr; int n_tri_mats = 0, n_faces = 0;   // N4, survive scene re-uploads
     bool has_scene = false;
+    // N3: 4-wide quantised tree over the packed binary one, built on first use (gpt_wide.cu)
+    float4* wnodes = nullptr; int n_wide = 0, wide_levels = 0; bool wide_tried = false;
     // identity of the reference arrays the packed BVH was built from (gpt_launch re-packs on change)
     const void* src_nodes = nullptr; const void* src_tris = nullptr; const void* src_idx = nullptr;
     size_t src_n_nodes = 0, src_n_tris = 0, src_n_idx = 0;
@@ -81,8 +83,14 @@ int gpt_create(gpt_ctx** out, int device)
     return GPT_OK;
 }
 
+static void free_wide(gpt_ctx* c)
+{
+    cudaFree(c->wnodes); c->wnodes = nullptr; c->n_wide = 0; c->wide_levels = 0; c->wide_tried = false;
+}
+
 static void free_scene(gpt_ctx* c)
 {
+    free_wide(c);
     cudaFree(c->nodes); cudaFree(c->tris); cudaFree(c->spheres); cudaFree(c->boxes);
     c->nodes = c->tris = nullptr; c->spheres = c->boxes = nullptr;
     c->n_nodes = c->n_tris = c->n_spheres = c->n_boxes = 0;
@@ -156,6 +164,7 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
                                 const int32_t* idx, size_t n_idx)
 {
     cudaFree(c->nodes); cudaFree(c->tris); c->nodes = c->tris = nullptr; c->n_nodes = c->n_tris = 0;
+    free_wide(c);
     if (n_node_vec4 == 0 || !nodes) return GPT_OK;     // sphere-only scene
     if (!tris || !idx) return fail(c, GPT_ERR_INVALID, "BVH nodes given without triangle / index arrays");
     RepackResult r;
@@ -319,12 +328,50 @@ static int make_params(gpt_ctx* c, const gpt_kernel_info* info, uint64_t seed, R
     return GPT_OK;
 }
 
-static void uploaded_scene(const gpt_ctx* c, DevScene* sc)
+// does this context traverse the 4-wide tree?  (flags win; else by size, see include/gpt.h)
+static bool wide_wanted(const gpt_ctx* c)
 {
+    if (!c->nodes || c->n_nodes <= 0 || (c->flags & GPT_FLAG_BINARY_BVH) || (c->flags & GPT_FLAG_MEGAKERNEL)) return false;
+    if (c->flags & GPT_FLAG_WIDE_BVH) return true;
+    // measured on B200 (profiles/r01_wide_ab.jsonl): the wide tree is 12-18 % slower up to 1.6 M triangles and level at
+    // 20 M -- the extend kernel is issue-bound, not fetch-bound -- so it is never picked by size unless asked to
+    static const long long min_tris = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : -1ll; }();
+    return min_tris >= 0 && (long long)c->n_tris >= min_tris;
+}
+
+// builds the wide tree on first use; a tree that cannot be quantised (non-finite boxes) or is too deep for the wide
+// stack silently keeps the binary traversal -- same results either way
+static void ensure_wide(gpt_ctx* c)
+{
+    if (c->wnodes || c->wide_tried || !wide_wanted(c)) return;
+    c->wide_tried = true;
+    WideResult w;
+    if (cudaDeviceSynchronize() != cudaSuccess) return;
+    if (gptk_build_wide(c->nodes, c->n_nodes, &w, 0) != cudaSuccess) { cudaGetLastError(); return; }
+    c->launches += (unsigned long long)w.launches;
+    if (w.status != 0 || !w.wnodes || 3 * w.levels + 2 > GPT_W4_STACK) { cudaFree(w.wnodes); return; }
+    c->wnodes = w.wnodes; c->n_wide = w.n_wide; c->wide_levels = w.levels;
+}
+
+static void uploaded_scene(gpt_ctx* c, DevScene* sc)
+{
+    ensure_wide(c);
+    sc->wnodes = wide_wanted(c) ? c->wnodes : nullptr;
     sc->nodes = c->nodes; sc->tris = c->tris; sc->n_nodes = c->n_nodes; sc->n_tris = c->n_tris;
     sc->spheres = c->spheres; sc->n_spheres = c->n_spheres;
     sc->boxes = c->boxes; sc->n_boxes = c->n_boxes;
     sc->tri_mats = c->tri_mats; sc->face_mat = c->face_mat; sc->n_tri_mats = c->n_tri_mats; sc->n_faces = c->n_faces;
+}
+
+int gpt_wide_info(gpt_ctx* c, int* n_wide, int* levels)
+{
+    if (!c) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    ensure_wide(c);
+    const bool on = wide_wanted(c) && c->wnodes;
+    if (n_wide) *n_wide = on ? c->n_wide : 0;
+    if (levels) *levels = on ? c->wide_levels : 0;
+    return GPT_OK;
 }
 
 // scene for a launch: pointers carried by kernelInfo win (drop-in use), else the uploaded scene

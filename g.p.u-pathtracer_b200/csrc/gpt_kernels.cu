@@ -192,8 +192,10 @@ k_trace_rays(const DevScene sc, const float* __restrict__ o, const float* __rest
 {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         TriHit h; h.t = GPT_F32_MAX; h.tri = -1;
-        if (sc.n_nodes > 0)
-            h = traverse_bvh(sc.nodes, sc.tris, mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]), cull != 0);
+        if (sc.n_nodes > 0) {
+            const f3 ro = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), rd = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+            h = sc.wnodes ? traverse_bvh4(sc.wnodes, sc.tris, ro, rd, cull != 0) : traverse_bvh(sc.nodes, sc.tris, ro, rd, cull != 0);
+        }
         if (tri_idx) tri_idx[i] = h.tri >= 0 ? __float_as_int(__ldg(sc.tris + 3 * h.tri).w) : -1;
         if (tri_addr) tri_addr[i] = h.tri >= 0 ? __float_as_int(__ldg(sc.tris + 3 * h.tri + 1).w) : -1;
         if (t_out) t_out[i] = h.t;

@@ -66,6 +66,11 @@ struct BuildResult { float4* nodes; size_t n_node_vec4; float4* tris; size_t n_t
 cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, size_t n_tris, int max_leaf,
                             BuildResult* out, cudaStream_t st);
 
+// 4-wide quantised BVH collapsed on the device from the packed binary nodes (gpt_wide.cu).
+// status: 0 ok, 1 non-finite / inverted box (not quantisable), 2 internal, 3 not a tree
+struct WideResult { float4* wnodes; int n_wide; int levels; int status; int launches; };
+cudaError_t gptk_build_wide(const float4* nodes2, int n_inner, WideResult* out, cudaStream_t st);
+
 // wavefront pipeline (gpt_wavefront.cu).  Per-path arrays hold `capacity` entries, lsum one per pixel.
 struct WaveBuffers {
     float4 *ray_o, *ray_d, *mask, *accu, *lsum;

@@ -19,6 +19,8 @@
 
 #define GPT_SENTINEL 0x76543210          // bottom-of-stack marker (same value as cudaUtils.h:21)
 #define GPT_STACK_SIZE 64                // cudaUtils.h:22; builder MaxDepth 64 (SplitBVHBuilder.hpp:15)
+#define GPT_W4_EMPTY 0x7fffffff           // unused child slot of a wide node (gpt_wide.cu)
+#define GPT_W4_STACK 96                  // traversal stack of the wide tree: <= 3 pushes per wide level
 #define GPT_MAX_SMEM_SPHERES 64
 #define GPT_MAX_SMEM_BOXES 32
 
@@ -40,6 +42,8 @@ struct DevScene {
     const int*   face_mat;   // n_faces entries, indexed by the remapped OBJ face index (cudaUtils.h:452-456)
     int n_tri_mats;
     int n_faces;
+    // N3: optional 4-wide quantised tree over the same packed triangles (gpt_wide.cu); nullptr = traverse the binary tree
+    const float4* wnodes;
 };
 
 // the kernelInfo fields the device code reads (CpuStructs.hpp:45-72), flattened

@@ -115,6 +115,55 @@ __device__ __forceinline__ void node_step(const float4* __restrict__ nodes, Trav
     s.node = next;
 }
 
+// One visit of a 4-wide quantised node (gpt_wide.cu): same state machine as node_step -- nearest hit child next, the others
+// pushed farthest first, a first leaf postponed -- over four children per 64-B fetch instead of two.
+__device__ __forceinline__ float w4_plane(const unsigned w, const unsigned sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f; }
+#define W4_CSWAP(ka, ca, kb, cb) { const bool sw_ = kb < ka; const float tk_ = sw_ ? ka : kb; const int tc_ = sw_ ? ca : cb; ka = sw_ ? kb : ka; ca = sw_ ? cb : ca; kb = tk_; cb = tc_; }
+__device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravState& s, int* stack)
+{
+    const int node = s.node;
+    const float4 h = __ldg(wn + node);
+    const uint4 qa = __ldg(reinterpret_cast<const uint4*>(wn + node + 1));
+    const uint4 qb = __ldg(reinterpret_cast<const uint4*>(wn + node + 2));
+    const int4 ch = __ldg(reinterpret_cast<const int4*>(wn + node + 3));
+    const unsigned eb = __float_as_uint(h.w);
+    // plane = origin + q * 2^e  =>  t = (plane - o) / d = q * (2^e / d) + (origin - o) / d
+    const float sx = __uint_as_float((eb & 0xffu) << 23) * s.idx;
+    const float sy = __uint_as_float((eb & 0xff00u) << 15) * s.idy;
+    const float sz = __uint_as_float((eb & 0xff0000u) << 7) * s.idz;
+    const float bx = fmaf(h.x, s.idx, -s.oodx), by = fmaf(h.y, s.idy, -s.oody), bz = fmaf(h.z, s.idz, -s.oodz);
+    // entry planes are the lo planes where the direction is positive, the hi planes otherwise
+    const bool px = s.idx >= 0.0f, py = s.idy >= 0.0f, pz = s.idz >= 0.0f;
+    const unsigned nx = px ? qa.x : qa.y, fx = px ? qa.y : qa.x;
+    const unsigned ny = py ? qa.z : qa.w, fy = py ? qa.w : qa.z;
+    const unsigned nz = pz ? qb.x : qb.y, fz = pz ? qb.y : qb.x;
+    const float inf = __int_as_float(0x7f800000);
+    float k0, k1, k2, k3;
+    int c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
+#define W4_CHILD(i, kk, cc) { \
+        const unsigned sel = 0x7650u | (i); \
+        const float tn = fmaxf(fmaxf(fmaf(w4_plane(nx, sel), sx, bx), fmaf(w4_plane(ny, sel), sy, by)), fmaxf(fmaf(w4_plane(nz, sel), sz, bz), 0.0f)); \
+        const float tf = fminf(fminf(fmaf(w4_plane(fx, sel), sx, bx), fmaf(w4_plane(fy, sel), sy, by)), fminf(fmaf(w4_plane(fz, sel), sz, bz), s.t)); \
+        kk = (tn <= tf && cc != GPT_W4_EMPTY) ? tn : inf; }
+    W4_CHILD(0u, k0, c0) W4_CHILD(1u, k1, c1) W4_CHILD(2u, k2, c2) W4_CHILD(3u, k3, c3)
+#undef W4_CHILD
+    W4_CSWAP(k0, c0, k1, c1) W4_CSWAP(k2, c2, k3, c3) W4_CSWAP(k0, c0, k2, c2) W4_CSWAP(k1, c1, k3, c3) W4_CSWAP(k1, c1, k2, c2)
+    int next;
+    if (!(k0 < inf)) {
+        next = stack[s.sp]; --s.sp;
+    } else {
+        next = c0;
+        if (k3 < inf) { ++s.sp; stack[s.sp] = c3; }
+        if (k2 < inf) { ++s.sp; stack[s.sp] = c2; }
+        if (k1 < inf) { ++s.sp; stack[s.sp] = c1; }
+    }
+    if (next < 0 && s.leaf >= 0) {           // first leaf: postpone it and keep descending
+        s.leaf = next; s.tri_cur = ~next;
+        next = stack[s.sp]; --s.sp;
+    }
+    s.node = next;
+}
+
 // One triangle of the postponed leaf: cudaUtils.h:405-446.  Requires trav_wants_tri(s).
 __device__ __forceinline__ void tri_step(const float4* __restrict__ tris, TravState& s, int* stack,
                                          const f3 o, const f3 d, const bool cull)
@@ -143,6 +192,24 @@ __device__ __forceinline__ TriHit traverse_bvh(const float4* __restrict__ nodes,
         // inner nodes until every converged lane holds a leaf (or ran out of nodes)
         while (trav_wants_node(s)) {
             node_step(nodes, s, stack);
+            if (!__any_sync(__activemask(), s.leaf >= 0)) break;
+        }
+        while (trav_wants_tri(s)) tri_step(tris, s, stack, o, d, cull);
+    }
+    TriHit hit; hit.t = s.t; hit.tri = s.tri;
+    return hit;
+}
+
+// same loop over the 4-wide tree
+__device__ __forceinline__ TriHit traverse_bvh4(const float4* __restrict__ wnodes, const float4* __restrict__ tris,
+                                                const f3 o, const f3 d, const bool cull)
+{
+    int stack[GPT_W4_STACK];
+    TravState s;
+    trav_init(s, stack, o, d, true);
+    while (!trav_finished(s)) {
+        while (trav_wants_node(s)) {
+            node4_step(wnodes, s, stack);
             if (!__any_sync(__activemask(), s.leaf >= 0)) break;
         }
         while (trav_wants_tri(s)) tri_step(tris, s, stack, o, d, cull);

@@ -127,8 +127,12 @@ k_wf_extend(const DevScene sc, const int cull, const uint32_t* __restrict__ queu
 // persistent while-while loop.  All lanes meet at the top of the outer loop once per "descend to the next leaf +
 // test that leaf" round; idle lanes are re-armed there.  Tighter inner loops than the voted steps above, but
 // lanes wait for the slowest descent / largest leaf of the round.
-template <bool CULL>      // back-face culling resolved at compile time: the flag is tested once per triangle otherwise
-__global__ void __launch_bounds__(WF_THREADS, WF_MIN_BLOCKS)
+#ifndef WF_WIDE_MIN_BLOCKS
+#define WF_WIDE_MIN_BLOCKS 8
+#endif
+// WIDE: the inner-node phase walks the 4-wide quantised tree (gpt_wide.cu, node4_step) instead of the binary one.
+template <bool CULL, bool WIDE>      // back-face culling resolved at compile time: the flag is tested once per triangle otherwise
+__global__ void __launch_bounds__(WF_THREADS, WIDE ? WF_WIDE_MIN_BLOCKS : WF_MIN_BLOCKS)
 k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
                unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                int2* __restrict__ hit, const int refill_min)
@@ -137,7 +141,7 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
     const unsigned lt_mask = (1u << lane) - 1u;
     const unsigned n = *n_ptr;
     const bool do_cull = CULL;
-    int stack[GPT_STACK_SIZE];
+    int stack[WIDE ? GPT_W4_STACK : GPT_STACK_SIZE];
     TravState ts;
     f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
     uint32_t pid = 0;
@@ -166,7 +170,7 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
         if (__ballot_sync(GPT_FULL_MASK, active) == 0u) break;      // nothing armed: queue exhausted
         if (active) {
             while (trav_wants_node(ts)) {
-                node_step(sc.nodes, ts, stack);
+                if (WIDE) node4_step(sc.wnodes, ts, stack); else node_step(sc.nodes, ts, stack);
                 if (!__any_sync(__activemask(), ts.leaf >= 0)) break;
             }
             while (trav_wants_tri(ts)) {
@@ -414,8 +418,14 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
     static int ext_grid = 0;
     if (!ext_grid) {
         int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ext_kind == 0 ? (const void*)k_wf_extend_pool : ext_kind == 1 ? (const void*)k_wf_extend_ww<true> : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ext_kind == 0 ? (const void*)k_wf_extend_pool : ext_kind == 1 ? (const void*)k_wf_extend_ww<true, false> : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
         ext_grid = sm_count * per_sm;
+    }
+    static int wide_grid = 0;
+    if (!wide_grid) {
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_extend_ww<true, true>, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        wide_grid = sm_count * per_sm;
     }
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
     const int n_pix = p.width * p.height;
@@ -448,12 +458,15 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                 const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
                 if (has_mesh) {
                     if (kt) kt->tick(KT_EXTEND, st);
-                    if (ext_kind == 0)
+                    if (ext_kind == 0 && !sc.wnodes)
                         k_wf_extend_pool<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                           wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                    else if (ext_kind == 1) {
-                        if (p.cull) k_wf_extend_ww<true><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                        else k_wf_extend_ww<false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                    else if (sc.wnodes) {
+                        if (p.cull) k_wf_extend_ww<true, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        else k_wf_extend_ww<false, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                    } else if (ext_kind == 1) {
+                        if (p.cull) k_wf_extend_ww<true, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        else k_wf_extend_ww<false, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
                     } else
                         k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                      wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);

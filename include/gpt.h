@@ -98,7 +98,15 @@ enum {
     GPT_FLAG_METAL_FIXED = 1u << 1,  /* use the reflection vector w1 instead of the reference's int `w` */
     GPT_FLAG_MEGAKERNEL  = 1u << 2,  /* single persistent megakernel instead of the (default) wavefront pipeline */
     GPT_FLAG_COUNT_BOUNCES = 1u << 3, /* fill gpt_stats.rays_by_bounce (slower) */
-    GPT_FLAG_TIME_KERNELS = 1u << 4  /* CUDA-event timing per kernel class, read with gpt_get_kernel_times */
+    GPT_FLAG_TIME_KERNELS = 1u << 4, /* CUDA-event timing per kernel class, read with gpt_get_kernel_times */
+    /* Traversal structure of the wavefront pipeline and of gpt_trace_rays.  Default: the binary tree as
+     * uploaded (CudaBVH.cpp:121-270; visit order and therefore ties identical to cudaUtils.h:298-448).  Alternative: a
+     * 4-wide tree with 8-bit quantised child boxes collapsed from it on the device (64 B per four children).  Same
+     * nearest hit (t, face index); between two copies of a spatially split triangle -- bit-equal t -- the reported slot
+     * may be the other copy.  Measured slower than the binary tree on B200 up to 1.6 M triangles and level at 20 M
+     * (DESIGN.md), so it is opt-in: this flag, or GPT_WIDE_MIN_TRIS=<packed triangle count> in the environment. */
+    GPT_FLAG_WIDE_BVH   = 1u << 5,   /* always the 4-wide tree */
+    GPT_FLAG_BINARY_BVH = 1u << 6    /* always the binary tree */
 };
 
 typedef struct {
@@ -227,6 +235,9 @@ GPT_API int gpt_trace_rays(gpt_ctx* ctx, const float* o, const float* d, size_t 
                            int32_t* tri_idx, int32_t* tri_addr, float* t, gpt_stream stream);
 GPT_API int gpt_get_stats(gpt_ctx* ctx, gpt_stats* out);      /* synchronises the context's streams */
 GPT_API int gpt_reset_stats(gpt_ctx* ctx);
+/* The 4-wide tree in use (built lazily by the first launch that wants it): *n_wide = nodes (0 = binary tree in use),
+ * *levels = wide levels.  Returns GPT_OK, or the error of the build. */
+GPT_API int gpt_wide_info(gpt_ctx* ctx, int* n_wide, int* levels);
 GPT_API int gpt_get_kernel_times(gpt_ctx* ctx, gpt_kernel_times* out);  /* synchronises; see GPT_FLAG_TIME_KERNELS */
 
 /* ---- host-side helpers mirroring the reference's scene setup (no GPU needed) ---- */

@@ -1,0 +1,130 @@
+"""4-wide quantised BVH (g.p.u-pathtracer_b200/csrc/gpt_wide.cu) against the binary tree and the oracle (-m gpu).
+
+The wide tree is collapsed on the device from the packed binary tree; its quantised boxes contain the binary boxes, so the
+nearest hit (t and the remapped face index) must be IDENTICAL to the binary traversal / the oracle.  The triangle slot may be
+the other copy of a spatially split triangle (bit-equal t, different visit order) -- nothing else may differ."""
+import numpy as np
+import pytest
+
+from support import procedural, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def dev(torch, arr):
+    return torch.from_numpy(np.ascontiguousarray(arr)).cuda()
+
+
+def trace(torch, ctx, o, d, cull):
+    n = len(o)
+    tri = torch.empty(n, dtype=torch.int32, device="cuda"); addr = torch.empty_like(tri)
+    t = torch.empty(n, dtype=torch.float32, device="cuda")
+    ctx.trace_rays(dev(torch, o), dev(torch, d), n, cull, tri, addr, t)
+    torch.cuda.synchronize()
+    return tri.cpu().numpy(), addr.cpu().numpy(), t.cpu().numpy()
+
+
+@pytest.mark.parametrize("name,n", [("cornell", 20000), ("sphere_mesh", 20000), ("bunny_cornell", 40000)])
+@pytest.mark.parametrize("cull", [True, False])
+def test_wide_trace_equals_oracle(gpt, torch_cuda, name, n, cull):
+    torch = torch_cuda
+    sc = scenes.load_scene(name)
+    o, d = scenes.random_rays(sc, n, seed=23)
+    d[:64] = 0.0; d[:64, 2] = -1.0            # axis-parallel directions: the 2^-80 guard against the quantised planes
+    d[64:128] = 0.0; d[64:128, 0] = 1.0
+    d[128:192] = 0.0; d[128:192, 1] = -1.0
+    tri_o, addr_o, t_o, _ = scenes.oracle_trace_rays(sc, o, d, cull=cull)
+    with gpt.Context(0, gpt.FLAG_WIDE_BVH) as ctx:
+        ctx.upload_scene(sc["nodes"], sc["tris"], sc["indices"], gpt.default_spheres(), None)
+        n_wide, levels = ctx.wide_info()
+        assert 0 < n_wide <= len(sc["nodes"]) // 4 and 0 < levels <= 30
+        tri, addr, t = trace(torch, ctx, o, d, cull)
+    assert (t_o < 3e38).sum() > n // 20
+    np.testing.assert_array_equal(t, t_o)                          # hit distance: bit exact
+    np.testing.assert_array_equal(tri, tri_o)                      # remapped OBJ face index
+    other_copy = addr != addr_o                                    # allowed only between copies of one split triangle
+    assert other_copy.mean() <= 0.01
+    assert np.array_equal(tri[other_copy], tri_o[other_copy])
+
+
+def test_wide_flags_and_binary_default(gpt, torch_cuda):
+    sc = scenes.load_scene("bunny_cornell")
+    with gpt.Context(0) as ctx:                                    # small scene: binary by default
+        ctx.upload_scene(sc["nodes"], sc["tris"], sc["indices"], gpt.default_spheres(), None)
+        assert ctx.wide_info() == (0, 0)
+        ctx.set_flags(gpt.FLAG_WIDE_BVH)
+        n_wide, levels = ctx.wide_info()
+        assert n_wide > 0 and levels > 0
+        ctx.set_flags(gpt.FLAG_BINARY_BVH)
+        assert ctx.wide_info() == (0, 0)
+        ctx.set_flags(gpt.FLAG_WIDE_BVH | gpt.FLAG_MEGAKERNEL)     # the megakernel walks the binary tree
+        assert ctx.wide_info() == (0, 0)
+    with gpt.Context(0, gpt.FLAG_WIDE_BVH) as ctx:                 # sphere-only scene: nothing to collapse
+        ctx.upload_scene(None, None, None, gpt.default_spheres(), None)
+        assert ctx.wide_info() == (0, 0)
+
+
+@pytest.mark.parametrize("name,mat,cull,depth", [("bunny_cornell", 0, 1, 6), ("bunny_cornell", 3, 0, 5), ("sphere_mesh", 2, 1, 4),
+                                                 ("cornell", 1, 1, 5)])
+def test_wide_render_equals_binary_render(gpt, torch_cuda, name, mat, cull, depth):
+    """same frame through both trees, wavefront pipeline, native and legacy contract: bit-identical images"""
+    torch = torch_cuda
+    sc = scenes.load_scene(name)
+    w, h = 240, 136
+    info = gpt.default_kernel_info(w, h)
+    info.cam.dist = 12.0 * h / 720.0
+    if name == "sphere_mesh":
+        gpt.set_camera(info, (0.0, 0.0, 30.0), 0.0, 0.0)
+    info.depth, info.triCurrentMat, info.cullBackFaces = depth, mat, cull
+    out = []
+    for flags in (gpt.FLAG_BINARY_BVH, gpt.FLAG_WIDE_BVH):
+        with gpt.Context(0, flags) as ctx:
+            ctx.upload_scene(sc["nodes"], sc["tris"], sc["indices"], gpt.default_spheres(), None)
+            acc = torch.zeros(h, w, 4, dtype=torch.float32, device="cuda")
+            ctx.render(info, acc, 99, 0, 4)
+            torch.cuda.synchronize()
+            assert (ctx.wide_info()[0] > 0) == (flags == gpt.FLAG_WIDE_BVH)
+            out.append(acc.cpu().numpy())
+    assert out[0][..., :3].max() > 0
+    differing = np.any(out[0] != out[1], axis=-1).mean()
+    assert differing <= 1e-4, differing                            # a t-tie between two copies of a split triangle cannot change the image
+
+
+def test_wide_on_built_lbvh_large_scene(gpt, torch_cuda):
+    """1.2 M-triangle procedural scene, device-built LBVH: the wide tree's hits equal the oracle's on the binary arrays, and a
+    frame equals the binary tree's frame"""
+    torch = torch_cuda
+    verts, faces = procedural.synthetic_scene(1_200_000, seed=77)
+    n = 4000
+    rng = np.random.default_rng(5)
+    o = np.zeros((n, 3), np.float32)
+    tgt = np.stack([rng.uniform(-18, 18, n), rng.uniform(-14, 14, n), rng.uniform(-300, -25, n)], 1)
+    d = (tgt / np.linalg.norm(tgt, axis=1, keepdims=True)).astype(np.float32)
+    w, h = 256, 144
+    info = gpt.default_kernel_info(w, h)
+    info.cam.dist = 12.0 * h / 720.0
+    info.depth = 4
+    frames = []
+    for flags in (gpt.FLAG_WIDE_BVH, 0):
+        with gpt.Context(0, flags) as ctx:
+            b = ctx.build_bvh(verts, faces)
+            ctx.upload_built(b, gpt.default_spheres())
+            n_wide, levels = ctx.wide_info()
+            if flags:
+                assert n_wide > 0 and 3 * levels + 2 <= 96, (n_wide, levels)
+                assert n_wide < b.n_inner_nodes
+                arr = ctx.built_to_host(b)
+                tri_o, addr_o, t_o, _ = scenes.oracle_trace_rays(dict(verts=verts, faces=faces, **arr), o, d, cull=True)
+                tri, addr, t = trace(torch, ctx, o, d, True)
+                assert (t_o < 3e38).mean() > 0.5
+                np.testing.assert_array_equal(t, t_o)
+                np.testing.assert_array_equal(tri, tri_o)
+                print("wide tree: %d nodes in %d levels over %d binary nodes (depth %d)" % (n_wide, levels, b.n_inner_nodes, b.depth))
+            else:
+                assert n_wide == 0
+            acc = torch.zeros(h, w, 4, dtype=torch.float32, device="cuda")
+            ctx.render(info, acc, 5, 0, 2)
+            torch.cuda.synchronize()
+            frames.append(acc.cpu().numpy())
+            ctx.free_bvh(b)
+    assert np.any(frames[0] != frames[1], axis=-1).mean() <= 1e-4
