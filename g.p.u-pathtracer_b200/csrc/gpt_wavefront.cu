@@ -20,6 +20,9 @@
 #include <cstring>
 
 #define WF_THREADS 128
+#ifndef SHADE_MIN_BLOCKS
+#define SHADE_MIN_BLOCKS 4
+#endif
 #ifndef WF_MIN_BLOCKS
 #define WF_MIN_BLOCKS 10   // 51-register cap, no spills; measured +1.5% over 8 (profiles/r01_sweep_extend.log)
 #endif
@@ -292,7 +295,7 @@ k_wf_extend_pool(const DevScene sc, const int cull, const uint32_t* __restrict__
 
 // One thread per path alive at bounce `bounce`: the rest of the bounce-loop body (tracer.cu:98-296), the
 // per-pixel launch sum when the path ends (tracer.cu:305 / :141), and compaction of the survivors.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, SHADE_MIN_BLOCKS)
 k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sample0, const uint32_t bounce, const uint32_t pix0, const uint32_t n_wave,
            const uint32_t* __restrict__ queue_in, unsigned int* __restrict__ counters,
            uint32_t* __restrict__ queue_out, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
