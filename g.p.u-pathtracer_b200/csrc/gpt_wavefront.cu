@@ -23,6 +23,9 @@
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 4
 #endif
+#ifndef WF_NODE_K
+#define WF_NODE_K 3      // node-loop exit policy of k_wf_extend_ww, see there (profiles/r01_schedules.md #16)
+#endif
 #ifndef WF_MIN_BLOCKS
 #define WF_MIN_BLOCKS 10   // 51-register cap, no spills; measured +1.5% over 8 (profiles/r01_sweep_extend.log)
 #endif
@@ -174,7 +177,10 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
         if (active) {
             while (trav_wants_node(ts)) {
                 if (WIDE) node4_step(sc.wnodes, ts, stack); else node_step(sc.nodes, ts, stack);
-                if (!__any_sync(__activemask(), ts.leaf >= 0)) break;
+                // reference policy (WF_NODE_K = 1, cudaUtils.h:385-391): descend until every lane still in the loop holds a
+                // leaf.  WF_NODE_K = k leaves as soon as fewer than k lanes lack a leaf -- they resume after the leaf phase --
+                // instead of making the whole warp wait for one or two stragglers (k = 2..3: -3 % extend time; k >= 8 loses)
+                if (WF_NODE_K == 1 ? !__any_sync(__activemask(), ts.leaf >= 0) : __popc(__ballot_sync(__activemask(), ts.leaf >= 0)) < WF_NODE_K) break;
             }
             while (trav_wants_tri(ts)) {
                 tri_step(sc.tris, ts, stack, o, d, do_cull);
