@@ -103,6 +103,7 @@ static void free_wave(gpt_ctx* c)
     WaveBuffers& w = c->wave;
     cudaFree(w.ray_o); cudaFree(w.ray_d); cudaFree(w.mask); cudaFree(w.accu); cudaFree(w.lsum); cudaFree(w.hit);
     cudaFree(w.queue[0]); cudaFree(w.queue[1]); cudaFree(w.counters);
+    cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp);
     w = WaveBuffers{}; c->wave_pixels = 0; c->wave_counters = 0;
 }
 
@@ -127,6 +128,29 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     CU(c, cudaMalloc(&w.counters, nc * sizeof(unsigned int)));
     w.capacity = want;
     c->wave_pixels = n_pix; c->wave_counters = nc;
+    w.sort_keys[0] = w.sort_keys[1] = w.sort_vals = nullptr; w.sort_tmp = nullptr; w.sort_tmp_bytes = 0;
+    return GPT_OK;
+}
+
+// Ray reordering before the secondary extends (gpt_wavefront.cu, k_wf_sort_keys + CUB radix sort): pays on large scenes
+// (synthetic 2 M triangles: extend -22 %, frame +11 %; 20 M: +18 %), loses 4 % on the 1.6 M-triangle dragon and 30 % on the
+// 5 k-triangle bench scene (a sort costs ~37 ps per ray).  GPT_WF_SORT=0 never, =1..3 always (key layout), unset: from
+// GPT_SORT_MIN_TRIS (2 Mi) packed triangles up.  Images are bit-identical either way.
+static int ensure_sort(gpt_ctx* c)
+{
+    static const int env = []{ const char* e = getenv("GPT_WF_SORT"); return e ? atoi(e) : -1; }();
+    static const long long sort_min_tris = []{ const char* e = getenv("GPT_SORT_MIN_TRIS"); return e ? atoll(e) : (2ll << 20); }();
+    const bool want = c->nodes && !(c->flags & GPT_FLAG_MEGAKERNEL) && (env > 0 || (env < 0 && (long long)c->n_tris >= sort_min_tris));
+    WaveBuffers& w = c->wave;
+    if (want == (w.sort_vals != nullptr)) return GPT_OK;
+    CU(c, cudaDeviceSynchronize());
+    cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp);
+    w.sort_keys[0] = w.sort_keys[1] = w.sort_vals = nullptr; w.sort_tmp = nullptr; w.sort_tmp_bytes = 0;
+    if (!want || w.capacity == 0) return GPT_OK;
+    w.sort_tmp_bytes = gptk_wave_sort_tmp_bytes(w.capacity);
+    CU(c, cudaMalloc(&w.sort_keys[0], w.capacity * sizeof(uint32_t))); CU(c, cudaMalloc(&w.sort_keys[1], w.capacity * sizeof(uint32_t)));
+    CU(c, cudaMalloc(&w.sort_vals, w.capacity * sizeof(uint32_t)));
+    CU(c, cudaMalloc(&w.sort_tmp, w.sort_tmp_bytes ? w.sort_tmp_bytes : 16));
     return GPT_OK;
 }
 
@@ -333,9 +357,10 @@ static bool wide_wanted(const gpt_ctx* c)
 {
     if (!c->nodes || c->n_nodes <= 0 || (c->flags & GPT_FLAG_BINARY_BVH) || (c->flags & GPT_FLAG_MEGAKERNEL)) return false;
     if (c->flags & GPT_FLAG_WIDE_BVH) return true;
-    // measured on B200 (profiles/r01_wide_ab.jsonl): the wide tree is 12-18 % slower up to 1.6 M triangles and level at
-    // 20 M -- the extend kernel is issue-bound, not fetch-bound -- so it is never picked by size unless asked to
-    static const long long min_tris = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : -1ll; }();
+    // measured on B200 (profiles/r01_wide_ab.jsonl, r01_schedules.md #15/#19): with unsorted rays the wide tree is 12-18 %
+    // slower up to 1.6 M triangles and level at 20 M; with the ray reordering that large scenes get anyway it is level at
+    // 2 M, +2.5 % at 5-10 M and +16 % at 20 M (4K).  Default: from 4 Mi packed triangles up.
+    static const long long min_tris = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : (4ll << 20); }();
     return min_tris >= 0 && (long long)c->n_tris >= min_tris;
 }
 
@@ -411,6 +436,7 @@ int gpt_launch(gpt_ctx* c, const gpt_kernel_info* info, gpt_stream stream)
     cudaError_t e;
     if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
         rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, 1u); if (rc) return rc;
+        rc = ensure_sort(c); if (rc) return rc;
         e = gptk_render_wavefront(sc, p, c->wave, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u,
                                   c->stats, c->sm_count, (cudaStream_t)stream, &c->launches,
                                   (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);
@@ -435,6 +461,7 @@ int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_
     cudaError_t e;
     if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
         rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, sample_count); if (rc) return rc;
+        rc = ensure_sort(c); if (rc) return rc;
         e = gptk_render_wavefront(sc, p, c->wave, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count,
                                   c->stats, c->sm_count, (cudaStream_t)stream, &c->launches,
                                   (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);

@@ -78,8 +78,11 @@ struct WaveBuffers {
     uint32_t* queue[2];
     unsigned int* counters;     // gptk_wave_counter_count(depth) entries
     size_t capacity;            // paths the per-path arrays hold (lsum: one per pixel of the frame)
+    // optional ray reordering before each secondary extend (GPT_WF_SORT): all nullptr = off
+    uint32_t* sort_keys[2]; uint32_t* sort_vals; void* sort_tmp; size_t sort_tmp_bytes;
 };
 size_t gptk_wave_counter_count(unsigned int depth);
+size_t gptk_wave_sort_tmp_bytes(size_t capacity);
 cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,
                                   float4* accum_f4, float* accum_v3, uint32_t* draw, unsigned long long constant_pdf,
                                   unsigned long long sample_begin, uint32_t sample_count,

@@ -18,6 +18,7 @@
 #include "gpt_kernels.h"
 #include <cstdlib>
 #include <cstring>
+#include <cub/device/device_radix_sort.cuh>
 
 #define WF_THREADS 128
 #ifndef SHADE_MIN_BLOCKS
@@ -414,6 +415,63 @@ static int wf_knob(const char* name, int dflt)
 
 size_t gptk_wave_counter_count(unsigned int depth) { return 2 * ((size_t)depth + 1); }
 
+// ---- optional ray reordering (GPT_WF_SORT): secondary rays are incoherent; sorting the queue by a key made of the
+// origin's cell (7 bits per axis of the mesh bounds, Morton order) and the direction's octant puts rays that walk the
+// same part of the tree into the same warp.  Only the ORDER in which the extend kernel fetches rays changes: hit[pid]
+// is per ray, so images are bit-identical.  The count of live rays stays on the device; entries past it get the
+// largest key and are never fetched.
+#define WF_SORT_BITS 30     // upper bound (temporary storage is sized for it); the bits actually sorted depend on the mode
+__device__ __forceinline__ unsigned wf_spread7(unsigned v) { v &= 0x7fu; v = (v | (v << 8)) & 0x00700fu; v = (v | (v << 4)) & 0x0430c3u; v = (v | (v << 2)) & 0x049249u; return v; }
+__host__ __device__ __forceinline__ int wf_sort_bits(const int mode) { return mode == 3 ? 30 : 24; }
+// mode 1: 7 bits per axis of the origin (Morton) + direction octant          = 24 bits
+// mode 2: 6 bits per axis of the origin + 2 bits per axis of the direction   = 24 bits
+// mode 3: 7 bits per axis of the origin + 3 bits per axis of the direction   = 30 bits
+__global__ void __launch_bounds__(256)
+k_wf_sort_keys(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr, const unsigned n_slots,
+               const float4* __restrict__ ray_o, const float4* __restrict__ ray_d, uint32_t* __restrict__ keys, const int mode)
+{
+    const unsigned n = *n_ptr;
+    const unsigned kmax = 0xffffffffu >> (32 - wf_sort_bits(mode));
+    // mesh bounds = union of the root's two child boxes
+    const float4 n0 = __ldg(sc.nodes), n1 = __ldg(sc.nodes + 1), nz = __ldg(sc.nodes + 2);
+    const float lox = fminf(n0.x, n1.x), hix = fmaxf(n0.y, n1.y), loy = fminf(n0.z, n1.z), hiy = fmaxf(n0.w, n1.w);
+    const float loz = fminf(nz.x, nz.z), hiz = fmaxf(nz.y, nz.w);
+    const float sx = 127.99f / fmaxf(hix - lox, 1e-20f), sy = 127.99f / fmaxf(hiy - loy, 1e-20f), sz = 127.99f / fmaxf(hiz - loz, 1e-20f);
+    for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n_slots; j += gridDim.x * blockDim.x) {
+        unsigned key = kmax;
+        if (j < n) {
+            const uint32_t pid = queue[j];
+            const float4 o = ray_o[pid], d = ray_d[pid];
+            unsigned cx = (unsigned)fminf(fmaxf((o.x - lox) * sx, 0.0f), 127.0f);
+            unsigned cy = (unsigned)fminf(fmaxf((o.y - loy) * sy, 0.0f), 127.0f);
+            unsigned cz = (unsigned)fminf(fmaxf((o.z - loz) * sz, 0.0f), 127.0f);
+            if (mode == 1) {
+                const unsigned oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+                key = ((wf_spread7(cx) | (wf_spread7(cy) << 1) | (wf_spread7(cz) << 2)) << 3) | oct;
+            } else {
+                const int db = mode == 2 ? 2 : 3;                    // direction bits per axis
+                const float ds = (float)(1 << db) * 0.4999f;
+                const unsigned qx = (unsigned)fminf(fmaxf((d.x + 1.0f) * ds, 0.0f), (float)((1 << db) - 1));
+                const unsigned qy = (unsigned)fminf(fmaxf((d.y + 1.0f) * ds, 0.0f), (float)((1 << db) - 1));
+                const unsigned qz = (unsigned)fminf(fmaxf((d.z + 1.0f) * ds, 0.0f), (float)((1 << db) - 1));
+                if (mode == 2) { cx >>= 1; cy >>= 1; cz >>= 1; }
+                const unsigned om = wf_spread7(cx) | (wf_spread7(cy) << 1) | (wf_spread7(cz) << 2);       // 21 (18) bits
+                const unsigned dm = wf_spread7(qx) | (wf_spread7(qy) << 1) | (wf_spread7(qz) << 2);       // 3*db bits
+                key = (om << (3 * db)) | dm;
+            }
+            if (key >= kmax) key = kmax - 1u;
+        }
+        keys[j] = key;
+    }
+}
+size_t gptk_wave_sort_tmp_bytes(size_t capacity)
+{
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr,
+                                    (long long)capacity, 0, WF_SORT_BITS, (cudaStream_t)0);
+    return bytes;
+}
+
 cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,
                                   float4* accum_f4, float* accum_v3, uint32_t* draw, unsigned long long constant_pdf,
                                   unsigned long long sample_begin, uint32_t sample_count,
@@ -436,6 +494,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_extend_ww<true, true>, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
         wide_grid = sm_count * per_sm;
     }
+    static const int sort_mode = []{ const int m = wf_knob("GPT_WF_SORT", 3); return m > 3 ? 3 : m; }();
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
     const int n_pix = p.width * p.height;
     // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays
@@ -465,19 +524,29 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
             *launches += 1;
             for (uint32_t b = 0; b < p.depth; ++b) {
                 const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
+                const uint32_t* q_ext = q_in;       // order in which the extend kernel fetches the rays
+                if (has_mesh && b > 0 && wb.sort_vals) {
+                    if (kt) kt->tick(KT_OTHER, st);
+                    k_wf_sort_keys<<<grid, 256, 0, st>>>(sc, q_in, wb.counters + b, (unsigned)n_paths, wb.ray_o, wb.ray_d, wb.sort_keys[0], sort_mode);
+                    size_t tb = wb.sort_tmp_bytes;
+                    if ((e = cub::DeviceRadixSort::SortPairs(wb.sort_tmp, tb, (const uint32_t*)wb.sort_keys[0], wb.sort_keys[1], q_in, wb.sort_vals,
+                                                             (long long)n_paths, 0, wf_sort_bits(sort_mode), st)) != cudaSuccess) return e;
+                    *launches += 4;
+                    q_ext = wb.sort_vals;
+                }
                 if (has_mesh) {
                     if (kt) kt->tick(KT_EXTEND, st);
                     if (ext_kind == 0 && !sc.wnodes)
-                        k_wf_extend_pool<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
+                        k_wf_extend_pool<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                           wb.ray_o, wb.ray_d, wb.hit, refill_min);
                     else if (sc.wnodes) {
-                        if (p.cull) k_wf_extend_ww<true, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                        else k_wf_extend_ww<false, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        if (p.cull) k_wf_extend_ww<true, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        else k_wf_extend_ww<false, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
                     } else if (ext_kind == 1) {
-                        if (p.cull) k_wf_extend_ww<true, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                        else k_wf_extend_ww<false, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_in, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        if (p.cull) k_wf_extend_ww<true, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        else k_wf_extend_ww<false, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
                     } else
-                        k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_in, wb.counters + b, wb.counters + p.depth + 1 + b,
+                        k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                      wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);
                     *launches += 1;
                 }

@@ -103,8 +103,9 @@ enum {
      * uploaded (CudaBVH.cpp:121-270; visit order and therefore ties identical to cudaUtils.h:298-448).  Alternative: a
      * 4-wide tree with 8-bit quantised child boxes collapsed from it on the device (64 B per four children).  Same
      * nearest hit (t, face index); between two copies of a spatially split triangle -- bit-equal t -- the reported slot
-     * may be the other copy.  Measured slower than the binary tree on B200 up to 1.6 M triangles and level at 20 M
-     * (DESIGN.md), so it is opt-in: this flag, or GPT_WIDE_MIN_TRIS=<packed triangle count> in the environment. */
+     * may be the other copy.  Measured on B200: slower than the binary tree on small and medium scenes,
+     * faster from a few million triangles up once rays are re-ordered, so the default picks it from 4 Mi packed
+     * triangles (GPT_WIDE_MIN_TRIS in the environment moves the threshold); the two flags force either structure. */
     GPT_FLAG_WIDE_BVH   = 1u << 5,   /* always the 4-wide tree */
     GPT_FLAG_BINARY_BVH = 1u << 6    /* always the binary tree */
 };

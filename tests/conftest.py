@@ -6,6 +6,10 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+# The library re-orders secondary rays before each extend from GPT_SORT_MIN_TRIS packed triangles up (default 2 Mi; read once,
+# at the first render).  Lowered here so that the 1.2 M-triangle scene of test_gpu_wide.py goes through the sorted pipeline
+# while the 1.0 M-triangle scene of test_gpu_build.py stays on the unsorted one.
+os.environ.setdefault("GPT_SORT_MIN_TRIS", "1100000")
 
 
 def pytest_configure(config):
