@@ -24,6 +24,9 @@
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 4
 #endif
+#ifndef WF_LEAF_SPLIT
+#define WF_LEAF_SPLIT 0   // A/B: culled leaves in two passes (determinant filter, then full tests), see leaf_step_culled; measured 1.5 % slower
+#endif
 #ifndef WF_NODE_K
 #define WF_NODE_K 3      // node-loop exit policy of k_wf_extend_ww, see there (profiles/r01_schedules.md #16)
 #endif
@@ -183,11 +186,15 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
                 // instead of making the whole warp wait for one or two stragglers (k = 2..3: -3 % extend time; k >= 8 loses)
                 if (WF_NODE_K == 1 ? !__any_sync(__activemask(), ts.leaf >= 0) : __popc(__ballot_sync(__activemask(), ts.leaf >= 0)) < WF_NODE_K) break;
             }
-            while (trav_wants_tri(ts)) {
-                tri_step(sc.tris, ts, stack, o, d, do_cull);
-                // a second leaf was postponed while this one waited: leave it for the next round (measured
-                // faster than draining it here: the round ends sooner for the rest of the warp)
-                if (ts.leaf < 0 && ts.tri_cur == ~ts.leaf) break;
+            if (CULL && WF_LEAF_SPLIT) {
+                if (trav_wants_tri(ts)) leaf_step_culled(sc.tris, ts, stack, o, d);     // one leaf per round, like the loop below
+            } else {
+                while (trav_wants_tri(ts)) {
+                    tri_step(sc.tris, ts, stack, o, d, do_cull);
+                    // a second leaf was postponed while this one waited: leave it for the next round (measured
+                    // faster than draining it here: the round ends sooner for the rest of the warp)
+                    if (ts.leaf < 0 && ts.tri_cur == ~ts.leaf) break;
+                }
             }
             if (trav_finished(ts)) {
                 hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
