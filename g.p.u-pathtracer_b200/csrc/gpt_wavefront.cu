@@ -428,44 +428,43 @@ size_t gptk_wave_counter_count(unsigned int depth) { return 2 * ((size_t)depth +
 // is per ray, so images are bit-identical.  The count of live rays stays on the device; entries past it get the
 // largest key and are never fetched.
 #define WF_SORT_BITS 30     // upper bound (temporary storage is sized for it); the bits actually sorted depend on the mode
-__device__ __forceinline__ unsigned wf_spread7(unsigned v) { v &= 0x7fu; v = (v | (v << 8)) & 0x00700fu; v = (v | (v << 4)) & 0x0430c3u; v = (v | (v << 2)) & 0x049249u; return v; }
-__host__ __device__ __forceinline__ int wf_sort_bits(const int mode) { return mode == 3 ? 30 : 24; }
-// mode 1: 7 bits per axis of the origin (Morton) + direction octant          = 24 bits
-// mode 2: 6 bits per axis of the origin + 2 bits per axis of the direction   = 24 bits
-// mode 3: 7 bits per axis of the origin + 3 bits per axis of the direction   = 30 bits
+__device__ __forceinline__ unsigned wf_spread10(unsigned v)      // 10 bits -> every third bit
+{
+    v &= 0x3ffu; v = (v | (v << 16)) & 0x030000ffu; v = (v | (v << 8)) & 0x0300f00fu; v = (v | (v << 4)) & 0x030c30c3u; v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+__host__ __device__ __forceinline__ int wf_sort_bits(const int mode) { return mode >= 3 ? 30 : 24; }
+// key = Morton cell of the origin (ob bits per axis of the mesh bounds) above Morton cell of the direction (db bits per axis):
+// mode 1: 7 + 1 (octant) = 24 bits   mode 2: 6 + 2 = 24   mode 3: 7 + 3 = 30   mode 4: 9 + 1 = 30   mode 5: 8 + 2 = 30   mode 6: 6 + 4 = 30   mode 7: 5 + 5 = 30
 __global__ void __launch_bounds__(256)
 k_wf_sort_keys(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr, const unsigned n_slots,
                const float4* __restrict__ ray_o, const float4* __restrict__ ray_d, uint32_t* __restrict__ keys, const int mode)
 {
     const unsigned n = *n_ptr;
     const unsigned kmax = 0xffffffffu >> (32 - wf_sort_bits(mode));
+    const int ob = mode == 1 ? 7 : mode == 2 ? 6 : mode == 3 ? 7 : mode == 4 ? 9 : mode == 5 ? 8 : mode == 6 ? 6 : 5;
+    const int db = mode == 1 ? 1 : mode == 2 ? 2 : mode == 3 ? 3 : mode == 4 ? 1 : mode == 5 ? 2 : mode == 6 ? 4 : 5;
     // mesh bounds = union of the root's two child boxes
     const float4 n0 = __ldg(sc.nodes), n1 = __ldg(sc.nodes + 1), nz = __ldg(sc.nodes + 2);
     const float lox = fminf(n0.x, n1.x), hix = fmaxf(n0.y, n1.y), loy = fminf(n0.z, n1.z), hiy = fmaxf(n0.w, n1.w);
     const float loz = fminf(nz.x, nz.z), hiz = fmaxf(nz.y, nz.w);
-    const float sx = 127.99f / fmaxf(hix - lox, 1e-20f), sy = 127.99f / fmaxf(hiy - loy, 1e-20f), sz = 127.99f / fmaxf(hiz - loz, 1e-20f);
+    const float oc = (float)(1 << ob), omax = oc - 1.0f;
+    const float sx = oc * 0.9999f / fmaxf(hix - lox, 1e-20f), sy = oc * 0.9999f / fmaxf(hiy - loy, 1e-20f), sz = oc * 0.9999f / fmaxf(hiz - loz, 1e-20f);
+    const float ds = (float)(1 << db) * 0.4999f, dmax = (float)((1 << db) - 1);
     for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n_slots; j += gridDim.x * blockDim.x) {
         unsigned key = kmax;
         if (j < n) {
             const uint32_t pid = queue[j];
             const float4 o = ray_o[pid], d = ray_d[pid];
-            unsigned cx = (unsigned)fminf(fmaxf((o.x - lox) * sx, 0.0f), 127.0f);
-            unsigned cy = (unsigned)fminf(fmaxf((o.y - loy) * sy, 0.0f), 127.0f);
-            unsigned cz = (unsigned)fminf(fmaxf((o.z - loz) * sz, 0.0f), 127.0f);
-            if (mode == 1) {
-                const unsigned oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
-                key = ((wf_spread7(cx) | (wf_spread7(cy) << 1) | (wf_spread7(cz) << 2)) << 3) | oct;
-            } else {
-                const int db = mode == 2 ? 2 : 3;                    // direction bits per axis
-                const float ds = (float)(1 << db) * 0.4999f;
-                const unsigned qx = (unsigned)fminf(fmaxf((d.x + 1.0f) * ds, 0.0f), (float)((1 << db) - 1));
-                const unsigned qy = (unsigned)fminf(fmaxf((d.y + 1.0f) * ds, 0.0f), (float)((1 << db) - 1));
-                const unsigned qz = (unsigned)fminf(fmaxf((d.z + 1.0f) * ds, 0.0f), (float)((1 << db) - 1));
-                if (mode == 2) { cx >>= 1; cy >>= 1; cz >>= 1; }
-                const unsigned om = wf_spread7(cx) | (wf_spread7(cy) << 1) | (wf_spread7(cz) << 2);       // 21 (18) bits
-                const unsigned dm = wf_spread7(qx) | (wf_spread7(qy) << 1) | (wf_spread7(qz) << 2);       // 3*db bits
-                key = (om << (3 * db)) | dm;
-            }
+            const unsigned cx = (unsigned)fminf(fmaxf((o.x - lox) * sx, 0.0f), omax);
+            const unsigned cy = (unsigned)fminf(fmaxf((o.y - loy) * sy, 0.0f), omax);
+            const unsigned cz = (unsigned)fminf(fmaxf((o.z - loz) * sz, 0.0f), omax);
+            const unsigned qx = (unsigned)fminf(fmaxf((d.x + 1.0f) * ds, 0.0f), dmax);
+            const unsigned qy = (unsigned)fminf(fmaxf((d.y + 1.0f) * ds, 0.0f), dmax);
+            const unsigned qz = (unsigned)fminf(fmaxf((d.z + 1.0f) * ds, 0.0f), dmax);
+            const unsigned om = wf_spread10(cx) | (wf_spread10(cy) << 1) | (wf_spread10(cz) << 2);
+            const unsigned dm = wf_spread10(qx) | (wf_spread10(qy) << 1) | (wf_spread10(qz) << 2);
+            key = (om << (3 * db)) | dm;
             if (key >= kmax) key = kmax - 1u;
         }
         keys[j] = key;
@@ -501,7 +500,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_extend_ww<true, true>, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
         wide_grid = sm_count * per_sm;
     }
-    static const int sort_mode = []{ const int m = wf_knob("GPT_WF_SORT", 3); return m > 3 ? 3 : m; }();
+    static const int sort_mode = []{ const int m = wf_knob("GPT_WF_SORT", 3); return m > 7 ? 7 : m; }();
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
     const int n_pix = p.width * p.height;
     // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays
