@@ -357,10 +357,9 @@ static bool wide_wanted(const gpt_ctx* c)
 {
     if (!c->nodes || c->n_nodes <= 0 || (c->flags & GPT_FLAG_BINARY_BVH) || (c->flags & GPT_FLAG_MEGAKERNEL)) return false;
     if (c->flags & GPT_FLAG_WIDE_BVH) return true;
-    // measured on B200 (profiles/r01_wide_ab.jsonl, r01_schedules.md #15/#19): with unsorted rays the wide tree is 12-18 %
-    // slower up to 1.6 M triangles and level at 20 M; with the ray reordering that large scenes get anyway it is level at
-    // 2 M, +2.5 % at 5-10 M and +16 % at 20 M (4K).  Default: from 4 Mi packed triangles up.
-    static const long long min_tris = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : (4ll << 20); }();
+    // measured on B200 (profiles/r01_schedules.md #15/#19/#23): the wide tree loses 3-9 % up to 100 k triangles, wins 4 % at
+    // 1.6 M (rays in path order), 6 % at 2 M, 10 % at 5 M and 24 % at 20 M (rays re-ordered).  Default: from 1 Mi packed triangles.
+    static const long long min_tris = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : (1ll << 20); }();
     return min_tris >= 0 && (long long)c->n_tris >= min_tris;
 }
 

@@ -117,21 +117,26 @@ __device__ __forceinline__ void node_step(const float4* __restrict__ nodes, Trav
 
 // One visit of a 4-wide quantised node (gpt_wide.cu): same state machine as node_step -- nearest hit child next, the others
 // pushed farthest first, a first leaf postponed -- over four children per 64-B fetch instead of two.
-__device__ __forceinline__ float w4_plane(const unsigned w, const unsigned sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f; }
 #define W4_CSWAP(ka, ca, kb, cb) { const bool sw_ = kb < ka; const float tk_ = sw_ ? ka : kb; const int tc_ = sw_ ? ca : cb; ka = sw_ ? kb : ka; ca = sw_ ? cb : ca; kb = tk_; cb = tc_; }
 __device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravState& s, int* stack)
 {
     const int node = s.node;
     const float4 h = __ldg(wn + node);
     const uint4 qa = __ldg(reinterpret_cast<const uint4*>(wn + node + 1));
-    const uint4 qb = __ldg(reinterpret_cast<const uint4*>(wn + node + 2));
+    const uint2 qb = __ldg(reinterpret_cast<const uint2*>(wn + node + 2));
     const int4 ch = __ldg(reinterpret_cast<const int4*>(wn + node + 3));
     const unsigned eb = __float_as_uint(h.w);
-    // plane = origin + q * 2^e  =>  t = (plane - o) / d = q * (2^e / d) + (origin - o) / d
+    // plane = origin + q * 2^e  =>  t = (plane - o) / d = q * s + b  with s = 2^e / d, b = (origin - o) / d.  The byte q is
+    // dropped into the mantissa of 2^23 (one PRMT, selector immediate, 2^23 kept in a register) and the 2^23 * s it
+    // brings along is taken out of b once per axis; gpt_wide.cu leaves a cell of slack for the rounding of that.
+    unsigned magic;
+    asm volatile("mov.b32 %0, 0x4B000000;" : "=r"(magic));
     const float sx = __uint_as_float((eb & 0xffu) << 23) * s.idx;
     const float sy = __uint_as_float((eb & 0xff00u) << 15) * s.idy;
     const float sz = __uint_as_float((eb & 0xff0000u) << 7) * s.idz;
-    const float bx = fmaf(h.x, s.idx, -s.oodx), by = fmaf(h.y, s.idy, -s.oody), bz = fmaf(h.z, s.idz, -s.oodz);
+    const float bx = fmaf(-8388608.0f, sx, fmaf(h.x, s.idx, -s.oodx));
+    const float by = fmaf(-8388608.0f, sy, fmaf(h.y, s.idy, -s.oody));
+    const float bz = fmaf(-8388608.0f, sz, fmaf(h.z, s.idz, -s.oodz));
     // entry planes are the lo planes where the direction is positive, the hi planes otherwise
     const bool px = s.idx >= 0.0f, py = s.idy >= 0.0f, pz = s.idz >= 0.0f;
     const unsigned nx = px ? qa.x : qa.y, fx = px ? qa.y : qa.x;
@@ -140,13 +145,15 @@ __device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravSt
     const float inf = __int_as_float(0x7f800000);
     float k0, k1, k2, k3;
     int c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
-#define W4_CHILD(i, kk, cc) { \
-        const unsigned sel = 0x7650u | (i); \
-        const float tn = fmaxf(fmaxf(fmaf(w4_plane(nx, sel), sx, bx), fmaf(w4_plane(ny, sel), sy, by)), fmaxf(fmaf(w4_plane(nz, sel), sz, bz), 0.0f)); \
-        const float tf = fminf(fminf(fmaf(w4_plane(fx, sel), sx, bx), fmaf(w4_plane(fy, sel), sy, by)), fminf(fmaf(w4_plane(fz, sel), sz, bz), s.t)); \
-        kk = (tn <= tf && cc != GPT_W4_EMPTY) ? tn : inf; }
-    W4_CHILD(0u, k0, c0) W4_CHILD(1u, k1, c1) W4_CHILD(2u, k2, c2) W4_CHILD(3u, k3, c3)
+#define W4_Q(w, i) __uint_as_float(__byte_perm(w, magic, 0x7650u | (i)))
+    // an unused slot has an inverted box (entry plane beyond exit plane on every axis): tn > tf without a test of its own
+#define W4_CHILD(i, kk) { \
+        const float tn = fmaxf(fmaxf(fmaf(W4_Q(nx, i), sx, bx), fmaf(W4_Q(ny, i), sy, by)), fmaxf(fmaf(W4_Q(nz, i), sz, bz), 0.0f)); \
+        const float tf = fminf(fminf(fmaf(W4_Q(fx, i), sx, bx), fmaf(W4_Q(fy, i), sy, by)), fminf(fmaf(W4_Q(fz, i), sz, bz), s.t)); \
+        kk = tn <= tf ? tn : inf; }
+    W4_CHILD(0u, k0) W4_CHILD(1u, k1) W4_CHILD(2u, k2) W4_CHILD(3u, k3)
 #undef W4_CHILD
+#undef W4_Q
     W4_CSWAP(k0, c0, k1, c1) W4_CSWAP(k2, c2, k3, c3) W4_CSWAP(k0, c0, k2, c2) W4_CSWAP(k1, c1, k3, c3) W4_CSWAP(k1, c1, k2, c2)
     int next;
     if (!(k0 < inf)) {

@@ -7,7 +7,8 @@
 //
 // Node, 4 x float4 (64 B, one 64-B aligned fetch group like the binary node):
 //   [0] = origin.x origin.y origin.z  bits(ex | ey<<8 | ez<<16)   e* = biased exponent: cell size on that axis = 2^(e-127)
-//   [1] = u32 lo.x[4]  hi.x[4]  lo.y[4]  hi.y[4]                   one byte per child: plane = origin + q * cell
+//   [1] = u32 lo.x[4]  hi.x[4]  lo.y[4]  hi.y[4]                   one byte per child: plane = origin + q * cell (one cell of
+//                                                                  slack outwards, see k_w4_collapse_level); unused slot: lo 255, hi 0
 //   [2] = u32 lo.z[4]  hi.z[4]  0  0
 //   [3] = int child[4]     >= 0: float4 index of a wide node;  < 0: ~(first packed triangle of a leaf);  GPT_W4_EMPTY: unused
 // Quantisation is conservative (lo rounded down, hi up, verified in float arithmetic), so a quantised box CONTAINS the
@@ -59,24 +60,36 @@ k_w4_collapse_level(const float4* __restrict__ nodes2, const int* __restrict__ q
         w4_read_pair(nodes2, s[best].child, a, b);
         s[best] = a; s[cnt++] = b;
     }
-    // frame of the node: the union box; per axis the smallest power-of-two cell with 255 cells covering the extent
-    float ulo[3], uhi[3], cell[3];
+    // frame of the node: per axis the smallest power-of-two cell with 253 cells covering the extent of the union box, origin one
+    // cell BELOW the union's lower corner.  A child's planes are the tightest conservative ones (plane(q) = origin + q * cell,
+    // verified in float arithmetic) moved ONE MORE cell outwards: the traversal evaluates (2^23 + q) * s + (b - 2^23 * s) with
+    // the byte dropped into the mantissa of 2^23 -- no int-to-float conversion, no subtraction -- and rounding b - 2^23 * s
+    // costs up to half a cell, which the extra cell absorbs.
+    float org[3], cell[3];
     unsigned ebits = 0;
     bool ok = true;
     for (int ax = 0; ax < 3; ++ax) {
         float lo = s[0].lo[ax], hi = s[0].hi[ax];
         for (int k = 1; k < cnt; ++k) { lo = fminf(lo, s[k].lo[ax]); hi = fmaxf(hi, s[k].hi[ax]); }
         for (int k = 0; k < cnt; ++k) ok = ok && isfinite(s[k].lo[ax]) && isfinite(s[k].hi[ax]) && s[k].lo[ax] <= s[k].hi[ax];
-        ulo[ax] = lo; uhi[ax] = hi;
         const float ext = hi - lo;
         int e = -100;
-        if (ext > 0.0f && isfinite(ext)) { (void)frexpf(ext / 255.0f, &e); }
+        if (ext > 0.0f && isfinite(ext)) { (void)frexpf(ext / 253.0f, &e); }
         else if (!(ext == 0.0f)) ok = false;
-        if (e < -120) e = -120;
-        if (e > 120) { ok = false; e = 120; }
-        float c = ldexpf(1.0f, e);
-        while (ok && fmaf(255.0f, c, lo) < hi && e < 120) { ++e; c = ldexpf(1.0f, e); }
-        cell[ax] = c;
+        // a cell must stay above the rounding of the coordinates themselves, or origin - cell == origin
+        const float mag = fmaxf(fabsf(lo), fabsf(hi));
+        if (mag > 0.0f && isfinite(mag)) { int em; (void)frexpf(mag, &em); if (e < em - 22) e = em - 22; }
+        if (e < -100) e = -100;
+        if (e > 100) { ok = false; e = 100; }
+        float c = ldexpf(1.0f, e), o = lo - c;
+        while (ok) {
+            o = lo - c;
+            while (fmaf(1.0f, c, o) > lo) o = nextafterf(o, -INFINITY);      // plane(1) must not lie above the lower corner
+            if (fmaf(254.0f, c, o) >= hi && o < lo) break;
+            if (++e > 100) { ok = false; break; }
+            c = ldexpf(1.0f, e);
+        }
+        cell[ax] = c; org[ax] = o;
         ebits |= (unsigned)(e + 127) << (8 * ax);
     }
     if (!ok) { atomicExch(bad, 1); return; }
@@ -85,18 +98,18 @@ k_w4_collapse_level(const float4* __restrict__ nodes2, const int* __restrict__ q
     for (int k = 0; k < 4; ++k) {
         if (k >= cnt) {
             child[k] = GPT_W4_EMPTY;
-            for (int ax = 0; ax < 3; ++ax) { qlo[ax] |= 255u << (8 * k); }      // inverted box: lo 255, hi 0
+            for (int ax = 0; ax < 3; ++ax) { qlo[ax] |= 255u << (8 * k); }      // inverted box (lo 255, hi 0): entry > exit, never hit
             continue;
         }
         for (int ax = 0; ax < 3; ++ax) {
-            const float c = cell[ax], o = ulo[ax];
-            int ql = (int)fminf(fmaxf(floorf((s[k].lo[ax] - o) / c), 0.0f), 255.0f);
-            while (ql > 0 && fmaf((float)ql, c, o) > s[k].lo[ax]) --ql;
-            int qh = (int)fminf(fmaxf(ceilf((s[k].hi[ax] - o) / c), 0.0f), 255.0f);
-            while (qh < 255 && fmaf((float)qh, c, o) < s[k].hi[ax]) ++qh;
-            if (fmaf((float)qh, c, o) < s[k].hi[ax]) atomicExch(bad, 2);       // cannot happen: 255 cells cover the union
-            qlo[ax] |= (unsigned)ql << (8 * k);
-            qhi[ax] |= (unsigned)qh << (8 * k);
+            const float c = cell[ax], o = org[ax];
+            int ql = (int)fminf(fmaxf(floorf((s[k].lo[ax] - o) / c), 1.0f), 254.0f);
+            while (ql > 1 && fmaf((float)ql, c, o) > s[k].lo[ax]) --ql;
+            int qh = (int)fminf(fmaxf(ceilf((s[k].hi[ax] - o) / c), 1.0f), 254.0f);
+            while (qh < 254 && fmaf((float)qh, c, o) < s[k].hi[ax]) ++qh;
+            if (fmaf((float)ql, c, o) > s[k].lo[ax] || fmaf((float)qh, c, o) < s[k].hi[ax]) atomicExch(bad, 2);   // cannot happen
+            qlo[ax] |= (unsigned)(ql - 1) << (8 * k);
+            qhi[ax] |= (unsigned)(qh + 1) << (8 * k);
         }
         if (s[k].child >= 0) {
             const int j = atomicAdd(n_out, 1);
@@ -107,7 +120,7 @@ k_w4_collapse_level(const float4* __restrict__ nodes2, const int* __restrict__ q
         }
     }
     float4* w = wnodes + 4 * (size_t)(base_in + i);
-    w[0] = make_float4(ulo[0], ulo[1], ulo[2], __uint_as_float(ebits));
+    w[0] = make_float4(org[0], org[1], org[2], __uint_as_float(ebits));
     w[1] = make_float4(__uint_as_float(qlo[0]), __uint_as_float(qhi[0]), __uint_as_float(qlo[1]), __uint_as_float(qhi[1]));
     w[2] = make_float4(__uint_as_float(qlo[2]), __uint_as_float(qhi[2]), 0.0f, 0.0f);
     w[3] = make_float4(__int_as_float(child[0]), __int_as_float(child[1]), __int_as_float(child[2]), __int_as_float(child[3]));

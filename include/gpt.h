@@ -104,7 +104,7 @@ enum {
      * 4-wide tree with 8-bit quantised child boxes collapsed from it on the device (64 B per four children).  Same
      * nearest hit (t, face index); between two copies of a spatially split triangle -- bit-equal t -- the reported slot
      * may be the other copy.  Measured on B200: slower than the binary tree on small and medium scenes,
-     * faster from a few million triangles up once rays are re-ordered, so the default picks it from 4 Mi packed
+     * faster from about a million triangles up, so the default picks it from 1 Mi packed
      * triangles (GPT_WIDE_MIN_TRIS in the environment moves the threshold); the two flags force either structure. */
     GPT_FLAG_WIDE_BVH   = 1u << 5,   /* always the 4-wide tree */
     GPT_FLAG_BINARY_BVH = 1u << 6    /* always the binary tree */

@@ -105,12 +105,12 @@ def test_wide_on_built_lbvh_large_scene(gpt, torch_cuda):
     info.cam.dist = 12.0 * h / 720.0
     info.depth = 4
     frames = []
-    for flags in (gpt.FLAG_WIDE_BVH, 0):
+    for flags in (0, gpt.FLAG_BINARY_BVH):                         # 1.2 M triangles: the wide tree is the default
         with gpt.Context(0, flags) as ctx:
             b = ctx.build_bvh(verts, faces)
             ctx.upload_built(b, gpt.default_spheres())
             n_wide, levels = ctx.wide_info()
-            if flags:
+            if not flags:
                 assert n_wide > 0 and 3 * levels + 2 <= 96, (n_wide, levels)
                 assert n_wide < b.n_inner_nodes
                 arr = ctx.built_to_host(b)
