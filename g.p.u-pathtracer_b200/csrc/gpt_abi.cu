@@ -23,6 +23,8 @@ struct gpt_ctx {
     bool has_scene = false;
     // N3: 4-wide quantised tree over the packed binary one, built on first use (gpt_wide.cu)
     float4* wnodes = nullptr; int n_wide = 0, wide_levels = 0; bool wide_tried = false;
+    // ray reordering (gpt_wavefront.cu): decided per scene, by environment, size threshold or a four-call trial (sort_policy)
+    int sort_phase = 0; bool sort_on = false; double sort_trial_ns_per_ray[2] = {0.0, 0.0};
     // identity of the reference arrays the packed BVH was built from (gpt_launch re-packs on change)
     const void* src_nodes = nullptr; const void* src_tris = nullptr; const void* src_idx = nullptr;
     size_t src_n_nodes = 0, src_n_tris = 0, src_n_idx = 0;
@@ -86,6 +88,7 @@ int gpt_create(gpt_ctx** out, int device)
 static void free_wide(gpt_ctx* c)
 {
     cudaFree(c->wnodes); c->wnodes = nullptr; c->n_wide = 0; c->wide_levels = 0; c->wide_tried = false;
+    c->sort_phase = 0; c->sort_on = false;            // a new tree: the reordering question is open again
 }
 
 static void free_scene(gpt_ctx* c)
@@ -132,25 +135,80 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     return GPT_OK;
 }
 
-// Ray reordering before the secondary extends (gpt_wavefront.cu, k_wf_sort_keys + CUB radix sort): pays on large scenes
-// (synthetic 2 M triangles: extend -22 %, frame +11 %; 20 M: +18 %), loses 4 % on the 1.6 M-triangle dragon and 30 % on the
-// 5 k-triangle bench scene (a sort costs ~37 ps per ray).  GPT_WF_SORT=0 never, =1..3 always (key layout), unset: from
-// GPT_SORT_MIN_TRIS (2 Mi) packed triangles up.  Images are bit-identical either way.
-static int ensure_sort(gpt_ctx* c)
+// Ray reordering before the secondary extends (gpt_wavefront.cu, k_wf_sort_keys + CUB radix sort, ~40 ps per ray).  Whether it
+// pays depends on the scene, not just on its size: synthetic 2 M / 20 M triangles gain 11 % / 18 % per frame, the 1.6 M-triangle
+// dragon in its box loses 15 %, the 5 k-triangle bench scene 30 % (profiles/r01_schedules.md #19-#24).  Images are bit-identical
+// either way.  Policy:
+//   GPT_WF_SORT=0 never; =1..9 always (key layout);
+//   GPT_SORT_MIN_TRIS=n: from n packed triangles up;
+//   otherwise: never below 256 Ki packed triangles; above, the first four large render calls after a scene upload are a
+//   trial -- warm-up and one timed call in path order, warm-up and one timed call re-ordered (these two calls synchronise) --
+//   and the faster order per ray is kept.
+enum { SORT_TRIAL_WARM_OFF = 0, SORT_TRIAL_TIME_OFF = 1, SORT_TRIAL_WARM_ON = 2, SORT_TRIAL_TIME_ON = 3, SORT_DECIDED = 4 };
+struct SortPlan { bool use; bool timed; bool trial; };
+static SortPlan sort_policy(gpt_ctx* c, size_t n_paths)
 {
     static const int env = []{ const char* e = getenv("GPT_WF_SORT"); return e ? atoi(e) : -1; }();
-    static const long long sort_min_tris = []{ const char* e = getenv("GPT_SORT_MIN_TRIS"); return e ? atoll(e) : (2ll << 20); }();
-    const bool want = c->nodes && !(c->flags & GPT_FLAG_MEGAKERNEL) && (env > 0 || (env < 0 && (long long)c->n_tris >= sort_min_tris));
+    static const long long min_tris = []{ const char* e = getenv("GPT_SORT_MIN_TRIS"); return e ? atoll(e) : -1ll; }();
+    SortPlan pl = {false, false, false};
+    if (!c->nodes || (c->flags & GPT_FLAG_MEGAKERNEL) || env == 0) return pl;
+    if (env > 0) { pl.use = true; return pl; }
+    if (min_tris >= 0) { pl.use = (long long)c->n_tris >= min_tris; return pl; }
+    if (c->n_tris < (256 << 10)) return pl;
+    if (c->sort_phase >= SORT_DECIDED) { pl.use = c->sort_on; return pl; }
+    if (n_paths < ((size_t)1 << 20)) return pl;                      // too small a call to judge by: path order, trial pending
+    pl.trial = true;
+    pl.use = c->sort_phase >= SORT_TRIAL_WARM_ON;
+    pl.timed = c->sort_phase == SORT_TRIAL_TIME_OFF || c->sort_phase == SORT_TRIAL_TIME_ON;
+    return pl;
+}
+
+static int ensure_sort(gpt_ctx* c, bool want)
+{
     WaveBuffers& w = c->wave;
-    if (want == (w.sort_vals != nullptr)) return GPT_OK;
+    if (!want || w.sort_vals != nullptr || w.capacity == 0) return GPT_OK;       // buffers are kept once allocated
     CU(c, cudaDeviceSynchronize());
-    cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp);
-    w.sort_keys[0] = w.sort_keys[1] = w.sort_vals = nullptr; w.sort_tmp = nullptr; w.sort_tmp_bytes = 0;
-    if (!want || w.capacity == 0) return GPT_OK;
     w.sort_tmp_bytes = gptk_wave_sort_tmp_bytes(w.capacity);
     CU(c, cudaMalloc(&w.sort_keys[0], w.capacity * sizeof(uint32_t))); CU(c, cudaMalloc(&w.sort_keys[1], w.capacity * sizeof(uint32_t)));
     CU(c, cudaMalloc(&w.sort_vals, w.capacity * sizeof(uint32_t)));
     CU(c, cudaMalloc(&w.sort_tmp, w.sort_tmp_bytes ? w.sort_tmp_bytes : 16));
+    return GPT_OK;
+}
+
+// one wavefront render call under the reordering policy (both contracts)
+static int render_wavefront(gpt_ctx* c, const DevScene& sc, const RenderParams& p, float4* accum_f4, float* accum_v3, uint32_t* draw,
+                            unsigned long long constant_pdf, unsigned long long sample_begin, uint32_t sample_count, cudaStream_t st)
+{
+    int rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, sample_count); if (rc) return rc;
+    const SortPlan pl = sort_policy(c, (size_t)p.width * p.height * sample_count);
+    rc = ensure_sort(c, pl.use); if (rc) return rc;
+    WaveBuffers wb = c->wave;
+    if (!pl.use) wb.sort_vals = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    unsigned long long rays0 = 0, rays1 = 0;
+    if (pl.timed) {
+        CU(c, cudaStreamSynchronize(st));
+        CU(c, cudaMemcpy(&rays0, c->stats, sizeof(rays0), cudaMemcpyDeviceToHost));
+        CU(c, cudaEventCreate(&e0)); CU(c, cudaEventCreate(&e1));
+        CU(c, cudaEventRecord(e0, st));
+    }
+    cudaError_t e = gptk_render_wavefront(sc, p, wb, accum_f4, accum_v3, draw, constant_pdf, sample_begin, sample_count,
+                                          c->stats, c->sm_count, st, &c->launches, (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);
+    if (e != cudaSuccess) { if (e0) { cudaEventDestroy(e0); cudaEventDestroy(e1); } return fail(c, GPT_ERR_CUDA, "render launch", e); }
+    if (pl.timed) {
+        float ms = 0.0f;
+        cudaEventRecord(e1, st);
+        e = cudaEventSynchronize(e1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+        if (e == cudaSuccess) e = cudaMemcpy(&rays1, c->stats, sizeof(rays1), cudaMemcpyDeviceToHost);
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "reordering trial", e);
+        c->sort_trial_ns_per_ray[pl.use ? 1 : 0] = rays1 > rays0 ? (double)ms * 1e6 / (double)(rays1 - rays0) : 0.0;
+    }
+    if (pl.trial && ++c->sort_phase == SORT_DECIDED) {
+        const double off = c->sort_trial_ns_per_ray[0], on = c->sort_trial_ns_per_ray[1];
+        c->sort_on = on > 0.0 && off > 0.0 && on < 0.97 * off;
+    }
     return GPT_OK;
 }
 
@@ -387,6 +445,16 @@ static void uploaded_scene(gpt_ctx* c, DevScene* sc)
     sc->tri_mats = c->tri_mats; sc->face_mat = c->face_mat; sc->n_tri_mats = c->n_tri_mats; sc->n_faces = c->n_faces;
 }
 
+int gpt_reorder_info(gpt_ctx* c, int* state, double* ns_per_ray_path_order, double* ns_per_ray_reordered)
+{
+    if (!c) return GPT_ERR_INVALID;
+    const SortPlan pl = sort_policy(c, (size_t)1 << 30);
+    if (state) *state = pl.trial ? -1 : (pl.use ? 1 : 0);
+    if (ns_per_ray_path_order) *ns_per_ray_path_order = c->sort_trial_ns_per_ray[0];
+    if (ns_per_ray_reordered) *ns_per_ray_reordered = c->sort_trial_ns_per_ray[1];
+    return GPT_OK;
+}
+
 int gpt_wide_info(gpt_ctx* c, int* n_wide, int* levels)
 {
     if (!c) return GPT_ERR_INVALID;
@@ -434,11 +502,7 @@ int gpt_launch(gpt_ctx* c, const gpt_kernel_info* info, gpt_stream stream)
     rc = launch_scene(c, info, &sc); if (rc) return rc;
     cudaError_t e;
     if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
-        rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, 1u); if (rc) return rc;
-        rc = ensure_sort(c); if (rc) return rc;
-        e = gptk_render_wavefront(sc, p, c->wave, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u,
-                                  c->stats, c->sm_count, (cudaStream_t)stream, &c->launches,
-                                  (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);
+        return render_wavefront(c, sc, p, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u, (cudaStream_t)stream);
     } else {
         e = gptk_render_legacy(sc, p, info->accumBuffer, info->dev_drawRes, info->constantPdf,
                                c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
@@ -459,11 +523,7 @@ int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_
     rc = launch_scene(c, info, &sc); if (rc) return rc;
     cudaError_t e;
     if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
-        rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, sample_count); if (rc) return rc;
-        rc = ensure_sort(c); if (rc) return rc;
-        e = gptk_render_wavefront(sc, p, c->wave, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count,
-                                  c->stats, c->sm_count, (cudaStream_t)stream, &c->launches,
-                                  (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);
+        return render_wavefront(c, sc, p, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count, (cudaStream_t)stream);
     } else {
         e = gptk_render_mega(sc, p, reinterpret_cast<float4*>(accum_f4), sample_begin, sample_count,
                              c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);

@@ -433,17 +433,17 @@ __device__ __forceinline__ unsigned wf_spread10(unsigned v)      // 10 bits -> e
     v &= 0x3ffu; v = (v | (v << 16)) & 0x030000ffu; v = (v | (v << 8)) & 0x0300f00fu; v = (v | (v << 4)) & 0x030c30c3u; v = (v | (v << 2)) & 0x09249249u;
     return v;
 }
-__host__ __device__ __forceinline__ int wf_sort_bits(const int mode) { return mode >= 3 ? 30 : 24; }
+__host__ __device__ __forceinline__ int wf_sort_bits(const int mode) { return mode >= 8 ? 16 : mode >= 3 ? 30 : 24; }
 // key = Morton cell of the origin (ob bits per axis of the mesh bounds) above Morton cell of the direction (db bits per axis):
-// mode 1: 7 + 1 (octant) = 24 bits   mode 2: 6 + 2 = 24   mode 3: 7 + 3 = 30   mode 4: 9 + 1 = 30   mode 5: 8 + 2 = 30   mode 6: 6 + 4 = 30   mode 7: 5 + 5 = 30
+// mode 1: 7 + 1 (octant) = 24 bits   mode 2: 6 + 2 = 24   mode 3: 7 + 3 = 30   mode 4: 9 + 1 = 30   mode 5: 8 + 2 = 30   mode 6: 6 + 4 = 30   mode 7: 5 + 5 = 30   mode 8: 4 + 1 = 15 (two radix passes)   mode 9: 3 + 2 = 15
 __global__ void __launch_bounds__(256)
 k_wf_sort_keys(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr, const unsigned n_slots,
                const float4* __restrict__ ray_o, const float4* __restrict__ ray_d, uint32_t* __restrict__ keys, const int mode)
 {
     const unsigned n = *n_ptr;
     const unsigned kmax = 0xffffffffu >> (32 - wf_sort_bits(mode));
-    const int ob = mode == 1 ? 7 : mode == 2 ? 6 : mode == 3 ? 7 : mode == 4 ? 9 : mode == 5 ? 8 : mode == 6 ? 6 : 5;
-    const int db = mode == 1 ? 1 : mode == 2 ? 2 : mode == 3 ? 3 : mode == 4 ? 1 : mode == 5 ? 2 : mode == 6 ? 4 : 5;
+    const int ob = mode == 1 ? 7 : mode == 2 ? 6 : mode == 3 ? 7 : mode == 4 ? 9 : mode == 5 ? 8 : mode == 6 ? 6 : mode == 7 ? 5 : mode == 8 ? 4 : 3;
+    const int db = mode == 1 ? 1 : mode == 2 ? 2 : mode == 3 ? 3 : mode == 4 ? 1 : mode == 5 ? 2 : mode == 6 ? 4 : mode == 7 ? 5 : mode == 8 ? 1 : 2;
     // mesh bounds = union of the root's two child boxes
     const float4 n0 = __ldg(sc.nodes), n1 = __ldg(sc.nodes + 1), nz = __ldg(sc.nodes + 2);
     const float lox = fminf(n0.x, n1.x), hix = fmaxf(n0.y, n1.y), loy = fminf(n0.z, n1.z), hiy = fmaxf(n0.w, n1.w);
@@ -500,7 +500,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_extend_ww<true, true>, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
         wide_grid = sm_count * per_sm;
     }
-    static const int sort_mode = []{ const int m = wf_knob("GPT_WF_SORT", 3); return m > 7 ? 7 : m; }();
+    static const int sort_mode = []{ const int m = wf_knob("GPT_WF_SORT", 3); return m > 9 ? 9 : m; }();
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
     const int n_pix = p.width * p.height;
     // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays

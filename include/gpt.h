@@ -239,6 +239,10 @@ GPT_API int gpt_reset_stats(gpt_ctx* ctx);
 /* The 4-wide tree in use (built lazily by the first launch that wants it): *n_wide = nodes (0 = binary tree in use),
  * *levels = wide levels.  Returns GPT_OK, or the error of the build. */
 GPT_API int gpt_wide_info(gpt_ctx* ctx, int* n_wide, int* levels);
+/* Ray reordering before the secondary extends (images are bit-identical with and without): *state = 1 on, 0 off,
+ * -1 still on trial (the first four large render calls after a scene upload time both orders when neither GPT_WF_SORT nor
+ * GPT_SORT_MIN_TRIS is set and the scene has >= 256 Ki packed triangles); the two figures are the trial's whole-call times. */
+GPT_API int gpt_reorder_info(gpt_ctx* ctx, int* state, double* ns_per_ray_path_order, double* ns_per_ray_reordered);
 GPT_API int gpt_get_kernel_times(gpt_ctx* ctx, gpt_kernel_times* out);  /* synchronises; see GPT_FLAG_TIME_KERNELS */
 
 /* ---- host-side helpers mirroring the reference's scene setup (no GPU needed) ---- */

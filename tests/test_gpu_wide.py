@@ -133,3 +133,40 @@ def test_wide_on_built_lbvh_large_scene(gpt, torch_cuda):
     # order changes, so the frame still equals the oracle's on the built arrays, pixel for pixel
     want = scenes.oracle_render(host_scene, gpt.default_spheres(), info, 5, 0, 2)
     assert np.any(frames[1] != want, axis=-1).mean() <= 1e-3
+
+
+def test_reordering_trial_runs_and_keeps_images(gpt, torch_cuda, tmp_path):
+    """Without GPT_WF_SORT / GPT_SORT_MIN_TRIS in the environment (a fresh process: both are read once) a scene of >= 256 Ki
+    triangles goes through the four-call trial -- warm-up + timed call in path order, warm-up + timed call re-ordered -- and then
+    reports a decision; the SAME samples rendered in path order (call 2) and re-ordered (call 4) give bit-identical frames."""
+    import json
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import json, sys, numpy as np, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import gpt_b200 as gpt
+from support import procedural
+v, f = procedural.synthetic_scene(300000, seed=9)
+info = gpt.default_kernel_info(1024, 1024); info.depth = 4; info.cam.dist = 12.0 * 1024 / 720.0
+with gpt.Context(0) as ctx:
+    b = ctx.build_bvh(v, f); ctx.upload_built(b, gpt.default_spheres())
+    states, frames = [ctx.reorder_info()[0]], []
+    for call in range(5):
+        acc = torch.zeros(1024, 1024, 4, dtype=torch.float32, device="cuda")
+        ctx.render(info, acc, 3, 0, 1)                  # the same sample every call
+        torch.cuda.synchronize()
+        frames.append(acc.cpu().numpy()); states.append(ctx.reorder_info()[0])
+    st, off, on = ctx.reorder_info()
+    print(json.dumps({"states": states, "off": off, "on": on, "same": bool(all(np.array_equal(frames[0], x) for x in frames[1:])),
+                      "lit": float(frames[0][..., :3].max())}))
+    ctx.free_bvh(b)
+''' % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if k not in ("GPT_WF_SORT", "GPT_SORT_MIN_TRIS")}
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    r = json.loads(out.stdout.strip().splitlines()[-1])
+    assert r["states"][:4] == [-1, -1, -1, -1] and r["states"][4] in (0, 1) and r["states"][5] == r["states"][4], r
+    assert r["off"] > 0.0 and r["on"] > 0.0, r
+    assert r["same"] and r["lit"] > 0.0, r
