@@ -53,6 +53,17 @@ def load_algo_bytes():
     return a["bytes_per_ray"], trav
 
 
+def load_issue_profile():
+    """warp instructions, lanes per instruction and issue-slot utilisation of one k_wf_extend_ww launch from the same committed
+    ncu capture (profiles/r01_traffic.json), or None."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as fh:
+        d = json.load(fh).get("k_wf_extend_ww", {})
+    return d if "warp_instructions" in d else None
+
+
 def load_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum of one k_wf_extend_ww launch from the committed `ncu --set full`
     capture of this same command (profiles/r01_traffic.json), or None."""
@@ -494,6 +505,19 @@ def run_ours(args):
                                  "of HBM peak; the binding resource is issue slots x SIMT efficiency (profiles/)"},
             "clocks": sampler.summary(),
         }
+        ip = load_issue_profile()
+        if ip is not None and kname == "k_wf_extend_ww":
+            # second view of the same kernel: the resource that actually binds it.  Peak = 4 warp instructions per SM per clock.
+            sm_count = torch.cuda.get_device_properties(0).multi_processor_count
+            mhz = (line["clocks"] or {}).get("sm_mhz") or 1965.0
+            peak = sm_count * 4 * mhz * 1e6
+            per_ray = ip["warp_instructions"] / 33177011.875
+            ach = per_ray * rays_per_launch / (k_avg_ms * 1e-3)
+            line["roofline"]["issue"] = {"bound": "issue slots", "warp_instructions_per_ray": per_ray, "lanes_per_instruction": ip["lanes_per_instruction"],
+                                         "achieved": ach / 1e12, "peak": peak / 1e12, "unit": "T warp-inst/s", "frac": ach / peak,
+                                         "ncu_issue_active_pct": ip["issue_active_pct"],
+                                         "what": "warp instructions per ray from the committed ncu capture x rays per launch / live launch time, against "
+                                                 "SMs x 4 schedulers x SM clock; the fraction the HBM figure cannot show"}
         if world == 1 and not args.no_cpu_baseline:
             base, port = cpu_baseline(gpt, sc, args)
             line["cpu_baseline"] = base
