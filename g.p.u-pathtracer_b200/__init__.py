@@ -93,7 +93,7 @@ assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 # every symbol include/gpt.h declares (tests check the library exports each one)
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
            "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
-           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_wide_info", "gpt_reorder_info",
+           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
            "gpt_reduce_resolve_ptrs", "gpt_frame_free",
@@ -133,6 +133,7 @@ def load_library():
     L.gpt_get_kernel_times.argtypes = [C.c_void_p, C.POINTER(KernelTimes)]
     L.gpt_wide_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.gpt_reorder_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.gpt_trial_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double)]
     L.gpt_build_bvh.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.POINTER(BuiltBVH)]
     L.gpt_free_bvh.argtypes = [C.c_void_p, C.POINTER(BuiltBVH)]
     L.gpt_copy_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
@@ -463,6 +464,13 @@ class Context:
         st, a, b = C.c_int(0), C.c_double(0.0), C.c_double(0.0)
         self._ck(self._L.gpt_reorder_info(self._h, C.byref(st), C.byref(a), C.byref(b)), "gpt_reorder_info")
         return st.value, a.value, b.value
+
+    def trial_info(self):
+        """(pending, [ns/ray binary tree, ns/ray wide tree, ns/ray chosen tree re-ordered]) of the per-scene trial."""
+        pend = C.c_int(0)
+        ns = (C.c_double * 3)()
+        self._ck(self._L.gpt_trial_info(self._h, C.byref(pend), ns), "gpt_trial_info")
+        return bool(pend.value), [ns[0], ns[1], ns[2]]
 
     def kernel_times(self):
         """{class name: (ms, launches)} since the last reset_stats (needs FLAG_TIME_KERNELS)."""

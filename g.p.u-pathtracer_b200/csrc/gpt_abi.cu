@@ -23,8 +23,9 @@ struct gpt_ctx {
     bool has_scene = false;
     // N3: 4-wide quantised tree over the packed binary one, built on first use (gpt_wide.cu)
     float4* wnodes = nullptr; int n_wide = 0, wide_levels = 0; bool wide_tried = false;
-    // ray reordering (gpt_wavefront.cu): decided per scene, by environment, size threshold or a four-call trial (sort_policy)
-    int sort_phase = 0; bool sort_on = false; double sort_trial_ns_per_ray[2] = {0.0, 0.0};
+    // per-scene choice of traversal structure and ray order (traversal_plan): flags and environment win, else a timed trial
+    int tune_step = 0; bool tune_done = false; bool tuned_wide = false, tuned_sort = false;
+    double tune_ns[3] = {0.0, 0.0, 0.0};          // ns per ray: binary tree / wide tree in path order, chosen tree re-ordered
     // identity of the reference arrays the packed BVH was built from (gpt_launch re-packs on change)
     const void* src_nodes = nullptr; const void* src_tris = nullptr; const void* src_idx = nullptr;
     size_t src_n_nodes = 0, src_n_tris = 0, src_n_idx = 0;
@@ -88,7 +89,8 @@ int gpt_create(gpt_ctx** out, int device)
 static void free_wide(gpt_ctx* c)
 {
     cudaFree(c->wnodes); c->wnodes = nullptr; c->n_wide = 0; c->wide_levels = 0; c->wide_tried = false;
-    c->sort_phase = 0; c->sort_on = false;            // a new tree: the reordering question is open again
+    c->tune_step = 0; c->tune_done = false; c->tuned_wide = c->tuned_sort = false;      // a new tree: the questions are open again
+    c->tune_ns[0] = c->tune_ns[1] = c->tune_ns[2] = 0.0;
 }
 
 static void free_scene(gpt_ctx* c)
@@ -135,32 +137,83 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     return GPT_OK;
 }
 
-// Ray reordering before the secondary extends (gpt_wavefront.cu, k_wf_sort_keys + CUB radix sort, ~40 ps per ray).  Whether it
-// pays depends on the scene, not just on its size: synthetic 2 M / 20 M triangles gain 11 % / 18 % per frame, the 1.6 M-triangle
-// dragon in its box loses 15 %, the 5 k-triangle bench scene 30 % (profiles/r01_schedules.md #19-#24).  Images are bit-identical
-// either way.  Policy:
-//   GPT_WF_SORT=0 never; =1..9 always (key layout);
-//   GPT_SORT_MIN_TRIS=n: from n packed triangles up;
-//   otherwise: never below 256 Ki packed triangles; above, the first four large render calls after a scene upload are a
-//   trial -- warm-up and one timed call in path order, warm-up and one timed call re-ordered (these two calls synchronise) --
-//   and the faster order per ray is kept.
-enum { SORT_TRIAL_WARM_OFF = 0, SORT_TRIAL_TIME_OFF = 1, SORT_TRIAL_WARM_ON = 2, SORT_TRIAL_TIME_ON = 3, SORT_DECIDED = 4 };
-struct SortPlan { bool use; bool timed; bool trial; };
-static SortPlan sort_policy(gpt_ctx* c, size_t n_paths)
+// ---- which tree, which ray order -------------------------------------------------------------------------------------------
+// Two choices change nothing in the image and a lot in the frame time, and neither follows from the triangle count alone
+// (profiles/r01_schedules.md #15-#25): the 4-wide quantised tree (gpt_wide.cu) against the binary tree as uploaded -- -10 % on a
+// 100 k-triangle dragon in a box, +3 % on 250 k triangles that fill space, +40 % at 20 M -- and re-ordering the secondary rays
+// before each extend (gpt_wavefront.cu, ~40 ps per ray) -- +11 % for the binary tree on 2 M space-filling triangles, -15 % on
+// the 1.6 M-triangle dragon.  Policy, per dimension:
+//   tree : GPT_FLAG_BINARY_BVH / GPT_FLAG_WIDE_BVH force it; GPT_WIDE_MIN_TRIS=n sets a size threshold; the megakernel and
+//          scenes under 64 Ki packed triangles use the binary tree; otherwise it is put on trial (default until decided:
+//          wide from 1 Mi triangles);
+//   order: GPT_WF_SORT=0 never, =1..9 always (key layout); GPT_SORT_MIN_TRIS=n a size threshold; never under 256 Ki packed
+//          triangles; otherwise on trial (default until decided: path order).
+// Trial: the first large render calls (>= 1 Mi paths) after a scene upload run each open candidate twice -- one warm-up call, one
+// timed call bracketed by events and a stream synchronise -- binary / path order, wide / path order, then the faster tree
+// re-ordered; ns per ray decide (the wide tree must win by 2 %, re-ordering by 3 %).  At most six calls synchronise.
+static const long long k_env_wide_min = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : -2ll; }();   // -2 = unset
+static const int k_env_sort = []{ const char* e = getenv("GPT_WF_SORT"); return e ? atoi(e) : -1; }();
+static const long long k_env_sort_min = []{ const char* e = getenv("GPT_SORT_MIN_TRIS"); return e ? atoll(e) : -2ll; }();
+
+// 0 = binary, 1 = wide, -1 = open (trial)
+static int tree_choice(const gpt_ctx* c)
 {
-    static const int env = []{ const char* e = getenv("GPT_WF_SORT"); return e ? atoi(e) : -1; }();
-    static const long long min_tris = []{ const char* e = getenv("GPT_SORT_MIN_TRIS"); return e ? atoll(e) : -1ll; }();
-    SortPlan pl = {false, false, false};
-    if (!c->nodes || (c->flags & GPT_FLAG_MEGAKERNEL) || env == 0) return pl;
-    if (env > 0) { pl.use = true; return pl; }
-    if (min_tris >= 0) { pl.use = (long long)c->n_tris >= min_tris; return pl; }
-    if (c->n_tris < (256 << 10)) return pl;
-    if (c->sort_phase >= SORT_DECIDED) { pl.use = c->sort_on; return pl; }
-    if (n_paths < ((size_t)1 << 20)) return pl;                      // too small a call to judge by: path order, trial pending
-    pl.trial = true;
-    pl.use = c->sort_phase >= SORT_TRIAL_WARM_ON;
-    pl.timed = c->sort_phase == SORT_TRIAL_TIME_OFF || c->sort_phase == SORT_TRIAL_TIME_ON;
+    if (!c->nodes || c->n_nodes <= 0 || (c->flags & (GPT_FLAG_BINARY_BVH | GPT_FLAG_MEGAKERNEL))) return 0;
+    if (c->wide_tried && !c->wnodes) return 0;                    // the tree could not be quantised: binary, same results
+    if (c->flags & GPT_FLAG_WIDE_BVH) return 1;
+    if (k_env_wide_min != -2) return k_env_wide_min >= 0 && (long long)c->n_tris >= k_env_wide_min ? 1 : 0;
+    if (c->n_tris < (64 << 10)) return 0;
+    return -1;
+}
+static int sort_choice(const gpt_ctx* c)
+{
+    if (!c->nodes || (c->flags & GPT_FLAG_MEGAKERNEL) || k_env_sort == 0) return 0;
+    if (k_env_sort > 0) return 1;
+    if (k_env_sort_min != -2) return k_env_sort_min >= 0 && (long long)c->n_tris >= k_env_sort_min ? 1 : 0;
+    if (c->n_tris < (256 << 10)) return 0;
+    return -1;
+}
+// what to use outside a trial call: forced, decided, or the default
+static bool current_wide(const gpt_ctx* c)
+{
+    const int t = tree_choice(c);
+    return t >= 0 ? t == 1 : (c->tune_done ? c->tuned_wide : c->n_tris >= (1 << 20));
+}
+static bool current_sort(const gpt_ctx* c)
+{
+    const int s = sort_choice(c);
+    return s >= 0 ? s == 1 : (c->tune_done && c->tuned_sort);
+}
+
+struct TraversalPlan { bool wide; bool sort; bool trial; bool timed; int slot; };     // slot = tune_ns index of a timed call
+static TraversalPlan traversal_plan(const gpt_ctx* c, size_t n_paths)
+{
+    TraversalPlan pl = {current_wide(c), current_sort(c), false, false, -1};
+    const int t = tree_choice(c), s = sort_choice(c);
+    const int n_tree = t < 0 ? 2 : 1, n_cand = n_tree + (s < 0 ? 1 : 0);
+    if (c->tune_done || n_cand < 2 || n_paths < ((size_t)1 << 20)) return pl;
+    const int cand = c->tune_step / 2;
+    pl.trial = true; pl.timed = (c->tune_step & 1) != 0;
+    if (cand < n_tree) {                                          // a tree candidate, rays in path order
+        pl.wide = t < 0 ? cand == 1 : t == 1;
+        pl.sort = false;
+        pl.slot = pl.wide ? 1 : 0;
+    } else {                                                      // the faster tree, re-ordered
+        pl.wide = t < 0 ? (c->tune_ns[1] > 0.0 && c->tune_ns[1] < 0.98 * c->tune_ns[0]) : t == 1;
+        pl.sort = true;
+        pl.slot = 2;
+    }
     return pl;
+}
+static void trial_advance(gpt_ctx* c)
+{
+    const int t = tree_choice(c), s = sort_choice(c);
+    const int n_tree = t < 0 ? 2 : 1, n_cand = n_tree + (s < 0 ? 1 : 0);
+    if (++c->tune_step < 2 * n_cand) return;
+    c->tune_done = true;
+    c->tuned_wide = t < 0 ? (c->tune_ns[1] > 0.0 && c->tune_ns[0] > 0.0 && c->tune_ns[1] < 0.98 * c->tune_ns[0]) : t == 1;
+    const double path = c->tune_ns[c->tuned_wide ? 1 : 0];
+    c->tuned_sort = s < 0 && c->tune_ns[2] > 0.0 && path > 0.0 && c->tune_ns[2] < 0.97 * path;
 }
 
 static int ensure_sort(gpt_ctx* c, bool want)
@@ -175,15 +228,17 @@ static int ensure_sort(gpt_ctx* c, bool want)
     return GPT_OK;
 }
 
-// one wavefront render call under the reordering policy (both contracts)
-static int render_wavefront(gpt_ctx* c, const DevScene& sc, const RenderParams& p, float4* accum_f4, float* accum_v3, uint32_t* draw,
+// one wavefront render call under that policy (both contracts)
+static int render_wavefront(gpt_ctx* c, const DevScene& sc_in, const RenderParams& p, float4* accum_f4, float* accum_v3, uint32_t* draw,
                             unsigned long long constant_pdf, unsigned long long sample_begin, uint32_t sample_count, cudaStream_t st)
 {
     int rc = ensure_wave(c, (size_t)p.width * p.height, p.depth, sample_count); if (rc) return rc;
-    const SortPlan pl = sort_policy(c, (size_t)p.width * p.height * sample_count);
-    rc = ensure_sort(c, pl.use); if (rc) return rc;
+    const TraversalPlan pl = traversal_plan(c, (size_t)p.width * p.height * sample_count);
+    rc = ensure_sort(c, pl.sort); if (rc) return rc;
+    DevScene sc = sc_in;
+    sc.wnodes = pl.wide ? c->wnodes : nullptr;
     WaveBuffers wb = c->wave;
-    if (!pl.use) wb.sort_vals = nullptr;
+    if (!pl.sort) wb.sort_vals = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     unsigned long long rays0 = 0, rays1 = 0;
     if (pl.timed) {
@@ -202,13 +257,10 @@ static int render_wavefront(gpt_ctx* c, const DevScene& sc, const RenderParams& 
         if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
         if (e == cudaSuccess) e = cudaMemcpy(&rays1, c->stats, sizeof(rays1), cudaMemcpyDeviceToHost);
         cudaEventDestroy(e0); cudaEventDestroy(e1);
-        if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "reordering trial", e);
-        c->sort_trial_ns_per_ray[pl.use ? 1 : 0] = rays1 > rays0 ? (double)ms * 1e6 / (double)(rays1 - rays0) : 0.0;
+        if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "traversal trial", e);
+        c->tune_ns[pl.slot] = rays1 > rays0 ? (double)ms * 1e6 / (double)(rays1 - rays0) : 0.0;
     }
-    if (pl.trial && ++c->sort_phase == SORT_DECIDED) {
-        const double off = c->sort_trial_ns_per_ray[0], on = c->sort_trial_ns_per_ray[1];
-        c->sort_on = on > 0.0 && off > 0.0 && on < 0.97 * off;
-    }
+    if (pl.trial) trial_advance(c);
     return GPT_OK;
 }
 
@@ -410,22 +462,11 @@ static int make_params(gpt_ctx* c, const gpt_kernel_info* info, uint64_t seed, R
     return GPT_OK;
 }
 
-// does this context traverse the 4-wide tree?  (flags win; else by size, see include/gpt.h)
-static bool wide_wanted(const gpt_ctx* c)
-{
-    if (!c->nodes || c->n_nodes <= 0 || (c->flags & GPT_FLAG_BINARY_BVH) || (c->flags & GPT_FLAG_MEGAKERNEL)) return false;
-    if (c->flags & GPT_FLAG_WIDE_BVH) return true;
-    // measured on B200 (profiles/r01_schedules.md #15/#19/#23): the wide tree loses 3-9 % up to 100 k triangles, wins 4 % at
-    // 1.6 M (rays in path order), 6 % at 2 M, 10 % at 5 M and 24 % at 20 M (rays re-ordered).  Default: from 1 Mi packed triangles.
-    static const long long min_tris = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : (1ll << 20); }();
-    return min_tris >= 0 && (long long)c->n_tris >= min_tris;
-}
-
-// builds the wide tree on first use; a tree that cannot be quantised (non-finite boxes) or is too deep for the wide
-// stack silently keeps the binary traversal -- same results either way
+// builds the wide tree when it is forced or a candidate; a tree that cannot be quantised (non-finite boxes) or is too deep for
+// the wide stack keeps the binary traversal -- same results either way
 static void ensure_wide(gpt_ctx* c)
 {
-    if (c->wnodes || c->wide_tried || !wide_wanted(c)) return;
+    if (c->wnodes || c->wide_tried || tree_choice(c) == 0) return;
     c->wide_tried = true;
     WideResult w;
     if (cudaDeviceSynchronize() != cudaSuccess) return;
@@ -438,7 +479,7 @@ static void ensure_wide(gpt_ctx* c)
 static void uploaded_scene(gpt_ctx* c, DevScene* sc)
 {
     ensure_wide(c);
-    sc->wnodes = wide_wanted(c) ? c->wnodes : nullptr;
+    sc->wnodes = current_wide(c) ? c->wnodes : nullptr;          // render calls refine this per call (render_wavefront)
     sc->nodes = c->nodes; sc->tris = c->tris; sc->n_nodes = c->n_nodes; sc->n_tris = c->n_tris;
     sc->spheres = c->spheres; sc->n_spheres = c->n_spheres;
     sc->boxes = c->boxes; sc->n_boxes = c->n_boxes;
@@ -448,10 +489,18 @@ static void uploaded_scene(gpt_ctx* c, DevScene* sc)
 int gpt_reorder_info(gpt_ctx* c, int* state, double* ns_per_ray_path_order, double* ns_per_ray_reordered)
 {
     if (!c) return GPT_ERR_INVALID;
-    const SortPlan pl = sort_policy(c, (size_t)1 << 30);
-    if (state) *state = pl.trial ? -1 : (pl.use ? 1 : 0);
-    if (ns_per_ray_path_order) *ns_per_ray_path_order = c->sort_trial_ns_per_ray[0];
-    if (ns_per_ray_reordered) *ns_per_ray_reordered = c->sort_trial_ns_per_ray[1];
+    const TraversalPlan pl = traversal_plan(c, (size_t)1 << 30);
+    if (state) *state = (pl.trial && sort_choice(c) < 0) ? -1 : (current_sort(c) ? 1 : 0);
+    if (ns_per_ray_path_order) *ns_per_ray_path_order = c->tune_ns[(c->tune_done ? c->tuned_wide : current_wide(c)) ? 1 : 0];
+    if (ns_per_ray_reordered) *ns_per_ray_reordered = c->tune_ns[2];
+    return GPT_OK;
+}
+
+int gpt_trial_info(gpt_ctx* c, int* pending, double ns_per_ray[3])
+{
+    if (!c) return GPT_ERR_INVALID;
+    if (pending) *pending = traversal_plan(c, (size_t)1 << 30).trial ? 1 : 0;
+    if (ns_per_ray) { ns_per_ray[0] = c->tune_ns[0]; ns_per_ray[1] = c->tune_ns[1]; ns_per_ray[2] = c->tune_ns[2]; }
     return GPT_OK;
 }
 
@@ -460,7 +509,7 @@ int gpt_wide_info(gpt_ctx* c, int* n_wide, int* levels)
     if (!c) return GPT_ERR_INVALID;
     CU(c, cudaSetDevice(c->device));
     ensure_wide(c);
-    const bool on = wide_wanted(c) && c->wnodes;
+    const bool on = current_wide(c) && c->wnodes;
     if (n_wide) *n_wide = on ? c->n_wide : 0;
     if (levels) *levels = on ? c->wide_levels : 0;
     return GPT_OK;

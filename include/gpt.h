@@ -103,9 +103,10 @@ enum {
      * uploaded (CudaBVH.cpp:121-270; visit order and therefore ties identical to cudaUtils.h:298-448).  Alternative: a
      * 4-wide tree with 8-bit quantised child boxes collapsed from it on the device (64 B per four children).  Same
      * nearest hit (t, face index); between two copies of a spatially split triangle -- bit-equal t -- the reported slot
-     * may be the other copy.  Measured on B200: slower than the binary tree on small and medium scenes,
-     * faster from about a million triangles up, so the default picks it from 1 Mi packed
-     * triangles (GPT_WIDE_MIN_TRIS in the environment moves the threshold); the two flags force either structure. */
+     * may be the other copy.  Measured on B200: slower than the binary tree on small scenes and on compact
+     * objects in a box, faster on scenes that fill space and on anything large.  Unless one of the two flags or
+     * GPT_WIDE_MIN_TRIS in the environment decides, scenes from 64 Ki packed triangles up are put on a timed trial during
+     * their first large render calls (gpt_trial_info); until it ends the wide tree is used from 1 Mi triangles. */
     GPT_FLAG_WIDE_BVH   = 1u << 5,   /* always the 4-wide tree */
     GPT_FLAG_BINARY_BVH = 1u << 6    /* always the binary tree */
 };
@@ -240,9 +241,13 @@ GPT_API int gpt_reset_stats(gpt_ctx* ctx);
  * *levels = wide levels.  Returns GPT_OK, or the error of the build. */
 GPT_API int gpt_wide_info(gpt_ctx* ctx, int* n_wide, int* levels);
 /* Ray reordering before the secondary extends (images are bit-identical with and without): *state = 1 on, 0 off,
- * -1 still on trial (the first four large render calls after a scene upload time both orders when neither GPT_WF_SORT nor
- * GPT_SORT_MIN_TRIS is set and the scene has >= 256 Ki packed triangles); the two figures are the trial's whole-call times. */
+ * -1 still on trial (scenes of >= 256 Ki packed triangles, when neither GPT_WF_SORT nor GPT_SORT_MIN_TRIS is set: part of the
+ * trial gpt_trial_info describes); the two figures are the trial's whole-call times for the tree in use. */
 GPT_API int gpt_reorder_info(gpt_ctx* ctx, int* state, double* ns_per_ray_path_order, double* ns_per_ray_reordered);
+/* The per-scene trial behind both choices (tree and ray order): *pending = 1 while large render calls are still being timed;
+ * ns_per_ray = whole-call ns per ray of the timed calls so far: [0] binary tree, [1] 4-wide tree (both in path order),
+ * [2] the faster tree with rays re-ordered; 0 = not measured (candidate forced, closed, or not reached yet). */
+GPT_API int gpt_trial_info(gpt_ctx* ctx, int* pending, double ns_per_ray[3]);
 GPT_API int gpt_get_kernel_times(gpt_ctx* ctx, gpt_kernel_times* out);  /* synchronises; see GPT_FLAG_TIME_KERNELS */
 
 /* ---- host-side helpers mirroring the reference's scene setup (no GPU needed) ---- */

@@ -29,7 +29,7 @@ def run(name, v, f, W, H, spp_total, mat, per_frame=16):
         acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
         rgba = torch.zeros(H, W, dtype=torch.int32, device="cuda")
         host = torch.zeros(H, W, dtype=torch.int32).pin_memory()
-        for r in range(5):                                  # warm-up + reordering trial, not part of the image
+        for r in range(7):                                  # warm-up + per-scene trial, not part of the image
             ctx.render(info, acc, 99, 10_000_000 + r * per_frame, per_frame)
         torch.cuda.synchronize()
         acc.zero_(); ctx.reset_stats()

@@ -24,13 +24,12 @@ def run(name, v, f, W, H, spp):
         ctx.upload_built(b, gpt.default_spheres())
         acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
         states = []
-        for r in range(5):
+        for r in range(7):
             ctx.render(info, acc, 0, 1000 + r * spp, spp)
-            states.append(ctx.reorder_info()[0])
+            states.append(int(ctx.trial_info()[0]))
         st, off, on = ctx.reorder_info()
         ms, rays, kt = time_ours(ctx, info, spp)
-        d = {"scene": name, "triangles": int(len(f)), "trial_states": states, "decision": st, "trial_ns_per_ray_path_order": off,
-             "trial_ns_per_ray_reordered": on, "wide_nodes": ctx.wide_info()[0], "Mrays_per_s": rays / ms / 1e3, "extend_ms": kt.get("extend"), "other_ms": kt.get("other")}
+        d = {"scene": name, "triangles": int(len(f)), "trial_pending_after_each_call": states, "reorder": st, "trial_ns_per_ray": ctx.trial_info()[1], "wide_nodes": ctx.wide_info()[0], "Mrays_per_s": rays / ms / 1e3, "extend_ms": kt.get("extend"), "other_ms": kt.get("other")}
         print(json.dumps(d), flush=True)
         with open(os.path.join(ROOT, "gpurun_out", "reorder_trial.jsonl"), "a") as fh:
             fh.write(json.dumps(d) + "\n")

@@ -22,10 +22,10 @@ with gpt.Context(0, gpt.FLAG_TIME_KERNELS | (gpt.FLAG_WIDE_BVH if kind == "wide"
     ctx.upload_built(b, gpt.default_spheres())
     print("wide_info", ctx.wide_info())
     acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
-    for r in range(5):                       # warm-up; also lets the reordering trial (4 calls) finish
+    for r in range(7):                       # warm-up; also lets the per-scene trial (up to 6 calls) finish
         ctx.render(info, acc, 0, 100 + r * spp, spp)
     torch.cuda.synchronize()
-    print("reorder_info", ctx.reorder_info())
+    print("reorder_info", ctx.reorder_info(), "trial", ctx.trial_info(), "wide", ctx.wide_info())
     ctx.reset_stats()
     ctx.render(info, acc, 0, spp, spp)
     torch.cuda.synchronize()

@@ -135,10 +135,11 @@ def test_wide_on_built_lbvh_large_scene(gpt, torch_cuda):
     assert np.any(frames[1] != want, axis=-1).mean() <= 1e-3
 
 
-def test_reordering_trial_runs_and_keeps_images(gpt, torch_cuda, tmp_path):
-    """Without GPT_WF_SORT / GPT_SORT_MIN_TRIS in the environment (a fresh process: both are read once) a scene of >= 256 Ki
-    triangles goes through the four-call trial -- warm-up + timed call in path order, warm-up + timed call re-ordered -- and then
-    reports a decision; the SAME samples rendered in path order (call 2) and re-ordered (call 4) give bit-identical frames."""
+def test_traversal_trial_runs_and_keeps_images(gpt, torch_cuda, tmp_path):
+    """Without GPT_WF_SORT / GPT_SORT_MIN_TRIS / GPT_WIDE_MIN_TRIS in the environment (a fresh process: they are read once) a scene
+    of >= 256 Ki triangles goes through the six-call trial -- warm-up + timed call for the binary tree, the wide tree, and the
+    faster of the two with rays re-ordered -- and then reports decisions; the SAME sample rendered under all candidates gives
+    bit-identical frames."""
     import json
     import os
     import subprocess
@@ -152,21 +153,21 @@ v, f = procedural.synthetic_scene(300000, seed=9)
 info = gpt.default_kernel_info(1024, 1024); info.depth = 4; info.cam.dist = 12.0 * 1024 / 720.0
 with gpt.Context(0) as ctx:
     b = ctx.build_bvh(v, f); ctx.upload_built(b, gpt.default_spheres())
-    states, frames = [ctx.reorder_info()[0]], []
-    for call in range(5):
+    pending, frames = [ctx.trial_info()[0]], []
+    for call in range(7):
         acc = torch.zeros(1024, 1024, 4, dtype=torch.float32, device="cuda")
         ctx.render(info, acc, 3, 0, 1)                  # the same sample every call
         torch.cuda.synchronize()
-        frames.append(acc.cpu().numpy()); states.append(ctx.reorder_info()[0])
-    st, off, on = ctx.reorder_info()
-    print(json.dumps({"states": states, "off": off, "on": on, "same": bool(all(np.array_equal(frames[0], x) for x in frames[1:])),
-                      "lit": float(frames[0][..., :3].max())}))
+        frames.append(acc.cpu().numpy()); pending.append(ctx.trial_info()[0])
+    print(json.dumps({"pending": pending, "ns": ctx.trial_info()[1], "reorder": ctx.reorder_info()[0], "wide_nodes": ctx.wide_info()[0],
+                      "same": bool(all(np.array_equal(frames[0], x) for x in frames[1:])), "lit": float(frames[0][..., :3].max())}))
     ctx.free_bvh(b)
 ''' % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
-    env = {k: v for k, v in os.environ.items() if k not in ("GPT_WF_SORT", "GPT_SORT_MIN_TRIS")}
+    env = {k: v for k, v in os.environ.items() if k not in ("GPT_WF_SORT", "GPT_SORT_MIN_TRIS", "GPT_WIDE_MIN_TRIS")}
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
     r = json.loads(out.stdout.strip().splitlines()[-1])
-    assert r["states"][:4] == [-1, -1, -1, -1] and r["states"][4] in (0, 1) and r["states"][5] == r["states"][4], r
-    assert r["off"] > 0.0 and r["on"] > 0.0, r
+    assert r["pending"] == [True] * 6 + [False, False], r
+    assert all(x > 0.0 for x in r["ns"]), r
+    assert r["reorder"] in (0, 1)
     assert r["same"] and r["lit"] > 0.0, r
