@@ -117,6 +117,10 @@ __device__ __forceinline__ void node_step(const float4* __restrict__ nodes, Trav
 
 // One visit of a 4-wide quantised node (gpt_wide.cu): same state machine as node_step -- nearest hit child next, the others
 // pushed farthest first, a first leaf postponed -- over four children per 64-B fetch instead of two.
+// 0x4B000000 = bits of 2^23.  A __constant__ the compiler cannot fold: as a literal it would be re-materialised as a second
+// immediate next to every PRMT selector and cost a register move per plane (measured: 24 fewer instructions per visit, +1 %;
+// masking the bytes in with LOP3 at two scales instead was 2 % slower).
+static __constant__ unsigned gpt_w4_magic = 0x4B000000u;
 #define W4_CSWAP(ka, ca, kb, cb) { const bool sw_ = kb < ka; const float tk_ = sw_ ? ka : kb; const int tc_ = sw_ ? ca : cb; ka = sw_ ? kb : ka; ca = sw_ ? cb : ca; kb = tk_; cb = tc_; }
 __device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravState& s, int* stack)
 {
@@ -129,8 +133,7 @@ __device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravSt
     // plane = origin + q * 2^e  =>  t = (plane - o) / d = q * s + b  with s = 2^e / d, b = (origin - o) / d.  The byte q is
     // dropped into the mantissa of 2^23 (one PRMT, selector immediate, 2^23 kept in a register) and the 2^23 * s it
     // brings along is taken out of b once per axis; gpt_wide.cu leaves a cell of slack for the rounding of that.
-    unsigned magic;
-    asm volatile("mov.b32 %0, 0x4B000000;" : "=r"(magic));
+    const unsigned magic = gpt_w4_magic;     // bits of 2^23, read from constant memory so that it stays in ONE register
     const float sx = __uint_as_float((eb & 0xffu) << 23) * s.idx;
     const float sy = __uint_as_float((eb & 0xff00u) << 15) * s.idy;
     const float sz = __uint_as_float((eb & 0xff0000u) << 7) * s.idz;
@@ -145,8 +148,8 @@ __device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravSt
     const float inf = __int_as_float(0x7f800000);
     float k0, k1, k2, k3;
     int c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
-#define W4_Q(w, i) __uint_as_float(__byte_perm(w, magic, 0x7650u | (i)))
     // an unused slot has an inverted box (entry plane beyond exit plane on every axis): tn > tf without a test of its own
+#define W4_Q(w, i) __uint_as_float(__byte_perm(w, magic, 0x7650u | (i)))
 #define W4_CHILD(i, kk) { \
         const float tn = fmaxf(fmaxf(fmaf(W4_Q(nx, i), sx, bx), fmaf(W4_Q(ny, i), sy, by)), fmaxf(fmaf(W4_Q(nz, i), sz, bz), 0.0f)); \
         const float tf = fminf(fminf(fmaf(W4_Q(fx, i), sx, bx), fmaf(W4_Q(fy, i), sy, by)), fminf(fmaf(W4_Q(fz, i), sz, bz), s.t)); \
