@@ -138,7 +138,7 @@ k_wf_extend(const DevScene sc, const int cull, const uint32_t* __restrict__ queu
 // test that leaf" round; idle lanes are re-armed there.  Tighter inner loops than the voted steps above, but
 // lanes wait for the slowest descent / largest leaf of the round.
 #ifndef WF_WIDE_MIN_BLOCKS
-#define WF_WIDE_MIN_BLOCKS 8
+#define WF_WIDE_MIN_BLOCKS 10   // 48 registers, no spills; measured +2 % (2 M triangles) to +6 % (20 M) over 8 (profiles/r01_schedules.md #28)
 #endif
 // WIDE: the inner-node phase walks the 4-wide quantised tree (gpt_wide.cu, node4_step) instead of the binary one.
 template <bool CULL, bool WIDE>      // back-face culling resolved at compile time: the flag is tested once per triangle otherwise
