@@ -155,6 +155,17 @@ static const long long k_env_wide_min = []{ const char* e = getenv("GPT_WIDE_MIN
 static const int k_env_sort = []{ const char* e = getenv("GPT_WF_SORT"); return e ? atoi(e) : -1; }();
 static const long long k_env_sort_min = []{ const char* e = getenv("GPT_SORT_MIN_TRIS"); return e ? atoll(e) : -2ll; }();
 
+// Which pipeline: the wavefront pipeline needs ~19 launches per call and each costs ~19 us of launch gap + drain, so below a few
+// hundred thousand paths per call the single-launch megakernel is faster (cornell 512x512, 1 spp, depth 4: 0.17 ms against
+// 0.20 ms, and against 0.21 ms for the reference's kernel; profiles/r01_small_frames.jsonl).  Same samples, same images.
+static const long long k_env_small_frame = []{ const char* e = getenv("GPT_SMALL_FRAME_PATHS"); return (e && *e) ? atoll(e) : 393216ll; }();
+static bool use_megakernel(const gpt_ctx* c, size_t n_paths)
+{
+    if (c->flags & GPT_FLAG_MEGAKERNEL) return true;
+    if (c->flags & GPT_FLAG_WAVEFRONT) return false;
+    return (long long)n_paths < k_env_small_frame;
+}
+
 // 0 = binary, 1 = wide, -1 = open (trial)
 static int tree_choice(const gpt_ctx* c)
 {
@@ -550,7 +561,7 @@ int gpt_launch(gpt_ctx* c, const gpt_kernel_info* info, gpt_stream stream)
     int rc = make_params(c, info, info->hash, &p); if (rc) return rc;
     rc = launch_scene(c, info, &sc); if (rc) return rc;
     cudaError_t e;
-    if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
+    if (!use_megakernel(c, (size_t)p.width * p.height)) {
         return render_wavefront(c, sc, p, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u, (cudaStream_t)stream);
     } else {
         e = gptk_render_legacy(sc, p, info->accumBuffer, info->dev_drawRes, info->constantPdf,
@@ -571,7 +582,7 @@ int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_
     int rc = make_params(c, info, seed, &p); if (rc) return rc;
     rc = launch_scene(c, info, &sc); if (rc) return rc;
     cudaError_t e;
-    if (!(c->flags & GPT_FLAG_MEGAKERNEL)) {
+    if (!use_megakernel(c, (size_t)p.width * p.height * sample_count)) {
         return render_wavefront(c, sc, p, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count, (cudaStream_t)stream);
     } else {
         e = gptk_render_mega(sc, p, reinterpret_cast<float4*>(accum_f4), sample_begin, sample_count,

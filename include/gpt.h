@@ -96,7 +96,8 @@ typedef struct {
 enum {
     GPT_FLAG_NO_JITTER   = 1u << 0,  /* camera jitter off (hit-ID parity runs) */
     GPT_FLAG_METAL_FIXED = 1u << 1,  /* use the reflection vector w1 instead of the reference's int `w` */
-    GPT_FLAG_MEGAKERNEL  = 1u << 2,  /* single persistent megakernel instead of the (default) wavefront pipeline */
+    GPT_FLAG_MEGAKERNEL  = 1u << 2,  /* always the single persistent megakernel (default: only for calls of fewer than
+                                      * GPT_SMALL_FRAME_PATHS = 393216 paths, where launch overhead dominates) */
     GPT_FLAG_COUNT_BOUNCES = 1u << 3, /* fill gpt_stats.rays_by_bounce (slower) */
     GPT_FLAG_TIME_KERNELS = 1u << 4, /* CUDA-event timing per kernel class, read with gpt_get_kernel_times */
     /* Traversal structure of the wavefront pipeline and of gpt_trace_rays.  Default: the binary tree as
@@ -108,7 +109,8 @@ enum {
      * GPT_WIDE_MIN_TRIS in the environment decides, scenes from 64 Ki packed triangles up are put on a timed trial during
      * their first large render calls (gpt_trial_info); until it ends the wide tree is used from 1 Mi triangles. */
     GPT_FLAG_WIDE_BVH   = 1u << 5,   /* always the 4-wide tree */
-    GPT_FLAG_BINARY_BVH = 1u << 6    /* always the binary tree */
+    GPT_FLAG_BINARY_BVH = 1u << 6,   /* always the binary tree */
+    GPT_FLAG_WAVEFRONT  = 1u << 7    /* always the wavefront pipeline, also for small calls */
 };
 
 typedef struct {

@@ -15,7 +15,8 @@ from support import refgpu, scenes  # noqa: E402
 
 refk = refgpu.RefGpuKernel(0) if refgpu.available() else None
 sph = gpt.default_spheres()
-for name, W, H, depth in [("cornell", 512, 512, 4), ("dragon_cornell", 1280, 720, 4), ("bunny_cornell", 1920, 1080, 8), ("bunny_cornell", 256, 144, 4)]:
+for name, W, H, depth in [("cornell", 512, 512, 4), ("dragon_cornell", 1280, 720, 4), ("bunny_cornell", 1920, 1080, 8), ("bunny_cornell", 256, 144, 4),
+                          ("bunny_cornell", 640, 360, 8), ("bunny_cornell", 800, 600, 8), ("bunny_cornell", 1024, 576, 8), ("dragon_cornell", 640, 480, 4)]:
     sc = scenes.load_scene(name)
     info = gpt.default_kernel_info(W, H)
     info.depth = depth
@@ -37,7 +38,7 @@ for name, W, H, depth in [("cornell", 512, 512, 4), ("dragon_cornell", 1280, 720
         return e0.elapsed_time(e1) / n
     if refk is not None:
         res["reference_kernel_ms"] = loop(refk.launch)
-    for label, flags in (("wavefront", 0), ("megakernel", gpt.FLAG_MEGAKERNEL)):
+    for label, flags in (("wavefront", gpt.FLAG_WAVEFRONT), ("megakernel", gpt.FLAG_MEGAKERNEL), ("default", 0)):
         with gpt.Context(0, flags) as ctx:
             res["gpt_launch_%s_ms" % label] = loop(ctx.launch)
     print(json.dumps(res), flush=True)

@@ -10,6 +10,9 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 # at the first render).  Lowered here so that the 1.2 M-triangle scene of test_gpu_wide.py goes through the sorted pipeline
 # while the 1.0 M-triangle scene of test_gpu_build.py stays on the unsorted one.
 os.environ.setdefault("GPT_SORT_MIN_TRIS", "1100000")
+# Calls of fewer than GPT_SMALL_FRAME_PATHS paths (default 393216) go to the megakernel.  The parity tests render small frames and
+# mean to exercise the pipeline their flags name, so the switch is off here; tests/test_gpu_parity.py::test_small_calls_* covers it.
+os.environ.setdefault("GPT_SMALL_FRAME_PATHS", "0")
 
 
 def pytest_configure(config):

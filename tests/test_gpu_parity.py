@@ -459,3 +459,44 @@ def test_per_triangle_materials_match_oracle(gpt, torch_cuda):
             assert np.mean(np.any(want != plain, axis=-1)) > 0.2    # the table really changes the image
             ctx.set_triangle_materials(None, None)
             assert_radiance_close(gpu_render(torch, ctx, info, 21, 0, 3)[..., :3], plain[..., :3])
+
+
+def test_small_calls_take_the_megakernel_same_image(gpt, torch_cuda):
+    """Default flags, GPT_SMALL_FRAME_PATHS unset (a fresh process: read once, conftest sets it to 0 for the other tests): a call of
+    fewer than 393216 paths runs as ONE megakernel launch, a larger one through the wavefront pipeline (many launches); forcing
+    either pipeline gives the identical frame; gpt_launch (legacy contract) switches the same way."""
+    import json
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import json, sys, numpy as np, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import gpt_b200 as gpt
+from support import scenes
+sc = scenes.load_scene("cornell")
+res = {}
+for label, (w, h) in (("small", (512, 512)), ("large", (768, 576))):
+    info = gpt.default_kernel_info(w, h); info.depth = 4; info.cam.dist = 12.0 * h / 720.0
+    frames, launches = [], []
+    for flags in (0, gpt.FLAG_WAVEFRONT, gpt.FLAG_MEGAKERNEL):
+        with gpt.Context(0, flags) as ctx:
+            ctx.upload_scene(sc["nodes"], sc["tris"], sc["indices"], gpt.default_spheres(), None)
+            acc = torch.zeros(h, w, 4, dtype=torch.float32, device="cuda")
+            ctx.render(info, acc, 11, 0, 1)
+            torch.cuda.synchronize()
+            launches.append(ctx.stats().kernel_launches); frames.append(acc.cpu().numpy())
+    res[label] = {"launches": launches, "same": bool(np.array_equal(frames[0], frames[1]) and np.array_equal(frames[0], frames[2])),
+                  "lit": float(frames[0][..., :3].max())}
+print(json.dumps(res))
+''' % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if k != "GPT_SMALL_FRAME_PATHS"}
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    r = json.loads(out.stdout.strip().splitlines()[-1])
+    for label in ("small", "large"):
+        assert r[label]["same"] and r[label]["lit"] > 0.0, r
+    d, wf, mk = r["small"]["launches"]
+    assert d == mk and wf > mk, r                      # 262144 paths: the default is the megakernel
+    d, wf, mk = r["large"]["launches"]
+    assert d == wf and wf > mk, r                      # 442368 paths: the default is the wavefront pipeline
