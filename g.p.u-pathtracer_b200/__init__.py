@@ -29,6 +29,7 @@ FLAG_TIME_KERNELS = 1 << 4
 FLAG_WIDE_BVH = 1 << 5        # always traverse the 4-wide quantised tree
 FLAG_BINARY_BVH = 1 << 6      # always traverse the binary tree as uploaded
 FLAG_WAVEFRONT = 1 << 7       # always the wavefront pipeline (default: megakernel for calls under GPT_SMALL_FRAME_PATHS paths)
+FLAG_BUILD_LBVH = 1 << 8      # build_bvh: Morton radix tree instead of PLOC clustering
 K_GENERATE, K_EXTEND, K_SHADE, K_COLLECT, K_ACCUMULATE, K_RESOLVE, K_OTHER = range(7)
 
 

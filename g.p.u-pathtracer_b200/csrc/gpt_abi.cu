@@ -392,19 +392,31 @@ int gpt_build_bvh(gpt_ctx* c, const float* verts, size_t n_verts, const int32_t*
             return fail(c, GPT_ERR_CUDA, "gpt_build_bvh: staging copy", e);
         }
     }
+    // topology: PLOC (area-driven clustering of the Morton-sorted triangles) unless GPT_FLAG_BUILD_LBVH / GPT_PLOC_RADIUS=0 ask for
+    // the plain Morton radix tree; a PLOC tree deeper than the traversal stack (adversarial input) is rebuilt as a radix tree,
+    // whose depth is bounded by the 63 key bits
+    static const int k_env_ploc = []{ const char* v = getenv("GPT_PLOC_RADIUS"); return (v && *v) ? atoi(v) : 24; }();
+    int radius = (c->flags & GPT_FLAG_BUILD_LBVH) ? 0 : k_env_ploc;
     BuildResult r;
-    e = gptk_build_lbvh(on_device ? verts : dv, n_verts, on_device ? tris : dt, n_tris, max_leaf_size ? (int)max_leaf_size : 8, &r, 0);
+    for (;;) {
+        e = gptk_build_lbvh(on_device ? verts : dv, n_verts, on_device ? tris : dt, n_tris, max_leaf_size ? (int)max_leaf_size : 8, radius, &r, 0);
+        c->launches += (unsigned long long)r.launches;
+        if (e != cudaSuccess || radius <= 0) break;
+        const bool deep = r.status == 0 && r.depth > GPT_STACK_SIZE;
+        if (!deep && r.status != 4 && r.status != 5) break;
+        if (deep) { cudaFree(r.nodes); cudaFree(r.tris); cudaFree(r.indices); }
+        radius = 0;
+    }
     cudaEventRecord(e1, 0);
     cudaEventSynchronize(e1);
     float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     cudaFree(dv); cudaFree(dt);
-    c->launches += (unsigned long long)r.launches;
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "gpt_build_bvh", e);
     if (r.status == 0 && r.depth > GPT_STACK_SIZE) { cudaFree(r.nodes); cudaFree(r.tris); cudaFree(r.indices); r.status = 4; }
     if (r.status) {
-        static const char* why[] = {"", "vertex index out of range", "non-finite vertex", "mesh too large for 32-bit offsets", "tree deeper than the 64-entry traversal stack"};
-        char buf[128]; snprintf(buf, sizeof(buf), "gpt_build_bvh: %s", why[r.status < 5 ? r.status : 0]);
+        static const char* why[] = {"", "vertex index out of range", "non-finite vertex", "mesh too large for 32-bit offsets", "tree deeper than the 64-entry traversal stack", "clustering did not converge"};
+        char buf[128]; snprintf(buf, sizeof(buf), "gpt_build_bvh: %s", why[r.status < 6 ? r.status : 0]);
         return fail(c, r.status == 3 || r.status == 4 ? GPT_ERR_LAYOUT : GPT_ERR_INVALID, buf);
     }
     out->bvh.dev_triNode = r.nodes; out->bvh.triNodeSize = r.n_node_vec4;

@@ -63,7 +63,9 @@ cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float
 // cudaMalloc'd by the callee.  status: 0 ok, 1 vertex index out of range, 2 non-finite vertex, 3 too large, 4 too deep
 struct BuildResult { float4* nodes; size_t n_node_vec4; float4* tris; size_t n_tri_vec4; int* indices; size_t n_indices;
                      int n_leaves; int depth; int status; int launches; };
-cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, size_t n_tris, int max_leaf,
+// ploc_radius: 0 = Morton radix tree (Karras 2012); > 0 = PLOC clustering with that search radius (<= 32).
+// status: 1 index out of range, 2 non-finite vertex, 3 too large, 4 too deep, 5 clustering did not converge
+cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, size_t n_tris, int max_leaf, int ploc_radius,
                             BuildResult* out, cudaStream_t st);
 
 // 4-wide quantised BVH collapsed on the device from the packed binary nodes (gpt_wide.cu).

@@ -110,7 +110,8 @@ enum {
      * their first large render calls (gpt_trial_info); until it ends the wide tree is used from 1 Mi triangles. */
     GPT_FLAG_WIDE_BVH   = 1u << 5,   /* always the 4-wide tree */
     GPT_FLAG_BINARY_BVH = 1u << 6,   /* always the binary tree */
-    GPT_FLAG_WAVEFRONT  = 1u << 7    /* always the wavefront pipeline, also for small calls */
+    GPT_FLAG_WAVEFRONT  = 1u << 7,   /* always the wavefront pipeline, also for small calls */
+    GPT_FLAG_BUILD_LBVH = 1u << 8    /* gpt_build_bvh: plain Morton radix tree instead of the (default) PLOC clustering */
 };
 
 typedef struct {

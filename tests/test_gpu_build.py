@@ -65,11 +65,12 @@ def validate_layout(arr, n_faces, verts, faces):
 
 @pytest.mark.parametrize("name", ["cornell", "sphere_mesh", "bunny_cornell"])
 @pytest.mark.parametrize("max_leaf", [1, 8])
-def test_built_tree_is_valid_and_traces_like_the_oracle(gpt, torch_cuda, name, max_leaf):
+@pytest.mark.parametrize("topology", ["ploc", "radix"])
+def test_built_tree_is_valid_and_traces_like_the_oracle(gpt, torch_cuda, name, max_leaf, topology):
     torch = torch_cuda
     sc = scenes.load_scene(name)
     verts, faces = sc["verts"], sc["faces"]
-    with gpt.Context(0) as ctx:
+    with gpt.Context(0, gpt.FLAG_BUILD_LBVH if topology == "radix" else 0) as ctx:
         b = ctx.build_bvh(verts, faces, max_leaf=max_leaf)
         arr = ctx.built_to_host(b)
         assert b.n_triangles == len(faces) and b.depth <= 64
@@ -115,7 +116,8 @@ def test_built_tree_is_valid_and_traces_like_the_oracle(gpt, torch_cuda, name, m
 def test_builder_edge_cases(gpt, torch_cuda):
     torch = torch_cuda
     v = np.array([[0, 0, -10], [4, 0, -10], [0, 4, -10], [4, 4, -12]], np.float32)
-    with gpt.Context(0) as ctx:
+    for flags in (0, gpt.FLAG_BUILD_LBVH):
+      with gpt.Context(0, flags) as ctx:
         for faces in (np.array([[0, 1, 2]], np.int32),                                   # root would be a leaf (CudaBVH.cpp:141 asserts)
                       np.array([[0, 1, 2], [1, 3, 2]], np.int32),
                       np.repeat(np.array([[0, 1, 2]], np.int32), 37, axis=0)):           # identical Morton codes: position tie-break
