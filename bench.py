@@ -518,6 +518,33 @@ def run_ours(args):
                                          "ncu_issue_active_pct": ip["issue_active_pct"],
                                          "what": "warp instructions per ray from the committed ncu capture x rays per launch / live launch time, against "
                                                  "SMs x 4 schedulers x SM clock; the fraction the HBM figure cannot show"}
+        if world == 1 and args.pipeline != "mega":
+            # secondary figure, NOT the headline: the same workload on the tree this library's own device builder makes from the
+            # same mesh (gpt_build_bvh, PLOC) instead of the reference's host-built SBVH the headline traverses
+            try:
+                with gpt.Context(local, 0) as c2:
+                    built = c2.build_bvh(sc["verts"], sc["faces"])
+                    c2.upload_built(built, sph)
+                    for i in range(max(3, args.warmup)):
+                        c2.render(info, frame, args.seed, i * SPP, SPP, stream.cuda_stream)
+                    torch.cuda.synchronize(dev)
+                    c2.reset_stats()
+                    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    t0.record(stream)
+                    for i in range(args.steps):
+                        flush.zero_()
+                        c2.render(info, frame, args.seed, (i + 8) * SPP, SPP, stream.cuda_stream)
+                        c2.resolve(frame, W, H, rgba, None, stream.cuda_stream)
+                    t1.record(stream)
+                    torch.cuda.synchronize(dev)
+                    ms2 = t0.elapsed_time(t1)
+                    line["device_built_tree"] = {"value": float(c2.stats().rays) / (ms2 * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms2 / args.steps,
+                                                 "builder": "gpt_build_bvh (PLOC clustering, SAH leaf collapse)", "build_ms": built.build_ms,
+                                                 "inner_nodes": built.n_inner_nodes, "depth": built.depth,
+                                                 "what": "same mesh, spheres, camera and samples; only the tree differs from the headline's"}
+                    c2.free_bvh(built)
+            except Exception as ex:
+                line["device_built_tree"] = {"unavailable": repr(ex)}
         if world == 1 and not args.no_cpu_baseline:
             base, port = cpu_baseline(gpt, sc, args)
             line["cpu_baseline"] = base

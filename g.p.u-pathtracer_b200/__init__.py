@@ -381,7 +381,7 @@ class Context:
         return s
 
     def build_bvh(self, verts, faces, on_device=False, max_leaf=8):
-        """Device-side LBVH build (gpt_build_bvh): verts (n,3) float32, faces (m,3) int32 -> BuiltBVH whose .bvh holds
+        """Device-side BVH build (gpt_build_bvh; PLOC topology, Morton radix tree with FLAG_BUILD_LBVH): verts (n,3) float32, faces (m,3) int32 -> BuiltBVH whose .bvh holds
         DEVICE arrays in CudaBVH's compact layout.  Free with free_bvh()."""
         def cnt(a):
             return int(a.numel() if hasattr(a, "numel") else a.size) // 3

@@ -16,6 +16,7 @@
 // Nearest-hit distances are independent of the tree (same per-triangle arithmetic); only which of two triangles
 // with bit-identical t is reported may differ from a reference-built tree.
 #include "gpt_kernels.h"
+#include <stdlib.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
@@ -140,7 +141,7 @@ __global__ void __launch_bounds__(256)
 k_fit(const int n, const int* __restrict__ vals, const float4* __restrict__ lo, const float4* __restrict__ hi,
       float4* __restrict__ slo, float4* __restrict__ shi, const int* __restrict__ child_l, const int* __restrict__ child_r,
       int* first, int* last, const int* __restrict__ parent_i, const int* __restrict__ parent_p,
-      float4* nlo, float4* nhi, float* cost, int* __restrict__ collapse, int* flag, const int max_leaf)
+      float4* nlo, float4* nhi, float* cost, int* __restrict__ collapse, int* flag, const int max_leaf, const float node_cost)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
@@ -166,7 +167,7 @@ k_fit(const int n, const int* __restrict__ vals, const float4* __restrict__ lo, 
             last[cur] = cr < 0 ? ~cr : __ldcg(last + cr);
         }
         const int cnt = last[cur] - first[cur] + 1;
-        const float leaf_cost = (float)cnt * a, split_cost = a + ca + cb;
+        const float leaf_cost = (float)cnt * a, split_cost = node_cost * a + ca + cb;
         const bool col = cnt <= max_leaf && leaf_cost <= split_cost;
         nlo[cur] = l; nhi[cur] = h; cost[cur] = col ? leaf_cost : split_cost; collapse[cur] = col ? 1 : 0;
         cur = parent_i[cur];
@@ -396,6 +397,7 @@ cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, 
     if (max_leaf > 64) max_leaf = 64;
     if (ploc_radius > PLOC_R_MAX) ploc_radius = PLOC_R_MAX;
     if (n < 2 || ploc_radius < 0) ploc_radius = 0;
+    static const float node_cost = []{ const char* v = getenv("GPT_SAH_NODE_COST"); return (v && *v) ? (float)atof(v) : 1.0f; }();
     cudaError_t e = cudaSuccess;
     // scratch
     float4 *lo = nullptr, *hi = nullptr, *slo = nullptr, *shi = nullptr, *nlo = nullptr, *nhi = nullptr;
@@ -476,11 +478,11 @@ cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, 
             k_ploc_positions<<<g, 256, 0, st>>>(n, child_l, child_r, parent_i, parent_p0, count, posmap, bad);
             k_ploc_remap<<<g, 256, 0, st>>>(n, posmap, vals2, parent_p0, vals, parent_p, child_l, child_r);
             svals = vals;
-            k_fit<true><<<g, 256, 0, st>>>(n, svals, lo, hi, slo, shi, child_l, child_r, first, last, parent_i, parent_p, nlo, nhi, cost, collapse, flag, max_leaf);
+            k_fit<true><<<g, 256, 0, st>>>(n, svals, lo, hi, slo, shi, child_l, child_r, first, last, parent_i, parent_p, nlo, nhi, cost, collapse, flag, max_leaf, node_cost);
             CK(cudaGetLastError());
         } else if (n >= 2) {
             k_radix_tree<<<g, 256, 0, st>>>(keys2, n, child_l, child_r, first, last, parent_i, parent_p);
-            k_fit<false><<<g, 256, 0, st>>>(n, svals, lo, hi, slo, shi, child_l, child_r, first, last, parent_i, parent_p, nlo, nhi, cost, collapse, flag, max_leaf);
+            k_fit<false><<<g, 256, 0, st>>>(n, svals, lo, hi, slo, shi, child_l, child_r, first, last, parent_i, parent_p, nlo, nhi, cost, collapse, flag, max_leaf, node_cost);
             CK(cudaGetLastError());
         }
         if (n >= 2) {
@@ -500,7 +502,7 @@ cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, 
             }
             n_em = end;
         } else {
-            k_fit<false><<<g, 256, 0, st>>>(n, svals, lo, hi, slo, shi, child_l, child_r, first, last, parent_i, parent_p, nlo, nhi, cost, collapse, flag, max_leaf);
+            k_fit<false><<<g, 256, 0, st>>>(n, svals, lo, hi, slo, shi, child_l, child_r, first, last, parent_i, parent_p, nlo, nhi, cost, collapse, flag, max_leaf, node_cost);
             const int one = 1;
             CK(cudaMemcpyAsync(leaf_start, &one, sizeof(int), cudaMemcpyHostToDevice, st));
             CK(cudaMemcpyAsync(h_small, small, sizeof(h_small), cudaMemcpyDeviceToHost, st));

@@ -167,9 +167,10 @@ GPT_API int gpt_set_triangle_materials(gpt_ctx* ctx, const gpt_tri_material* mat
  * uf::loadIndexedTris returns (utilfun.cpp:454-524; verts = n_verts*3 floats, tris = n_tris*3 ints), host
  * (on_device=0) or device pointers.  Output: DEVICE arrays in exactly the layout CudaBVH::getGpuNodes /
  * getDebugTri / getGpuTriIndices hand out, so `out->bvh` can be stored into kernelInfo.bvhData or passed to
- * gpt_upload_scene(..., on_device=1).  The tree is an LBVH (Morton radix tree + SAH leaf collapse with the
- * reference's cost model 1/1), not the reference's SBVH: hit distances are identical, tie-breaking between
- * triangles with bit-equal t may differ.  The arrays belong to the caller until gpt_free_bvh. */
+ * gpt_upload_scene(..., on_device=1).  The tree is built by PLOC clustering over the Morton-sorted triangles (area-driven
+ * merges, deterministic) with a SAH leaf collapse at the reference's cost model 1/1 -- not the reference's SBVH (no spatial
+ * splits): hit distances are identical, tie-breaking between triangles with bit-equal t may differ.  GPT_FLAG_BUILD_LBVH asks
+ * for the plain Morton radix tree instead.  The arrays belong to the caller until gpt_free_bvh. */
 typedef struct {
     gpt_bvh_data bvh;
     uint32_t n_inner_nodes, n_leaves, n_triangles, depth;
