@@ -7,7 +7,8 @@
 // -- CudaBVH.cpp:196-224), so its output is a drop-in for kernelInfo.bvhData / gpt_upload_scene and the CPU oracle
 // can traverse the very same arrays.  The tree is NOT the reference's SBVH (no spatial splits): it is
 //   1. 63-bit Morton codes of the triangle AABB centres, radix-sorted (CUB),
-//   2. the binary radix tree of Karras 2012 over the sorted codes (ties broken by position),
+//   2. a topology over the sorted triangles: PLOC clustering (ploc_radius > 0, the default -- see k_ploc_* below) or the
+//      binary radix tree of Karras 2012 over the sorted codes (ties broken by position),
 //   3. bottom-up AABB fit with a SAH evaluation (node cost 1, triangle cost 1 -- the reference's Platform() defaults,
 //      bvh_util.hpp) that collapses a subtree into one leaf when  n * A(node) <= A(node) + cost(left) + cost(right)
 //      and n <= max_leaf,
