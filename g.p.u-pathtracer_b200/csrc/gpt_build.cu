@@ -470,7 +470,7 @@ cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, 
                 CK(cudaMemcpyAsync(&tot, pfl + n + (m - 1), sizeof(tot), cudaMemcpyDeviceToHost, st));
                 CK(cudaStreamSynchronize(st));
                 const int m2 = (int)(tot >> 32), created = (int)(tot & 0xffffffffull);
-                if (created <= 0 || m2 != m - created || ++ploc_steps > 100000) { out->status = 5; goto done; }
+                if (created <= 0 || m2 != m - created || ++ploc_steps > 2048) { out->status = 5; goto done; }
                 made += created; m = m2; cur ^= 1;
             }
             if (made != n - 1) { out->status = 5; goto done; }

@@ -142,6 +142,40 @@ def test_builder_edge_cases(gpt, torch_cuda):
             ctx.build_bvh(bad, np.array([[0, 1, 2]], np.int32))
 
 
+def test_ploc_chain_falls_back_to_the_radix_tree(gpt, torch_cuda):
+    """Triangles growing geometrically make PLOC merge one pair per step into a chain deeper than the 64-entry traversal stack:
+    gpt_build_bvh must hand back the Morton radix tree instead (same arrays as GPT_FLAG_BUILD_LBVH), never a tree it cannot walk."""
+    torch = torch_cuda
+    n = 200
+    s = (1.45 ** np.arange(n)).astype(np.float32)
+    v = np.stack([np.stack([s, 0 * s, -s], 1), np.stack([2 * s, 0 * s, -s], 1), np.stack([s, s, -s], 1)], 1).reshape(-1, 3).astype(np.float32)
+    f = np.arange(3 * n, dtype=np.int32).reshape(n, 3)
+    out = []
+    for flags in (0, gpt.FLAG_BUILD_LBVH):
+        with gpt.Context(0, flags) as ctx:
+            b = ctx.build_bvh(v, f, max_leaf=1)
+            assert b.depth <= 64 and b.n_leaves == n
+            arr = ctx.built_to_host(b)
+            seen, n_leaves, depth = validate_layout(arr, n, v, f)
+            assert (seen == 1).all()
+            if not flags:
+                ctx.upload_built(b)
+                sr = s[:100:5]                                   # beyond ~1e19 the determinant overflows: no hits by the reference's own arithmetic
+                o = np.stack([1.2 * sr, 0.2 * sr, np.zeros_like(sr)], 1).astype(np.float32)
+                d = np.tile(np.array([[0, 0, -1]], np.float32), (len(o), 1))
+                tri_o, _, t_o, _ = scenes.oracle_trace_rays(dict(verts=v, faces=f, **arr), o, d, cull=False)
+                t = torch.empty(len(o), dtype=torch.float32, device="cuda"); tri = torch.empty(len(o), dtype=torch.int32, device="cuda")
+                ctx.trace_rays(dev(torch, o), dev(torch, d), len(o), False, tri, None, t)
+                torch.cuda.synchronize()
+                assert (t_o < 3e38).sum() >= len(o) // 2
+                np.testing.assert_array_equal(t.cpu().numpy(), t_o)
+                np.testing.assert_array_equal(tri.cpu().numpy(), tri_o)
+            out.append(arr)
+            ctx.free_bvh(b)
+    for k in ("nodes", "tris", "indices"):
+        np.testing.assert_array_equal(out[0][k].view(np.uint32), out[1][k].view(np.uint32))
+
+
 def test_device_input_and_kernelinfo_dropin(gpt, torch_cuda):
     """device-resident mesh in, built arrays straight into kernelInfo.bvhData (the reference's upload contract,
     BasicScene.cpp:294-313) and rendered through the legacy launchKernel path."""
