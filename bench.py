@@ -518,6 +518,43 @@ def run_ours(args):
                                          "ncu_issue_active_pct": ip["issue_active_pct"],
                                          "what": "warp instructions per ray from the committed ncu capture x rays per launch / live launch time, against "
                                                  "SMs x 4 schedulers x SM clock; the fraction the HBM figure cannot show"}
+        # SURVEY 8-d "secondary figure": traversal steps/s = (inner nodes + triangle tests) per ray (oracle counters on the reference
+        # arrays, profiles/r01_algorithmic_bytes.json) x rays/s, and rays/s per bounce index (coherent primaries vs incoherent
+        # secondaries) from depth-limited renders of the same samples: bounce b = render(depth b+1) - render(depth b)
+        try:
+            with open(os.path.join(ROOT, "profiles", "r01_algorithmic_bytes.json")) as fh:
+                ab = json.load(fh)[WORKLOAD]
+            steps_per_ray = ab["inner_nodes_per_ray"] + ab["tri_tests_per_ray"]
+            line["traversal_steps"] = {"per_ray": steps_per_ray, "value": steps_per_ray * line["value"] / 1e3, "unit": "G steps/s",
+                                       "what": "(inner-node visits + triangle tests) of the reference algorithm per ray x rays/s"}
+        except Exception as ex:
+            line["traversal_steps"] = {"unavailable": repr(ex)}
+        if world == 1:
+            try:
+                cum = []
+                for dpt in range(1, args.depth + 1):
+                    inf_d = bench_info(gpt, args)
+                    inf_d.depth = dpt
+                    ctx.render(inf_d, frame, args.seed, 0, SPP, stream.cuda_stream)      # warm-up of this depth's buffers
+                    torch.cuda.synchronize(dev)
+                    ctx.reset_stats()
+                    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    reps = 3
+                    t0.record(stream)
+                    for r in range(reps):
+                        ctx.render(inf_d, frame, args.seed, 0, SPP, stream.cuda_stream)
+                    t1.record(stream)
+                    torch.cuda.synchronize(dev)
+                    cum.append((float(ctx.stats().rays) / reps, t0.elapsed_time(t1) / reps))
+                pb, prev = [], (0.0, 0.0)
+                for b, c in enumerate(cum):
+                    dr, dt = c[0] - prev[0], c[1] - prev[1]
+                    pb.append({"bounce": b, "rays": dr, "ms": dt, "Mrays_s": dr / (dt * 1e-3) / 1e6 if dt > 0 else None})
+                    prev = c
+                line["per_bounce"] = {"rows": pb, "what": "differences of depth-limited renders of the same 16 samples (bounce 0 also carries "
+                                      "generate + collect + accumulate); no L2 flush between repetitions"}
+            except Exception as ex:
+                line["per_bounce"] = {"unavailable": repr(ex)}
         if world == 1 and args.pipeline != "mega":
             # secondary figure, NOT the headline: the same workload on the tree this library's own device builder makes from the
             # same mesh (gpt_build_bvh, PLOC) instead of the reference's host-built SBVH the headline traverses

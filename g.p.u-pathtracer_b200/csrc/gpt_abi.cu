@@ -106,13 +106,13 @@ static void free_scene(gpt_ctx* c)
 static void free_wave(gpt_ctx* c)
 {
     WaveBuffers& w = c->wave;
-    cudaFree(w.ray_o); cudaFree(w.ray_d); cudaFree(w.mask); cudaFree(w.accu); cudaFree(w.lsum); cudaFree(w.hit);
+    cudaFree(w.ray_o); cudaFree(w.ray_d); cudaFree(w.mask_z); cudaFree(w.accu); cudaFree(w.lsum); cudaFree(w.hit);
     cudaFree(w.queue[0]); cudaFree(w.queue[1]); cudaFree(w.counters);
     cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp);
     w = WaveBuffers{}; c->wave_pixels = 0; c->wave_counters = 0;
 }
 
-// wavefront scratch: per-path state for one wave (80 B/path) + one launch sum per pixel.  A wave holds as many
+// wavefront scratch: per-path state for one wave (68 B/path) + one launch sum per pixel.  A wave holds as many
 // samples of the frame as fit GPT_WAVE_MAX_PATHS (5 GB of the 180 GB HBM at the cap); grown on demand.
 #define GPT_WAVE_MAX_PATHS ((size_t)64 << 20)
 static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sample_count)
@@ -126,7 +126,7 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     free_wave(c);
     WaveBuffers& w = c->wave;
     CU(c, cudaMalloc(&w.ray_o, want * sizeof(float4))); CU(c, cudaMalloc(&w.ray_d, want * sizeof(float4)));
-    CU(c, cudaMalloc(&w.mask, want * sizeof(float4)));  CU(c, cudaMalloc(&w.accu, want * sizeof(float4)));
+    CU(c, cudaMalloc(&w.mask_z, want * sizeof(float)));  CU(c, cudaMalloc(&w.accu, want * sizeof(float4)));
     CU(c, cudaMalloc(&w.hit, want * sizeof(int2)));
     CU(c, cudaMalloc(&w.queue[0], want * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], want * sizeof(uint32_t)));
     CU(c, cudaMalloc(&w.lsum, n_pix * sizeof(float4)));

@@ -54,16 +54,22 @@ __device__ __forceinline__ f3 box_normal(const float* bx, f3 p)
 
 // One bounce of tracer.cu:112-296.  Returns false when the path ended on a miss (ps.accu then holds
 // the background colour, Q2); true when the path continues with the new ray in ps.
+// accu_slot != nullptr (wavefront pipeline): the accumulated colour lives in memory and ps.accu is not used.  It changes
+// only on a miss (overwritten with the background, no read) and on an emitting hit (read-modify-write); on any other
+// hit fma(mask, 0, accu) == accu bit for bit for a finite mask, so the slot is neither read nor written.
 __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderParams& p,
                                              const float* s_spheres, const float* s_boxes,
                                              const SceneHit h, const uint32_t pixel, const uint64_t sample,
-                                             const uint32_t bounce, PathState& ps)
+                                             const uint32_t bounce, PathState& ps, float4* accu_slot = nullptr)
 {
     // RNG first, while the warp is still converged: placed after the geometry branches the compiler
     // tail-duplicates the ten Philox rounds into each branch and the warp runs them once per geometry type
     // (ncu: 18 of 32 lanes active on those instructions).
     const float4 u = rng_block(p.seed, pixel, sample, bounce + 1u);
-    if (h.geom == GEO_NONE) { ps.accu = ld3(p.bk); return false; }       // tracer.cu:140-142
+    if (h.geom == GEO_NONE) {                                            // tracer.cu:140-142
+        if (accu_slot) *accu_slot = make_float4(p.bk[0], p.bk[1], p.bk[2], 0.0f); else ps.accu = ld3(p.bk);
+        return false;
+    }
     f3 hitpos = mad3(ps.d, h.t, ps.o);                                   // :112
     f3 n, nl, objcol, emit; int mat;
     if (h.geom == GEO_SPHERE) {                                          // :113-122
@@ -95,6 +101,14 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
         emit = mk3(bx[6], bx[7], bx[8]); objcol = mk3(bx[9], bx[10], bx[11]); mat = __float_as_int(bx[12]);
     }
+    if (accu_slot) {
+        const bool touch = emit.x != 0.0f || emit.y != 0.0f || emit.z != 0.0f
+                           || !(fabsf(ps.mask.x) <= GPT_F32_MAX) || !(fabsf(ps.mask.y) <= GPT_F32_MAX) || !(fabsf(ps.mask.z) <= GPT_F32_MAX);
+        if (touch) {
+            const float4 a = *accu_slot;
+            *accu_slot = make_float4(fmaf(ps.mask.x, emit.x, a.x), fmaf(ps.mask.y, emit.y, a.y), fmaf(ps.mask.z, emit.z, a.z), 0.0f);
+        }
+    } else
     ps.accu = mk3(fmaf(ps.mask.x, emit.x, ps.accu.x), fmaf(ps.mask.y, emit.y, ps.accu.y), fmaf(ps.mask.z, emit.z, ps.accu.z));   // :120/:133, contracted
 
     f3 nextdir;

@@ -57,7 +57,7 @@ __device__ __forceinline__ void stage_prims(const DevScene& sc, SmemPrims& sm, c
 //                                 [depth+1 .. 2depth+1] fetch[b] = extend's work-fetch cursor of bounce b
 __global__ void __launch_bounds__(256)
 k_wf_generate(const RenderParams p, const unsigned long long sample0, const int n_samples, const int pix0, const int n_wave,
-              float4* __restrict__ ray_o, float4* __restrict__ ray_d, float4* __restrict__ mask, float4* __restrict__ accu,
+              float4* __restrict__ ray_o, float4* __restrict__ ray_d, float* __restrict__ mask_z, float4* __restrict__ accu,
               unsigned int* __restrict__ counters, unsigned long long* __restrict__ stats)
 {
     // path id = s_local * n_wave + i  <->  (global sample sample0 + s_local, pixel pix0 + i): sample-major, so the
@@ -68,9 +68,10 @@ k_wf_generate(const RenderParams p, const unsigned long long sample0, const int 
         const int pixel = pix0 + (pid - s_local * n_wave);
         PathState ps;
         start_path(p, pixel % p.width, pixel / p.width, (uint32_t)pixel, sample0 + (unsigned long long)s_local, ps);
-        ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, 0.0f);
-        ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, 0.0f);
-        mask[pid] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        // the colour mask (tracer.cu:68) rides in the two free w lanes of the ray + one float: 36 B of ray state per path
+        ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, 1.0f);
+        ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, 1.0f);
+        mask_z[pid] = 1.0f;
         accu[pid] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) { counters[0] = (unsigned)n_paths; atomicAdd(&stats[1], (unsigned long long)n_paths); }
@@ -313,7 +314,7 @@ __global__ void __launch_bounds__(256, SHADE_MIN_BLOCKS)
 k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sample0, const uint32_t bounce, const uint32_t pix0, const uint32_t n_wave,
            const uint32_t* __restrict__ queue_in, unsigned int* __restrict__ counters,
            uint32_t* __restrict__ queue_out, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
-           const int2* __restrict__ hit, float4* __restrict__ mask, float4* __restrict__ accu,
+           const int2* __restrict__ hit, float* __restrict__ mask_z, float4* __restrict__ accu,
            unsigned long long* __restrict__ stats)
 {
     __shared__ SmemPrims sm;
@@ -336,25 +337,21 @@ k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sam
         if (i < n) {
             pid = queue_in ? queue_in[i] : i;
             const float4 ro = ray_o[pid], rd = ray_d[pid];
-            const float4 mk = mask[pid], ac = accu[pid];
             PathState ps;
             ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
-            ps.mask = mk3(mk.x, mk.y, mk.z); ps.accu = mk3(ac.x, ac.y, ac.z);
+            ps.mask = mk3(ro.w, rd.w, mask_z[pid]); ps.accu = mk3(0.0f, 0.0f, 0.0f);      // accu stays in memory (shade_bounce, accu_slot)
             float tri_t = GPT_F32_MAX; int tri = -1;
             if (has_mesh) { const int2 h = hit[pid]; tri_t = __int_as_float(h.x); tri = h.y; }
             const SceneHit h = finish_scene_hit(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
             const uint32_t s_local = pid / n_wave;
-            const bool cont = shade_bounce(sc, p, s_spheres, s_boxes, h, pix0 + (pid - s_local * n_wave), sample0 + s_local, bounce, ps);
+            // accu[pid] is touched inside only on a miss or an emitting hit; when the path is over its radiance (tracer.cu:305,
+            // or bkColor on a miss :141) stays there until k_wf_collect adds the wave's samples to the per-pixel launch sum
+            const bool cont = shade_bounce(sc, p, s_spheres, s_boxes, h, pix0 + (pid - s_local * n_wave), sample0 + s_local, bounce, ps, accu + pid);
             survive = cont && !last_bounce;
             if (survive) {
-                ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, 0.0f);
-                ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, 0.0f);
-                mask[pid] = make_float4(ps.mask.x, ps.mask.y, ps.mask.z, 0.0f);
-                accu[pid] = make_float4(ps.accu.x, ps.accu.y, ps.accu.z, 0.0f);
-            } else {
-                // path over: its radiance (tracer.cu:305, or bkColor on a miss :141) stays in accu[pid] until
-                // k_wf_collect adds the wave's samples to the per-pixel launch sum in sample order
-                accu[pid] = make_float4(ps.accu.x, ps.accu.y, ps.accu.z, 0.0f);
+                ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x);
+                ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y);
+                mask_z[pid] = ps.mask.z;
             }
         }
         // ---- compaction: one atomic per warp ----
@@ -526,7 +523,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
             const unsigned long long sample0 = sample_begin + s0;
             if ((e = cudaMemsetAsync(wb.counters, 0, sizeof(unsigned int) * gptk_wave_counter_count(p.depth), st)) != cudaSuccess) return e;
             if (kt) kt->tick(KT_GENERATE, st);
-            k_wf_generate<<<grid, 256, 0, st>>>(p, sample0, (int)ns, pix0, n_wave, wb.ray_o, wb.ray_d, wb.mask, wb.accu, wb.counters, stats);
+            k_wf_generate<<<grid, 256, 0, st>>>(p, sample0, (int)ns, pix0, n_wave, wb.ray_o, wb.ray_d, wb.mask_z, wb.accu, wb.counters, stats);
             *launches += 1;
             for (uint32_t b = 0; b < p.depth; ++b) {
                 const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
@@ -558,7 +555,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                 }
                 if (kt) kt->tick(KT_SHADE, st);
                 k_wf_shade<<<grid, 256, 0, st>>>(sc, p, sample0, b, (uint32_t)pix0, (uint32_t)n_wave, q_in, wb.counters, wb.queue[(b + 1u) & 1u],
-                                                 wb.ray_o, wb.ray_d, wb.hit, wb.mask, wb.accu, stats);
+                                                 wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
                 *launches += 1;
             }
             if (kt) kt->tick(KT_COLLECT, st);
