@@ -22,7 +22,7 @@
 
 #define WF_THREADS 128
 #ifndef SHADE_MIN_BLOCKS
-#define SHADE_MIN_BLOCKS 4
+#define SHADE_MIN_BLOCKS 5
 #endif
 #ifndef WF_LEAF_SPLIT
 #define WF_LEAF_SPLIT 0   // A/B: culled leaves in two passes (determinant filter, then full tests), see leaf_step_culled; measured 1.5 % slower
@@ -491,6 +491,15 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ext_kind == 0 ? (const void*)k_wf_extend_pool : ext_kind == 1 ? (const void*)k_wf_extend_ww<true, false> : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
         ext_grid = sm_count * per_sm;
     }
+    // shade grid: whole waves of resident CTAs (occupancy of the kernel as built x GPT_SHADE_WAVES), so no partial last wave
+    static int shade_grid = 0;
+    if (shade_grid == 0) {
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_shade, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+        const char* e = getenv("GPT_SHADE_WAVES");
+        const int waves = e ? atoi(e) : 16;      // measured 1 / 2 / 4 / 8 / 16 / 32 / 64 / one trip per thread: 11.46 / 11.27 / 11.0 / 10.82 / 10.75 / 10.87 / 11.09 / 11.92 ms
+        shade_grid = waves <= 0 ? 0x7fffffff : sm_count * per_sm * (waves > 4096 ? 4096 : waves);
+    }
     static int wide_grid = 0;
     if (!wide_grid) {
         int per_sm = 0;
@@ -519,6 +528,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
             const uint32_t ns = sample_count - s0 < wave_spp_max ? sample_count - s0 : wave_spp_max;
             const size_t n_paths = (size_t)ns * n_wave;
             int grid = (int)((n_paths + 255) / 256); if (grid > sm_count * 8) grid = sm_count * 8; if (grid < 1) grid = 1;
+            int sgrid = (int)((n_paths + 255) / 256); if (sgrid > shade_grid) sgrid = shade_grid; if (sgrid < 1) sgrid = 1;
             int cgrid = (n_wave + 255) / 256; if (cgrid > sm_count * 8) cgrid = sm_count * 8; if (cgrid < 1) cgrid = 1;
             const unsigned long long sample0 = sample_begin + s0;
             if ((e = cudaMemsetAsync(wb.counters, 0, sizeof(unsigned int) * gptk_wave_counter_count(p.depth), st)) != cudaSuccess) return e;
@@ -554,7 +564,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                     *launches += 1;
                 }
                 if (kt) kt->tick(KT_SHADE, st);
-                k_wf_shade<<<grid, 256, 0, st>>>(sc, p, sample0, b, (uint32_t)pix0, (uint32_t)n_wave, q_in, wb.counters, wb.queue[(b + 1u) & 1u],
+                k_wf_shade<<<sgrid, 256, 0, st>>>(sc, p, sample0, b, (uint32_t)pix0, (uint32_t)n_wave, q_in, wb.counters, wb.queue[(b + 1u) & 1u],
                                                  wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
                 *launches += 1;
             }
