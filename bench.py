@@ -561,6 +561,9 @@ def run_ours(args):
             try:
                 with gpt.Context(local, 0) as c2:
                     built = c2.build_bvh(sc["verts"], sc["faces"])
+                    cold_ms = built.build_ms          # first build of the process: CUDA loads the builder's kernels lazily
+                    c2.free_bvh(built)
+                    built = c2.build_bvh(sc["verts"], sc["faces"])
                     c2.upload_built(built, sph)
                     for i in range(max(3, args.warmup)):
                         c2.render(info, frame, args.seed, i * SPP, SPP, stream.cuda_stream)
@@ -576,7 +579,7 @@ def run_ours(args):
                     torch.cuda.synchronize(dev)
                     ms2 = t0.elapsed_time(t1)
                     line["device_built_tree"] = {"value": float(c2.stats().rays) / (ms2 * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms2 / args.steps,
-                                                 "builder": "gpt_build_bvh (PLOC clustering, SAH leaf collapse)", "build_ms": built.build_ms,
+                                                 "builder": "gpt_build_bvh (PLOC clustering, SAH leaf collapse)", "build_ms": built.build_ms, "build_ms_first_in_process": cold_ms,
                                                  "inner_nodes": built.n_inner_nodes, "depth": built.depth,
                                                  "what": "same mesh, spheres, camera and samples; only the tree differs from the headline's"}
                     c2.free_bvh(built)

@@ -179,6 +179,26 @@ def test_render_mixed_sphere_materials_and_metal_fixed(gpt, torch_cuda, ctxs):
         assert_radiance_close(got[..., :3], want[..., :3])
 
 
+def test_emitting_triangles_and_overflowing_mask(gpt, torch_cuda, ctxs):
+    """The wavefront pipeline keeps the accumulated colour in memory and touches it only on a miss, on an emitting hit, or
+    when the colour mask is no longer finite (then mask * 0 is NaN in tracer.cu:120/:133, and must be here).  Emitting
+    triangles exercise the read-modify-write; a colour of 1e30 overflows the mask to inf within two bounces."""
+    torch = torch_cuda
+    for col, emi, depth in (((0.8, 0.7, 0.6), (0.25, 0.5, 0.125), 6), ((1e30, 1e30, 0.5), (0.0, 0.0, 0.0), 5), ((1e30, 0.9, -2.0), (0.0, 1.0, 0.0), 5)):
+        for flags in (gpt.FLAG_WAVEFRONT, gpt.FLAG_MEGAKERNEL):
+            ctx, sc, sph = ctxs("bunny_cornell", flags=flags)
+            info = small_info(gpt, 128, 72, depth=depth)
+            info.col[:] = col
+            info.emi[:] = emi
+            want = scenes.oracle_render(sc, sph, info, 5, 0, 2)
+            got = gpu_render(torch, ctx, info, 5, 0, 2)
+            g, w = got[..., :3], want[..., :3]
+            # NaN counts as equal to NaN (the payload differs between x86 and the GPU); everything else bit for bit
+            diff = np.any((g != w) & ~(np.isnan(g) & np.isnan(w)), axis=-1)
+            assert np.isnan(w).any() == (col[0] > 1e20)           # the overflow cases do reach NaN in the reference arithmetic
+            assert diff.mean() <= MAX_DIFF_PIXEL_FRACTION, (col, emi, flags, diff.mean())
+
+
 def test_boxes_and_sphere_only_scene(gpt, torch_cuda, ctxs):
     """N2: Box primitive from the reference's commented spec; also a scene without any mesh."""
     torch = torch_cuda
