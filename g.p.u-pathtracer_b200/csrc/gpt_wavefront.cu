@@ -146,7 +146,7 @@ template <bool CULL, bool WIDE>      // back-face culling resolved at compile ti
 __global__ void __launch_bounds__(WF_THREADS, WIDE ? WF_WIDE_MIN_BLOCKS : WF_MIN_BLOCKS)
 k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
                unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
-               int2* __restrict__ hit, const int refill_min)
+               int2* __restrict__ hit, const int refill_min, const int node_k)
 {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -182,10 +182,10 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
         if (active) {
             while (trav_wants_node(ts)) {
                 if (WIDE) node4_step(sc.wnodes, ts, stack); else node_step(sc.nodes, ts, stack);
-                // reference policy (WF_NODE_K = 1, cudaUtils.h:385-391): descend until every lane still in the loop holds a
-                // leaf.  WF_NODE_K = k leaves as soon as fewer than k lanes lack a leaf -- they resume after the leaf phase --
+                // reference policy (node_k = 1, cudaUtils.h:385-391): descend until every lane still in the loop holds a
+                // leaf.  node_k = k leaves as soon as fewer than k lanes lack a leaf -- they resume after the leaf phase --
                 // instead of making the whole warp wait for one or two stragglers (k = 2..3: -3 % extend time; k >= 8 loses)
-                if (WF_NODE_K == 1 ? !__any_sync(__activemask(), ts.leaf >= 0) : __popc(__ballot_sync(__activemask(), ts.leaf >= 0)) < WF_NODE_K) break;
+                if (__popc(__ballot_sync(__activemask(), ts.leaf >= 0)) < node_k) break;
             }
             if (CULL && WF_LEAF_SPLIT) {
                 if (trav_wants_tri(ts)) leaf_step_culled(sc.tris, ts, stack, o, d);     // one leaf per round, like the loop below
@@ -508,6 +508,13 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
     }
     static const int sort_mode = []{ const int m = wf_knob("GPT_WF_SORT", 3); return m > 9 ? 9 : m; }();
     static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
+    // node-loop exit policy of k_wf_extend_ww (see there).  Small scenes spend half their steps in leaves and want full leaf
+    // phases (k = 3); larger scenes make 15-40 node visits per 1-2 triangle tests, so lanes that hold a leaf should not wait
+    // for the rest of the warp to find one.  Measured extend time, k = 3 / 6 / 10 / 16 (profiles/r01_schedules.md #39): bench scene
+    // (5 k triangles) 16.5 / - / 17.2 (k = 8) / 19.7; dragon 100 k 16.3 / 15.6 / 15.2 / 15.4; 16 cars 157 k 41.1 / 38.3 / 37.7 / 39.4;
+    // dragon 1.6 M 23.3 / 21.3 / 20.7 / 20.9; synthetic 2 M 20.8 / 19.2 / 18.4 / 18.1; 20 M 37.6 / 35.2 / 33.9 / 33.2
+    static const int node_k_env = getenv("GPT_WF_NODE_K") ? wf_knob("GPT_WF_NODE_K", WF_NODE_K) : 0;
+    const int node_k = node_k_env ? node_k_env : (sc.n_tris < (64 << 10) ? WF_NODE_K : (sc.n_tris < (2 << 20) ? 8 : 16));      // 8: between the reference-built dragon's best (6) and the device-built trees' (10)
     const int n_pix = p.width * p.height;
     // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays
     // hold (88 B/path).  Big waves matter: every launch has a fixed cost (launch gap + the tail where the
@@ -553,11 +560,11 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                         k_wf_extend_pool<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                           wb.ray_o, wb.ray_d, wb.hit, refill_min);
                     else if (sc.wnodes) {
-                        if (p.cull) k_wf_extend_ww<true, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                        else k_wf_extend_ww<false, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        if (p.cull) k_wf_extend_ww<true, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min, node_k);
+                        else k_wf_extend_ww<false, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min, node_k);
                     } else if (ext_kind == 1) {
-                        if (p.cull) k_wf_extend_ww<true, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                        else k_wf_extend_ww<false, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min);
+                        if (p.cull) k_wf_extend_ww<true, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min, node_k);
+                        else k_wf_extend_ww<false, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min, node_k);
                     } else
                         k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b,
                                                                      wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);
