@@ -99,7 +99,7 @@ EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string"
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
            "gpt_reduce_resolve_ptrs", "gpt_frame_free",
-           "gpt_set_triangle_materials", "gpt_load_obj", "gpt_load_obj_materials", "gpt_free_host", "gpt_write_png", "gpt_write_pfm", "gpt_save_accum", "gpt_load_accum",
+           "gpt_set_triangle_materials", "gpt_load_obj", "gpt_load_obj_materials", "gpt_free_host", "gpt_write_png", "gpt_write_pfm", "gpt_write_exr", "gpt_save_accum", "gpt_load_accum",
            "gpt_hash64", "gpt_default_spheres", "gpt_default_kernel_info", "gpt_set_camera"]
 
 _lib = None
@@ -164,6 +164,7 @@ def load_library():
     L.gpt_free_host.restype = None
     L.gpt_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
     L.gpt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+    L.gpt_write_exr.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
     L.gpt_save_accum.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64]
     L.gpt_load_accum.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     _lib = L
@@ -263,6 +264,14 @@ def write_pfm(path, rgb, width, height):
     rc = load_library().gpt_write_pfm(os.fsencode(path), a.ctypes.data, int(width), int(height))
     if rc != 0:
         raise GptError("gpt_write_pfm failed (%d)" % rc)
+
+
+def write_exr(path, rgb, width, height):
+    """rgb: host float32 W*H*3, row 0 = bottom (gpt_resolve's out_rgb_f32) -> uncompressed OpenEXR, top row first."""
+    a = np.ascontiguousarray(rgb, dtype=np.float32)
+    rc = load_library().gpt_write_exr(os.fsencode(path), a.ctypes.data, int(width), int(height))
+    if rc != 0:
+        raise GptError("gpt_write_exr failed (%d)" % rc)
 
 
 def save_accum(path, accum_f4, samples_done, seed):

@@ -345,6 +345,55 @@ int gpt_write_pfm(const char* path, const float* rgb, int width, int height)
     return ok ? GPT_OK : GPT_ERR_IO;
 }
 
+// Linear float image as OpenEXR 2.0 (north_star item 3: "headless PNG/EXR output"): single-part scan-line file, no compression,
+// three 32-bit FLOAT channels (stored alphabetically: B, G, R), increasing-Y line order with the TOP row first -- so the bottom-up
+// rows of out_rgb_f32 (row 0 = bottom, tracer.cu:352-358) are written last to first, the same flip gpt_write_png makes.
+// Layout per the OpenEXR file-layout document: magic 20000630, version 2, header attributes (name, type, size, value), a zero
+// byte, the table of 64-bit scan-line offsets, then per scan line: int32 y, int32 byte count, the channels' rows one after another.
+namespace {
+struct ExrBuf {
+    std::vector<unsigned char> b;
+    void raw(const void* p, size_t n) { const unsigned char* c = (const unsigned char*)p; b.insert(b.end(), c, c + n); }
+    void str(const char* z) { raw(z, strlen(z) + 1); }
+    void i32(int32_t v) { raw(&v, 4); }
+    void f32(float v) { raw(&v, 4); }
+    void attr(const char* name, const char* type, int32_t size) { str(name); str(type); i32(size); }
+};
+}
+
+int gpt_write_exr(const char* path, const float* rgb, int width, int height)
+{
+    if (!path || !rgb || width <= 0 || height <= 0) return GPT_ERR_INVALID;
+    ExrBuf h;
+    h.i32(20000630); h.i32(2);
+    h.attr("channels", "chlist", 3 * 18 + 1);
+    for (const char* ch : {"B", "G", "R"}) { h.str(ch); h.i32(2 /* FLOAT */); h.i32(0 /* pLinear + reserved */); h.i32(1); h.i32(1); }
+    h.b.push_back(0);
+    h.attr("compression", "compression", 1); h.b.push_back(0 /* NO_COMPRESSION */);
+    h.attr("dataWindow", "box2i", 16); h.i32(0); h.i32(0); h.i32(width - 1); h.i32(height - 1);
+    h.attr("displayWindow", "box2i", 16); h.i32(0); h.i32(0); h.i32(width - 1); h.i32(height - 1);
+    h.attr("lineOrder", "lineOrder", 1); h.b.push_back(0 /* INCREASING_Y */);
+    h.attr("pixelAspectRatio", "float", 4); h.f32(1.0f);
+    h.attr("screenWindowCenter", "v2f", 8); h.f32(0.0f); h.f32(0.0f);
+    h.attr("screenWindowWidth", "float", 4); h.f32(1.0f);
+    h.b.push_back(0);                                            // end of header
+    const uint64_t line_bytes = 8 + 12 * (uint64_t)width;        // y, size, three float rows
+    uint64_t off = h.b.size() + 8 * (uint64_t)height;
+    for (int y = 0; y < height; ++y, off += line_bytes) h.raw(&off, 8);
+    FILE* f = fopen(path, "wb");
+    if (!f) return GPT_ERR_IO;
+    bool ok = fwrite(h.b.data(), 1, h.b.size(), f) == h.b.size();
+    std::vector<float> row(3 * (size_t)width);
+    for (int y = 0; y < height && ok; ++y) {
+        const float* src = rgb + 3 * (size_t)width * (size_t)(height - 1 - y);     // EXR y = 0 is the top row
+        for (int x = 0; x < width; ++x) { row[x] = src[3 * x + 2]; row[width + x] = src[3 * x + 1]; row[2 * (size_t)width + x] = src[3 * x]; }
+        const int32_t hdr[2] = {y, (int32_t)(12 * width)};
+        ok = fwrite(hdr, 4, 2, f) == 2 && fwrite(row.data(), sizeof(float), row.size(), f) == row.size();
+    }
+    ok = (fclose(f) == 0) && ok;
+    return ok ? GPT_OK : GPT_ERR_IO;
+}
+
 // Accumulation checkpoint / resume: the reference keeps accumBuffer + constantPdf in process memory
 // only (BasicScene.cpp:399).  File = "GPTACC1\0", int32 width, height, uint64 samples done, uint64 seed, then W*H
 // float4 (sum r, g, b, sample count) as gpt_render accumulates them.

@@ -10,7 +10,7 @@
 //
 //   gpt_headless --obj scene.obj [--width 1280 --height 720 --spp 64 --depth 4 --mat diff|metal|spec|refr]
 //                [--col r g b --emi r g b --bk r g b --phong 30 --air 1.0 --glass 1.4 --no-cull]
-//                [--cam x y z yaw pitch] [--dist d] [--seed 0] [--mtl] [--checkpoint f] [--resume f] [--legacy] [--frames-per-pass 16] [--png out.png] [--pfm out.pfm]
+//                [--cam x y z yaw pitch] [--dist d] [--seed 0] [--mtl] [--checkpoint f] [--resume f] [--legacy] [--frames-per-pass 16] [--png out.png] [--pfm out.pfm] [--exr out.exr]
 #include "../../include/gpt.h"
 #include <chrono>
 #include <cstdio>
@@ -30,7 +30,7 @@ static int die(gpt_ctx* ctx, const char* what, int rc)
 
 int main(int argc, char** argv)
 {
-    std::string obj, png = "render.png", pfm, checkpoint, resume;
+    std::string obj, png = "render.png", pfm, exr, checkpoint, resume;
     bool use_mtl = false;
     int width = 1280, height = 720, device = 0;              // App/main.cpp:12
     unsigned spp = 16, depth = 4, per_pass = 16;
@@ -46,6 +46,7 @@ int main(int argc, char** argv)
         if (a == "--obj") { need(i, 1); obj = argv[++i]; }
         else if (a == "--png") { need(i, 1); png = argv[++i]; }
         else if (a == "--pfm") { need(i, 1); pfm = argv[++i]; }
+        else if (a == "--exr") { need(i, 1); exr = argv[++i]; }
         else if (a == "--checkpoint") { need(i, 1); checkpoint = argv[++i]; }   // write float4 sums + sample count at the end
         else if (a == "--resume") { need(i, 1); resume = argv[++i]; }           // continue a checkpoint (same size and seed)
         else if (a == "--mtl") use_mtl = true;                                  // per-triangle materials from the OBJ's mtllib (N4)
@@ -167,6 +168,11 @@ int main(int argc, char** argv)
         rc = gpt_write_pfm(pfm.c_str(), rgb.data(), width, height);
         if (rc) { fprintf(stderr, "gpt_headless: cannot write %s\n", pfm.c_str()); gpt_destroy(ctx); return 1; }
         printf("wrote %s\n", pfm.c_str());
+    }
+    if (!exr.empty()) {
+        rc = gpt_write_exr(exr.c_str(), rgb.data(), width, height);
+        if (rc) { fprintf(stderr, "gpt_headless: cannot write %s\n", exr.c_str()); gpt_destroy(ctx); return 1; }
+        printf("wrote %s\n", exr.c_str());
     }
     if (bvh.bvh.dev_triNode) gpt_free_bvh(ctx, &bvh);
     gpt_destroy(ctx);

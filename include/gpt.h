@@ -280,6 +280,9 @@ GPT_API int  gpt_save_accum(const char* path, const float* host_accum_f4, int wi
 GPT_API int  gpt_load_accum(const char* path, float* host_accum_f4, int width, int height, uint64_t* samples_done, uint64_t* seed);
 /* linear float RGB (gpt_resolve's out_rgb_f32, copied to the host) -> PFM, bottom row first */
 GPT_API int  gpt_write_pfm(const char* path, const float* host_rgb, int width, int height);
+/* the same image as OpenEXR 2.0 (north_star item 3: headless PNG/EXR output instead of the GL texture, BasicScene.cpp:424-432):
+ * single-part scan-line file, uncompressed, 32-bit FLOAT channels B, G, R, top row first */
+GPT_API int  gpt_write_exr(const char* path, const float* host_rgb, int width, int height);
 
 #ifdef __cplusplus
 }

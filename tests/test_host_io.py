@@ -4,6 +4,7 @@ import struct
 import zlib
 
 import numpy as np
+import pytest
 
 from support import objio, scenes
 
@@ -80,6 +81,62 @@ def test_png_and_pfm_writers(gpt, tmp_path):
     blob = open(p, "rb").read()
     assert blob.startswith(b"PF\n7 5\n-1.0\n")
     np.testing.assert_array_equal(np.frombuffer(blob[len(b"PF\n7 5\n-1.0\n"):], np.float32).reshape(5, 7, 3), rgb)
+
+
+def _exr_pixels(path):
+    """Minimal reader of what gpt_write_exr writes (OpenEXR file layout: magic, version, attributes, offset table, scan lines)."""
+    import struct
+    b = open(path, "rb").read()
+    assert struct.unpack_from("<ii", b, 0) == (20000630, 2)
+    pos, attrs = 8, {}
+    while b[pos] != 0:
+        e = b.index(b"\0", pos); name = b[pos:e].decode(); pos = e + 1
+        e = b.index(b"\0", pos); typ = b[pos:e].decode(); pos = e + 1
+        (size,) = struct.unpack_from("<i", b, pos); pos += 4
+        attrs[name] = (typ, b[pos:pos + size]); pos += size
+    pos += 1
+    assert attrs["compression"] == ("compression", b"\0") and attrs["lineOrder"] == ("lineOrder", b"\0")
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1])
+    assert attrs["displayWindow"][1] == attrs["dataWindow"][1] and (x0, y0) == (0, 0)
+    w, h = x1 + 1, y1 + 1
+    ch, names, q = attrs["channels"][1], [], 0
+    while ch[q] != 0:
+        e = ch.index(b"\0", q); names.append(ch[q:e].decode())
+        assert struct.unpack_from("<i4Bii", ch, e + 1) == (2, 0, 0, 0, 0, 1, 1)      # FLOAT, pLinear 0, sampling 1 x 1
+        q = e + 1 + 16
+    assert names == ["B", "G", "R"] and q == len(ch) - 1
+    offs = struct.unpack_from("<%dQ" % h, b, pos)
+    img = np.zeros((h, w, 3), np.float32)
+    for y in range(h):
+        yy, nbytes = struct.unpack_from("<ii", b, offs[y])
+        assert yy == y and nbytes == 12 * w
+        rows = np.frombuffer(b, np.float32, 3 * w, offs[y] + 8).reshape(3, w)
+        img[y, :, 2], img[y, :, 1], img[y, :, 0] = rows[0], rows[1], rows[2]
+    assert offs[-1] + 8 + 12 * w == len(b)
+    return img
+
+
+def test_exr_writer(gpt, tmp_path):
+    rng = np.random.default_rng(1)
+    for w, h in [(7, 5), (64, 33)]:
+        rgb = (rng.random((h, w, 3)) * 10.0).astype(np.float32)
+        rgb[0, 0] = (np.inf, -0.0, 1e-40)                            # float data is stored untouched
+        p = str(tmp_path / ("t%d.exr" % w))
+        gpt.write_exr(p, rgb, w, h)
+        got = _exr_pixels(p)
+        np.testing.assert_array_equal(got.view(np.uint32), rgb[::-1].view(np.uint32))     # row 0 of the buffer is the bottom row
+    # an independent reader where the image has one: OpenCV's OpenEXR codec (BGR, top row first)
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    try:
+        import cv2
+        img = cv2.imread(p, cv2.IMREAD_UNCHANGED)
+    except Exception:
+        img = None
+    if img is not None:
+        finite = rgb[::-1][..., ::-1].copy()
+        np.testing.assert_array_equal(img[1:], finite[1:])           # row 0 holds the inf / denormal probes
+    with pytest.raises(gpt.GptError):
+        gpt.write_exr(str(tmp_path / "no_such_dir" / "x.exr"), rgb, w, h)
 
 
 def test_load_obj_with_mtl(gpt, tmp_path):
