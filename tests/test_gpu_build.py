@@ -245,9 +245,9 @@ def test_headless_cli_renders_an_obj_like_the_library(gpt, torch_cuda, tmp_path)
     obj = str(tmp_path / "scene.obj")
     objio.write_obj(obj, sc["verts"], sc["faces"])
     W, H, SPP = 160, 90, 12
-    png, pfm = str(tmp_path / "o.png"), str(tmp_path / "o.pfm")
+    png, pfm, exr = str(tmp_path / "o.png"), str(tmp_path / "o.pfm"), str(tmp_path / "o.exr")
     out = subprocess.run([exe, "--obj", obj, "--width", str(W), "--height", str(H), "--spp", str(SPP), "--frames-per-pass", "5", "--depth", "5",
-                          "--mat", "spec", "--seed", "3", "--dist", "1.5", "--png", png, "--pfm", pfm], capture_output=True, text=True, timeout=300)
+                          "--mat", "spec", "--seed", "3", "--dist", "1.5", "--png", png, "--pfm", pfm, "--exr", exr], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "built on the device" in out.stdout
     blob = open(pfm, "rb").read()
@@ -273,6 +273,8 @@ def test_headless_cli_renders_an_obj_like_the_library(gpt, torch_cuda, tmp_path)
     im = np.array(Image.open(png))
     pack = (np.float32(255.0) * np.clip(want, 0, 1)).astype(np.int32).astype(np.uint8)[::-1]
     np.testing.assert_array_equal(im, pack)
+    from test_host_io import _exr_pixels                             # the EXR carries the same floats, top row first
+    np.testing.assert_array_equal(_exr_pixels(exr), want[::-1])
 
 
 def test_headless_cli_checkpoint_resume_and_mtl(gpt, torch_cuda, tmp_path):
