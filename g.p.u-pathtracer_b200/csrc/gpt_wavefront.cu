@@ -2,9 +2,10 @@
 // ray queues").  Same per-sample arithmetic as the megakernel (gpt_shade.cuh / gpt_traverse.cuh), so both
 // produce bit-identical images; what changes is the schedule:
 //
-//   wave = every pixel of the frame x ONE global sample index          (path id == pixel index)
+//   wave = a run of pixels x a run of global sample indices, up to 64 M paths   (path id = sample-major, then pixel)
 //   k_wf_generate : camera ray + path state for the whole wave                       (tracer.cu:61-69)
-//   per bounce    : k_wf_extend  persistent warps pull rays from the queue and traverse the BVH; a lane
+//   per bounce    : k_wf_extend_ww (default; k_wf_extend / k_wf_extend_pool are A/B schedules)
+//                                persistent warps pull rays from the queue and traverse the BVH; a lane
 //                                whose ray ends is re-armed with the next queued ray (a 32-byte load), so
 //                                short rays never wait for long ones                  (cudaUtils.h:256-460)
 //                   k_wf_shade   one thread per surviving path: sphere sweep, shading, next ray, and
