@@ -30,6 +30,7 @@ FLAG_WIDE_BVH = 1 << 5        # always traverse the 4-wide quantised tree (SURVE
 FLAG_BINARY_BVH = 1 << 6      # always traverse the binary tree as uploaded
 FLAG_WAVEFRONT = 1 << 7       # always the wavefront pipeline (default: megakernel for calls under GPT_SMALL_FRAME_PATHS paths)
 FLAG_BUILD_LBVH = 1 << 8      # build_bvh: Morton radix tree instead of PLOC clustering
+FLAG_NO_TRIAL = 1 << 9        # no timed per-scene trial: render calls never synchronise (graph capture, strict asynchrony)
 K_GENERATE, K_EXTEND, K_SHADE, K_COLLECT, K_ACCUMULATE, K_RESOLVE, K_OTHER = range(7)
 
 
@@ -94,7 +95,7 @@ assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 
 # every symbol include/gpt.h declares (tests check the library exports each one)
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
-           "gpt_upload_scene", "gpt_launch", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
+           "gpt_upload_scene", "gpt_launch", "gpt_invalidate_scene", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
            "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
@@ -125,6 +126,7 @@ def load_library():
     L.gpt_upload_scene.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
                                    C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int]
     L.gpt_launch.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_void_p]
+    L.gpt_invalidate_scene.argtypes = [C.c_void_p]
     L.gpt_render.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p]
     L.gpt_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gpt_render_frame_host.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]
@@ -363,6 +365,10 @@ class Context:
     def launch(self, info, stream=None):
         """Drop-in for BasicScene::launchKernel (tracer.cu:405-415): one legacy 1-spp pass."""
         self._ck(self._L.gpt_launch(self._h, C.byref(info), _ptr(stream)), "gpt_launch")
+
+    def invalidate_scene(self):
+        """The caller rewrote kernelInfo.bvhData's arrays in place: the next launch() re-packs them (gpt.h, pointer-identity rule)."""
+        self._ck(self._L.gpt_invalidate_scene(self._h), "gpt_invalidate_scene")
 
     def render(self, info, accum_f4, seed, sample_begin, sample_count, stream=None):
         self._ck(self._L.gpt_render(self._h, C.byref(info), _ptr(accum_f4), C.c_uint64(seed), C.c_uint64(sample_begin),

@@ -16,7 +16,7 @@ struct gpt_ctx {
     int sm_count = 0;
     uint32_t flags = 0;
     // uploaded scene (owned)
-    float4* nodes = nullptr; float4* tris = nullptr; int n_nodes = 0; int n_tris = 0;
+    float4* nodes = nullptr; float4* tris = nullptr; int n_nodes = 0; int n_tris = 0; int tree_depth = 0;
     float* spheres = nullptr; int n_spheres = 0;
     float* boxes = nullptr; int n_boxes = 0;
     float* tri_mats = nullptr; int* face_mat = nullptr; int n_tri_mats = 0, n_faces = 0;   // N4, survive scene re-uploads
@@ -34,6 +34,8 @@ struct gpt_ctx {
     unsigned long long* stats = nullptr;       // [0]=rays [1]=paths [2..17]=rays by bounce
     float4* frame_accum = nullptr; uint32_t* frame_rgba = nullptr; size_t frame_pixels = 0;
     WaveBuffers wave = {}; size_t wave_pixels = 0; size_t wave_counters = 0;   // wavefront scratch
+    WaveLaunchCfg wave_cfg = {};
+    bool wave_dirty = false;                  // a render call failed half-way: the queue counters must be re-zeroed before the next
     unsigned long long launches = 0;
     // multi-GPU peer frames
     float4* frames = nullptr; int frame_w = 0, frame_h = 0, frame_n = 0;
@@ -131,6 +133,7 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     CU(c, cudaMalloc(&w.queue[0], want * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], want * sizeof(uint32_t)));
     CU(c, cudaMalloc(&w.lsum, n_pix * sizeof(float4)));
     CU(c, cudaMalloc(&w.counters, nc * sizeof(unsigned int)));
+    CU(c, cudaMemset(w.counters, 0, nc * sizeof(unsigned int)));       // kept zero between calls by the pipeline's last kernel
     w.capacity = want;
     c->wave_pixels = n_pix; c->wave_counters = nc;
     w.sort_keys[0] = w.sort_keys[1] = w.sort_vals = nullptr; w.sort_tmp = nullptr; w.sort_tmp_bytes = 0;
@@ -148,9 +151,12 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
 //          wide from 1 Mi triangles);
 //   order: GPT_WF_SORT=0 never, =1..9 always (key layout); GPT_SORT_MIN_TRIS=n a size threshold; never under 256 Ki packed
 //          triangles; otherwise on trial (default until decided: path order).
-// Trial: the first large render calls (>= 1 Mi paths) after a scene upload run each open candidate twice -- one warm-up call, one
-// timed call bracketed by events and a stream synchronise -- binary / path order, wide / path order, then the faster tree
+// Trial: the first large render calls (>= 1 Mi paths) after a scene upload run each open candidate three times -- one warm-up
+// call, two timed calls bracketed by events and a stream synchronise, the faster of which counts (one noisy measurement must
+// not pin the slower path for the lifetime of the scene) -- binary / path order, wide / path order, then the faster tree
 // re-ordered; ns per ray decide (the wide tree must win by 2 %, re-ordering by 3 %).  At most six calls synchronise.
+// GPT_FLAG_NO_TRIAL (or GPT_NO_TRIAL=1): never -- every render call is then asynchronous and capturable; the size defaults apply.
+static const bool k_env_no_trial = []{ const char* e = getenv("GPT_NO_TRIAL"); return e && *e && *e != '0'; }();
 static const long long k_env_wide_min = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : -2ll; }();   // -2 = unset
 static const int k_env_sort = []{ const char* e = getenv("GPT_WF_SORT"); return e ? atoi(e) : -1; }();
 static const long long k_env_sort_min = []{ const char* e = getenv("GPT_SORT_MIN_TRIS"); return e ? atoll(e) : -2ll; }();
@@ -202,9 +208,9 @@ static TraversalPlan traversal_plan(const gpt_ctx* c, size_t n_paths)
     TraversalPlan pl = {current_wide(c), current_sort(c), false, false, -1};
     const int t = tree_choice(c), s = sort_choice(c);
     const int n_tree = t < 0 ? 2 : 1, n_cand = n_tree + (s < 0 ? 1 : 0);
-    if (c->tune_done || n_cand < 2 || n_paths < ((size_t)1 << 20)) return pl;
-    const int cand = c->tune_step / 2;
-    pl.trial = true; pl.timed = (c->tune_step & 1) != 0;
+    if (c->tune_done || n_cand < 2 || n_paths < ((size_t)1 << 20) || (c->flags & GPT_FLAG_NO_TRIAL) || k_env_no_trial) return pl;
+    const int cand = c->tune_step / 3;
+    pl.trial = true; pl.timed = (c->tune_step % 3) != 0;
     if (cand < n_tree) {                                          // a tree candidate, rays in path order
         pl.wide = t < 0 ? cand == 1 : t == 1;
         pl.sort = false;
@@ -220,7 +226,7 @@ static void trial_advance(gpt_ctx* c)
 {
     const int t = tree_choice(c), s = sort_choice(c);
     const int n_tree = t < 0 ? 2 : 1, n_cand = n_tree + (s < 0 ? 1 : 0);
-    if (++c->tune_step < 2 * n_cand) return;
+    if (++c->tune_step < 3 * n_cand) return;
     c->tune_done = true;
     c->tuned_wide = t < 0 ? (c->tune_ns[1] > 0.0 && c->tune_ns[0] > 0.0 && c->tune_ns[1] < 0.98 * c->tune_ns[0]) : t == 1;
     const double path = c->tune_ns[c->tuned_wide ? 1 : 0];
@@ -258,9 +264,11 @@ static int render_wavefront(gpt_ctx* c, const DevScene& sc_in, const RenderParam
         CU(c, cudaEventCreate(&e0)); CU(c, cudaEventCreate(&e1));
         CU(c, cudaEventRecord(e0, st));
     }
-    cudaError_t e = gptk_render_wavefront(sc, p, wb, accum_f4, accum_v3, draw, constant_pdf, sample_begin, sample_count,
-                                          c->stats, c->sm_count, st, &c->launches, (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);
-    if (e != cudaSuccess) { if (e0) { cudaEventDestroy(e0); cudaEventDestroy(e1); } return fail(c, GPT_ERR_CUDA, "render launch", e); }
+    if (!c->wave_cfg.ready) gptk_wave_launch_cfg(&c->wave_cfg, c->sm_count);
+    if (c->wave_dirty) { CU(c, cudaMemsetAsync(wb.counters, 0, c->wave_counters * sizeof(unsigned int), st)); c->wave_dirty = false; }
+    cudaError_t e = gptk_render_wavefront(sc, p, wb, c->wave_cfg, accum_f4, accum_v3, draw, constant_pdf, sample_begin, sample_count,
+                                          c->stats, st, &c->launches, (c->flags & GPT_FLAG_TIME_KERNELS) ? &c->timer : nullptr);
+    if (e != cudaSuccess) { c->wave_dirty = true; if (e0) { cudaEventDestroy(e0); cudaEventDestroy(e1); } return fail(c, GPT_ERR_CUDA, "render launch", e); }
     if (pl.timed) {
         float ms = 0.0f;
         cudaEventRecord(e1, st);
@@ -269,7 +277,8 @@ static int render_wavefront(gpt_ctx* c, const DevScene& sc_in, const RenderParam
         if (e == cudaSuccess) e = cudaMemcpy(&rays1, c->stats, sizeof(rays1), cudaMemcpyDeviceToHost);
         cudaEventDestroy(e0); cudaEventDestroy(e1);
         if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "traversal trial", e);
-        c->tune_ns[pl.slot] = rays1 > rays0 ? (double)ms * 1e6 / (double)(rays1 - rays0) : 0.0;
+        const double ns = rays1 > rays0 ? (double)ms * 1e6 / (double)(rays1 - rays0) : 0.0;
+        if (ns > 0.0 && (c->tune_ns[pl.slot] <= 0.0 || ns < c->tune_ns[pl.slot])) c->tune_ns[pl.slot] = ns;      // best of the two timed calls
     }
     if (pl.trial) trial_advance(c);
     return GPT_OK;
@@ -317,10 +326,12 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
     c->launches += 2;
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "device re-pack", e);
     if (r.bad_layout) {
-        char buf[128]; snprintf(buf, sizeof(buf), "malformed BVH arrays (code %d): not a CudaBVH BVHLayout_Compact tree", r.bad_layout);
+        char buf[160];
+        if (r.bad_layout == 5) snprintf(buf, sizeof(buf), "BVH has %d or more inner levels: deeper than the %d-entry traversal stack (cudaUtils.h:22)", GPT_STACK_SIZE, GPT_STACK_SIZE);
+        else snprintf(buf, sizeof(buf), "malformed BVH arrays (code %d): not a CudaBVH BVHLayout_Compact tree", r.bad_layout);
         return fail(c, GPT_ERR_LAYOUT, buf);
     }
-    c->nodes = r.nodes; c->tris = r.tris; c->n_nodes = r.n_nodes; c->n_tris = r.n_tris;
+    c->nodes = r.nodes; c->tris = r.tris; c->n_nodes = r.n_nodes; c->n_tris = r.n_tris; c->tree_depth = r.depth;
     return GPT_OK;
 }
 
@@ -402,7 +413,7 @@ int gpt_build_bvh(gpt_ctx* c, const float* verts, size_t n_verts, const int32_t*
         e = gptk_build_lbvh(on_device ? verts : dv, n_verts, on_device ? tris : dt, n_tris, max_leaf_size ? (int)max_leaf_size : 8, radius, &r, 0);
         c->launches += (unsigned long long)r.launches;
         if (e != cudaSuccess || radius <= 0) break;
-        const bool deep = r.status == 0 && r.depth > GPT_STACK_SIZE;
+        const bool deep = r.status == 0 && r.depth >= GPT_STACK_SIZE;      // sp reaches `depth`: int stack[GPT_STACK_SIZE] holds depth <= 63
         if (!deep && r.status != 4 && r.status != 5) break;
         if (deep) { cudaFree(r.nodes); cudaFree(r.tris); cudaFree(r.indices); }
         radius = 0;
@@ -413,9 +424,9 @@ int gpt_build_bvh(gpt_ctx* c, const float* verts, size_t n_verts, const int32_t*
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     cudaFree(dv); cudaFree(dt);
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "gpt_build_bvh", e);
-    if (r.status == 0 && r.depth > GPT_STACK_SIZE) { cudaFree(r.nodes); cudaFree(r.tris); cudaFree(r.indices); r.status = 4; }
+    if (r.status == 0 && r.depth >= GPT_STACK_SIZE) { cudaFree(r.nodes); cudaFree(r.tris); cudaFree(r.indices); r.status = 4; }
     if (r.status) {
-        static const char* why[] = {"", "vertex index out of range", "non-finite vertex", "mesh too large for 32-bit offsets", "tree deeper than the 64-entry traversal stack", "clustering did not converge"};
+        static const char* why[] = {"", "vertex index out of range", "non-finite vertex", "mesh too large for 32-bit offsets", "tree deeper than the 64-entry traversal stack (63 inner levels)", "clustering did not converge"};
         char buf[128]; snprintf(buf, sizeof(buf), "gpt_build_bvh: %s", why[r.status < 6 ? r.status : 0]);
         return fail(c, r.status == 3 || r.status == 4 ? GPT_ERR_LAYOUT : GPT_ERR_INVALID, buf);
     }
@@ -560,6 +571,13 @@ static int launch_scene(gpt_ctx* c, const gpt_kernel_info* info, DevScene* sc)
         if (info->numSpheres > (1u << 20)) return fail(c, GPT_ERR_INVALID, "numSpheres out of range");
         sc->spheres = reinterpret_cast<const float*>(info->sphereTex); sc->n_spheres = (int)info->numSpheres;
     }
+    return GPT_OK;
+}
+
+int gpt_invalidate_scene(gpt_ctx* c)
+{
+    if (!c) return GPT_ERR_INVALID;
+    c->src_nodes = c->src_tris = c->src_idx = nullptr;      // the next gpt_launch that carries BVH pointers re-packs them
     return GPT_OK;
 }
 

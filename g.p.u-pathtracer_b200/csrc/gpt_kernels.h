@@ -55,7 +55,7 @@ cudaError_t gptk_reduce_resolve(const float4* const* frames, int n_frames, int n
 
 // device re-pack (gpt_repack.cu): reference arrays (device pointers) -> packed nodes / triangles.
 // *out_nodes / *out_tris are cudaMalloc'd by the callee; returns the packed triangle count.
-struct RepackResult { float4* nodes; float4* tris; int n_nodes; int n_tris; int bad_layout; };
+struct RepackResult { float4* nodes; float4* tris; int n_nodes; int n_tris; int bad_layout; int depth; };   // bad_layout 5 = deeper than the traversal stack
 cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float4* ref_tris, size_t n_tri_vec4,
                         const int* ref_indices, size_t n_indices, RepackResult* out, cudaStream_t st);
 
@@ -86,8 +86,12 @@ struct WaveBuffers {
 };
 size_t gptk_wave_counter_count(unsigned int depth);
 size_t gptk_wave_sort_tmp_bytes(size_t capacity);
-cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,
+// per-context launch configuration of the pipeline (grids from the kernels' occupancy on this device, environment knobs)
+struct WaveLaunchCfg { int ready, sm_count, ext_grid, wide_grid, shade_grid, sort_mode, refill_min, node_k_env; size_t wave_cap_env; };
+void gptk_wave_launch_cfg(WaveLaunchCfg* cfg, int sm_count);
+// wb.counters must be all zero on entry and are all zero again once the enqueued work has run
+cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb, const WaveLaunchCfg& cfg,
                                   float4* accum_f4, float* accum_v3, uint32_t* draw, unsigned long long constant_pdf,
                                   unsigned long long sample_begin, uint32_t sample_count,
-                                  unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches,
+                                  unsigned long long* stats, cudaStream_t st, unsigned long long* launches,
                                   KernelTimer* kt);

@@ -80,10 +80,23 @@ __global__ void k_write_packed(const float4* __restrict__ ref_nodes, int n_inner
     }
 }
 
+// Depth of the packed tree (root = level 1), level by level: a node's level is its parent's + 1, children sit behind their
+// parents (checked by k_count_leaf_tris), so pass k fixes every node of level k + 1.  The traversal keeps one stack entry per
+// inner level below the root plus the sentinel (cudaUtils.h:22,259 sizes it 64 for the builder's MaxDepth 64,
+// SplitBVHBuilder.hpp:15): a tree of GPT_STACK_SIZE or more levels would write past the per-thread stack, so it is rejected.
+__global__ void k_node_levels(const float4* __restrict__ nodes, const int n_inner, int* __restrict__ level, const int pass, int* __restrict__ changed)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_inner || level[i] != pass) return;
+    const int4 ch = *reinterpret_cast<const int4*>(nodes + 4 * (size_t)i + 3);
+    if (ch.x >= 0) { level[ch.x >> 2] = pass + 1; *changed = 1; }
+    if (ch.y >= 0) { level[ch.y >> 2] = pass + 1; *changed = 1; }
+}
+
 cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float4* ref_tris, size_t n_tri_vec4,
                         const int* ref_indices, size_t n_indices, RepackResult* out, cudaStream_t st)
 {
-    out->nodes = nullptr; out->tris = nullptr; out->n_nodes = 0; out->n_tris = 0; out->bad_layout = 0;
+    out->nodes = nullptr; out->tris = nullptr; out->n_nodes = 0; out->n_tris = 0; out->bad_layout = 0; out->depth = 0;
     const int n_inner = (int)(n_node_vec4 / 4);
     if (n_inner == 0) return cudaSuccess;
     if (n_node_vec4 % 4 != 0 || n_node_vec4 / 4 > 0x1fffffffull) { out->bad_layout = 4; return cudaSuccess; }
@@ -114,6 +127,24 @@ cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(st));
         out->n_nodes = n_inner; out->n_tris = h_total;
+        // tree depth (the counts array is free again: reuse it for the levels)
+        CK(cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)n_inner, st));
+        { const int one = 1; CK(cudaMemcpyAsync(counts, &one, sizeof(int), cudaMemcpyHostToDevice, st)); }
+        int depth = 1;
+        for (; depth <= GPT_STACK_SIZE; ++depth) {
+            int h_changed = 0;
+            CK(cudaMemsetAsync(bad, 0, sizeof(int), st));
+            k_node_levels<<<(n_inner + 255) / 256, 256, 0, st>>>(out->nodes, n_inner, counts, depth, bad);
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(&h_changed, bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            if (!h_changed) break;
+        }
+        out->depth = depth;
+        if (depth >= GPT_STACK_SIZE) {
+            cudaFree(out->nodes); cudaFree(out->tris); out->nodes = nullptr; out->tris = nullptr; out->n_nodes = out->n_tris = 0;
+            out->bad_layout = 5;
+        }
     }
 done:
     cudaFree(counts); cudaFree(offsets); cudaFree(bad); cudaFree(tmp);

@@ -57,6 +57,9 @@ __device__ __forceinline__ f3 box_normal(const float* bx, f3 p)
 // accu_slot != nullptr (wavefront pipeline): the accumulated colour lives in memory and ps.accu is not used.  It changes
 // only on a miss (overwritten with the background, no read) and on an emitting hit (read-modify-write); on any other
 // hit fma(mask, 0, accu) == accu bit for bit for a finite mask, so the slot is neither read nor written.
+// FIRST (bounce 0 of the wavefront pipeline): the accumulated colour is still 0 (tracer.cu:69) and the slot holds nothing yet:
+// it is written unconditionally, never read.
+template <bool FIRST = false>
 __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderParams& p,
                                              const float* s_spheres, const float* s_boxes,
                                              const SceneHit h, const uint32_t pixel, const uint64_t sample,
@@ -101,7 +104,9 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
         emit = mk3(bx[6], bx[7], bx[8]); objcol = mk3(bx[9], bx[10], bx[11]); mat = __float_as_int(bx[12]);
     }
-    if (accu_slot) {
+    if (FIRST && accu_slot) {
+        *accu_slot = make_float4(fmaf(ps.mask.x, emit.x, 0.0f), fmaf(ps.mask.y, emit.y, 0.0f), fmaf(ps.mask.z, emit.z, 0.0f), 0.0f);
+    } else if (accu_slot) {
         const bool touch = emit.x != 0.0f || emit.y != 0.0f || emit.z != 0.0f
                            || !(fabsf(ps.mask.x) <= GPT_F32_MAX) || !(fabsf(ps.mask.y) <= GPT_F32_MAX) || !(fabsf(ps.mask.z) <= GPT_F32_MAX);
         if (touch) {

@@ -3,14 +3,16 @@
 // produce bit-identical images; what changes is the schedule:
 //
 //   wave = a run of pixels x a run of global sample indices, up to 64 M paths   (path id = sample-major, then pixel)
-//   k_wf_generate : camera ray + path state for the whole wave                       (tracer.cu:61-69)
+//   bounce 0      : no generate pass -- the first extend and the first shade both derive the camera ray from the path id
+//                   (tracer.cu:61-69; two Philox blocks cost less than writing and re-reading 52 B of state per path)
 //   per bounce    : k_wf_extend_ww (default; k_wf_extend / k_wf_extend_pool are A/B schedules)
 //                                persistent warps pull rays from the queue and traverse the BVH; a lane
 //                                whose ray ends is re-armed with the next queued ray (a 32-byte load), so
 //                                short rays never wait for long ones                  (cudaUtils.h:256-460)
 //                   k_wf_shade   one thread per surviving path: sphere sweep, shading, next ray, and
 //                                compaction of the survivors into the next queue      (tracer.cu:98-296)
-//   k_wf_accumulate : launch sums -> caller's accumulation buffer                    (tracer.cu:386-398)
+//   k_wf_accumulate : the wave's finished samples, summed per pixel in sample order -> caller's accumulation buffer
+//                     (tracer.cu:374,386-398); launches of several waves go through k_wf_collect + per-pixel launch sums
 //
 // ncu evidence for this choice over the megakernel is in profiles/ (r01_mega_*): with secondary rays the
 // per-ray traversal length is heavy tailed (mean 10.8 node+triangle steps, ~41 for the slowest lane of a
@@ -54,104 +56,38 @@ __device__ __forceinline__ void stage_prims(const DevScene& sc, SmemPrims& sm, c
     __syncthreads();
 }
 
-// counters layout (unsigned int): [0 .. depth]        n_q[b]   = paths alive at the start of bounce b
+// counters layout (unsigned int): [0 .. depth]        n_q[b]   = paths alive at the start of bounce b  (b >= 1; bounce 0 = the whole wave)
 //                                 [depth+1 .. 2depth+1] fetch[b] = extend's work-fetch cursor of bounce b
-__global__ void __launch_bounds__(256)
-k_wf_generate(const RenderParams p, const unsigned long long sample0, const int n_samples, const int pix0, const int n_wave,
-              float4* __restrict__ ray_o, float4* __restrict__ ray_d, float* __restrict__ mask_z, float4* __restrict__ accu,
-              unsigned int* __restrict__ counters, unsigned long long* __restrict__ stats)
+// path id = s_local * n_wave + i  <->  (global sample sample0 + s_local, pixel pix0 + i): sample-major, so the lanes of a warp
+// hold neighbouring pixels of the same sample.  At bounce 0 there is no queue and no stored ray: path ids run 0 .. n_paths-1
+// and the camera ray is a function of the id.
+struct PrimaryGen { RenderParams p; unsigned long long sample0; int pix0; int n_wave; unsigned n_paths; };
+
+__device__ __forceinline__ void primary_ray(const PrimaryGen& g, const uint32_t pid, PathState& ps)
 {
-    // path id = s_local * n_wave + i  <->  (global sample sample0 + s_local, pixel pix0 + i): sample-major, so the
-    // lanes of a warp hold neighbouring pixels of the same sample
-    const int n_paths = n_samples * n_wave;
-    for (int pid = blockIdx.x * blockDim.x + threadIdx.x; pid < n_paths; pid += gridDim.x * blockDim.x) {
-        const int s_local = pid / n_wave;
-        const int pixel = pix0 + (pid - s_local * n_wave);
-        PathState ps;
-        start_path(p, pixel % p.width, pixel / p.width, (uint32_t)pixel, sample0 + (unsigned long long)s_local, ps);
-        // the colour mask (tracer.cu:68) rides in the two free w lanes of the ray + one float: 36 B of ray state per path
-        ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, 1.0f);
-        ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, 1.0f);
-        mask_z[pid] = 1.0f;
-        accu[pid] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) { counters[0] = (unsigned)n_paths; atomicAdd(&stats[1], (unsigned long long)n_paths); }
+    const int s_local = (int)(pid / (unsigned)g.n_wave);
+    const int pixel = g.pix0 + (int)(pid - (unsigned)s_local * (unsigned)g.n_wave);
+    start_path(g.p, pixel % g.p.width, pixel / g.p.width, (uint32_t)pixel, g.sample0 + (unsigned long long)s_local, ps);
 }
 
-// Persistent traversal kernel.  Each trip the whole warp either re-arms its idle lanes from the queue, tests
-// one triangle per lane, or visits one inner node per lane -- chosen by vote, so the three code paths are
-// never serialised against each other inside a warp.
-__global__ void __launch_bounds__(WF_THREADS, 8)
-k_wf_extend(const DevScene sc, const int cull, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
-            unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
-            int2* __restrict__ hit, const int refill_min, const int tri_min)
-{
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const unsigned n = *n_ptr;
-    const bool do_cull = cull != 0;
-    int stack[GPT_STACK_SIZE];
-    TravState ts;
-    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
-    uint32_t pid = 0;
-    bool active = false;        // lane holds a ray that is still traversing
-    bool exhausted = false;     // the queue has no more rays for this warp (warp-uniform)
-    ts.node = GPT_SENTINEL; ts.leaf = 0; ts.sp = 0; ts.t = GPT_F32_MAX; ts.tri = -1; ts.tri_cur = 0;
-
-    while (true) {
-        const unsigned m_idle = __ballot_sync(GPT_FULL_MASK, !active);
-        if (m_idle != 0u && !exhausted && (__popc(m_idle) >= refill_min || m_idle == GPT_FULL_MASK)) {
-            // ---- re-arm idle lanes: one atomic per warp ----
-            unsigned base = 0;
-            const int leader = __ffs(m_idle) - 1;
-            if ((int)lane == leader) base = atomicAdd(fetch, (unsigned)__popc(m_idle));
-            base = __shfl_sync(GPT_FULL_MASK, base, leader);
-            if (base + (unsigned)__popc(m_idle) >= n) exhausted = true;      // uniform: this grab reached the end
-            if (!active) {
-                const unsigned j = base + (unsigned)__popc(m_idle & lt_mask);
-                if (j < n) {
-                    pid = queue ? queue[j] : j;
-                    const float4 ro = ray_o[pid], rd = ray_d[pid];
-                    o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
-                    trav_init(ts, stack, o, d, true);
-                    active = true;
-                }
-            }
-            continue;
-        }
-        const unsigned m_node = __ballot_sync(GPT_FULL_MASK, active && trav_wants_node(ts));
-        const unsigned m_tri = __ballot_sync(GPT_FULL_MASK, active && trav_wants_tri(ts));
-        if (m_tri != 0u && (__popc(m_tri) >= tri_min || m_node == 0u)) {
-            if (active && trav_wants_tri(ts)) tri_step(sc.tris, ts, stack, o, d, do_cull);
-        } else if (m_node != 0u) {
-            if (active && trav_wants_node(ts)) node_step(sc.nodes, ts, stack);
-        } else {
-            break;          // nothing traversing; the refill branch above did not fire => queue exhausted
-        }
-        if (active && trav_finished(ts)) {
-            hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
-            active = false;
-        }
-    }
-}
-
-// Alternative schedule of the same traversal (A/B kept for the ncu comparison in profiles/): the classic
-// persistent while-while loop.  All lanes meet at the top of the outer loop once per "descend to the next leaf +
-// test that leaf" round; idle lanes are re-armed there.  Tighter inner loops than the voted steps above, but
-// lanes wait for the slowest descent / largest leaf of the round.
+// Persistent while-while traversal kernel (cudaUtils.h:256-460).  All lanes of a warp meet at the top of the outer loop once
+// per "descend to the next leaf + test that leaf" round; idle lanes are re-armed there from the bounce's queue with one
+// warp-aggregated atomic.  Two other schedules were built and measured slower in round 1 (voted single steps, pooled leaves:
+// profiles/r01_schedules.md #6, #13; the code is in the history).
 #ifndef WF_WIDE_MIN_BLOCKS
 #define WF_WIDE_MIN_BLOCKS 10   // 48 registers, no spills; measured +2 % (2 M triangles) to +6 % (20 M) over 8 (profiles/r01_schedules.md #28)
 #endif
 // WIDE: the inner-node phase walks the 4-wide quantised tree (gpt_wide.cu, node4_step) instead of the binary one.
-template <bool CULL, bool WIDE>      // back-face culling resolved at compile time: the flag is tested once per triangle otherwise
+// PRIMARY: bounce 0 -- path ids come straight from the fetch cursor and the ray is the camera ray of that id (no stored ray yet).
+template <bool CULL, bool WIDE, bool PRIMARY>      // back-face culling resolved at compile time: the flag is tested once per triangle otherwise
 __global__ void __launch_bounds__(WF_THREADS, WIDE ? WF_WIDE_MIN_BLOCKS : WF_MIN_BLOCKS)
 k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
                unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
-               int2* __restrict__ hit, const int refill_min, const int node_k)
+               int2* __restrict__ hit, const int refill_min, const int node_k, const PrimaryGen gen)
 {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
-    const unsigned n = *n_ptr;
+    const unsigned n = PRIMARY ? gen.n_paths : *n_ptr;
     const bool do_cull = CULL;
     int stack[WIDE ? GPT_W4_STACK : GPT_STACK_SIZE];
     TravState ts;
@@ -171,9 +107,15 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
             if (!active) {
                 const unsigned j = base + (unsigned)__popc(m_idle & lt_mask);
                 if (j < n) {
-                    pid = queue ? queue[j] : j;
-                    const float4 ro = ray_o[pid], rd = ray_d[pid];
-                    o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
+                    if (PRIMARY) {
+                        pid = j;
+                        PathState ps; primary_ray(gen, pid, ps);
+                        o = ps.o; d = ps.d;
+                    } else {
+                        pid = queue[j];
+                        const float4 ro = ray_o[pid], rd = ray_d[pid];
+                        o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
+                    }
                     trav_init(ts, stack, o, d, true);
                     active = true;
                 }
@@ -206,113 +148,13 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
     }
 }
 
-// Third schedule (A/B, GPT_WF_EXTEND=pool; measured 17% slower than k_wf_extend_ww, see profiles/r01_schedules.md):
-// while-while like k_wf_extend_ww for the inner nodes, but the LEAF phase is pooled over
-// the warp.  In the reference's loop (cudaUtils.h:400-446) every lane walks its own leaf, so a round costs
-// max-leaf-size iterations while most lanes idle (ncu on k_wf_extend_ww: 22 lanes enter the triangle loop, 12 reach
-// the division, 5 the last dot product).  Here the warp's pending (ray, triangle) pairs are laid end to end
-// (exclusive scan of the leaf sizes; a leaf's size is carried by its first triangle) and handed out 32 at a time:
-// lane j of pass k tests pair 32k+j with the owner's ray fetched by shuffle, lanes without a leaf -- or without a
-// ray -- work too, and a round costs ceil(sum of leaf sizes / 32) iterations.  The owner's result is the
-// lexicographic minimum of (t, position in leaf) over the pairs with 0 < t < hitT, taken with one 64-bit shared
-// atomicMin per candidate: exactly what the sequential strict `t < hitT` update yields (first visited wins ties).
-#ifndef WF_POOL_MIN_BLOCKS
-#define WF_POOL_MIN_BLOCKS 8
-#endif
-__global__ void __launch_bounds__(WF_THREADS, WF_POOL_MIN_BLOCKS)
-k_wf_extend_pool(const DevScene sc, const int cull, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
-                 unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
-                 int2* __restrict__ hit, const int refill_min)
-{
-    __shared__ unsigned long long s_best[WF_THREADS];
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const unsigned n = *n_ptr;
-    const bool do_cull = cull != 0;
-    unsigned long long* best = s_best + (threadIdx.x & ~31u);
-    int stack[GPT_STACK_SIZE];
-    TravState ts;
-    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
-    uint32_t pid = 0;
-    bool active = false, exhausted = false;
-    ts.node = GPT_SENTINEL; ts.leaf = 0; ts.sp = 0; ts.t = GPT_F32_MAX; ts.tri = -1; ts.tri_cur = 0;
-
-    while (true) {
-        const unsigned m_idle = __ballot_sync(GPT_FULL_MASK, !active);
-        if (m_idle != 0u && !exhausted && (__popc(m_idle) >= refill_min || m_idle == GPT_FULL_MASK)) {
-            unsigned base = 0;
-            const int leader = __ffs(m_idle) - 1;
-            if ((int)lane == leader) base = atomicAdd(fetch, (unsigned)__popc(m_idle));
-            base = __shfl_sync(GPT_FULL_MASK, base, leader);
-            if (base + (unsigned)__popc(m_idle) >= n) exhausted = true;
-            if (!active) {
-                const unsigned j = base + (unsigned)__popc(m_idle & lt_mask);
-                if (j < n) {
-                    pid = queue ? queue[j] : j;
-                    const float4 ro = ray_o[pid], rd = ray_d[pid];
-                    o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
-                    trav_init(ts, stack, o, d, true);
-                    active = true;
-                }
-            }
-        }
-        if (__ballot_sync(GPT_FULL_MASK, active) == 0u) break;      // nothing armed: queue exhausted
-        if (active) {
-            while (trav_wants_node(ts)) {
-                node_step(sc.nodes, ts, stack);
-                if (!__any_sync(__activemask(), ts.leaf >= 0)) break;
-            }
-        }
-        __syncwarp();
-        // ---- pooled leaf phase: every lane of the warp takes part ----
-        const bool has_leaf = active && trav_wants_tri(ts);
-        const int first = ts.tri_cur;
-        int cnt = 0;
-        if (has_leaf) cnt = __float_as_int(__ldg(sc.tris + 3 * first + 2).w) + 1;      // leaf size, carried by its first triangle
-        int incl = cnt;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(GPT_FULL_MASK, incl, off); if ((int)lane >= off) incl += v; }
-        const int total = __shfl_sync(GPT_FULL_MASK, incl, 31);
-        const int excl = incl - cnt;
-        best[lane] = ~0ull;
-        __syncwarp();
-        for (int base = 0; base < total; base += 32) {
-            const int q = base + (int)lane;
-            // owner = number of lanes whose inclusive sum is <= q (the sums are non-decreasing in the lane index)
-            int own = 0;
-#pragma unroll
-            for (int step = 16; step > 0; step >>= 1) { const int v = __shfl_sync(GPT_FULL_MASK, incl, own + step - 1); if (v <= q) own += step; }
-            own &= 31;
-            const float ox = __shfl_sync(GPT_FULL_MASK, o.x, own), oy = __shfl_sync(GPT_FULL_MASK, o.y, own), oz = __shfl_sync(GPT_FULL_MASK, o.z, own);
-            const float dx = __shfl_sync(GPT_FULL_MASK, d.x, own), dy = __shfl_sync(GPT_FULL_MASK, d.y, own), dz = __shfl_sync(GPT_FULL_MASK, d.z, own);
-            const float ht = __shfl_sync(GPT_FULL_MASK, ts.t, own);
-            const int f0 = __shfl_sync(GPT_FULL_MASK, first, own), e0 = __shfl_sync(GPT_FULL_MASK, excl, own);
-            if (q < total) {
-                const int pos = q - e0, ti = f0 + pos;
-                const float4 a = __ldg(sc.tris + 3 * ti), b = __ldg(sc.tris + 3 * ti + 1), c = __ldg(sc.tris + 3 * ti + 2);
-                const float t = tri_test(a, b, c, mk3(ox, oy, oz), mk3(dx, dy, dz), do_cull);
-                if (t > 0.0f && t < ht)
-                    atomicMin(best + own, ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(unsigned)pos);
-            }
-        }
-        __syncwarp();
-        if (has_leaf) {
-            const unsigned long long k = best[lane];
-            if (k != ~0ull) { ts.t = __uint_as_float((unsigned)(k >> 32)); ts.tri = first + (int)(unsigned)(k & 0xffffffffull); }
-            ts.leaf = ts.node;                                           // cudaUtils.h:440: another leaf reached meanwhile?
-            if (ts.node < 0) { ts.tri_cur = ~ts.node; ts.node = stack[ts.sp]; --ts.sp; }
-        }
-        if (active && trav_finished(ts)) {
-            hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
-            active = false;
-        }
-    }
-}
-
-// One thread per path alive at bounce `bounce`: the rest of the bounce-loop body (tracer.cu:98-296), the
-// per-pixel launch sum when the path ends (tracer.cu:305 / :141), and compaction of the survivors.
+// One thread per path alive at bounce `bounce`: the rest of the bounce-loop body (tracer.cu:98-296), the path's radiance when
+// it ends (tracer.cu:305 / :141, left in accu[pid]), and compaction of the survivors.
+// FIRST: bounce 0 -- every path of the wave is alive, the ray is the camera ray of the path id (recomputed, not loaded), the
+// mask is 1 (tracer.cu:68) and the accumulated colour starts at 0 (:69), so the slot is WRITTEN here, never read.
+template <bool FIRST>
 __global__ void __launch_bounds__(256, SHADE_MIN_BLOCKS)
-k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sample0, const uint32_t bounce, const uint32_t pix0, const uint32_t n_wave,
+k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce,
            const uint32_t* __restrict__ queue_in, unsigned int* __restrict__ counters,
            uint32_t* __restrict__ queue_out, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
            const int2* __restrict__ hit, float* __restrict__ mask_z, float4* __restrict__ accu,
@@ -321,13 +163,16 @@ k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sam
     __shared__ SmemPrims sm;
     const float* s_spheres; const float* s_boxes;
     stage_prims(sc, sm, s_spheres, s_boxes);
-    const unsigned n = counters[bounce];
+    const RenderParams& p = gen.p;
+    const unsigned n = FIRST ? gen.n_paths : counters[bounce];
     unsigned int* n_out = counters + bounce + 1;
     const unsigned lane = threadIdx.x & 31u;
     const bool has_mesh = sc.n_nodes > 0;
     const bool last_bounce = bounce + 1u >= p.depth;
+    const uint32_t n_wave = (uint32_t)gen.n_wave, pix0 = (uint32_t)gen.pix0;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         atomicAdd(&stats[0], (unsigned long long)n);
+        if (FIRST) atomicAdd(&stats[1], (unsigned long long)n);
         if ((p.flags & RP_COUNT_BOUNCES) && bounce < 16) atomicAdd(&stats[2 + bounce], (unsigned long long)n);
     }
     // whole warps iterate together so the compaction ballot below is warp-uniform
@@ -336,18 +181,24 @@ k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sam
         bool survive = false;
         uint32_t pid = 0;
         if (i < n) {
-            pid = queue_in ? queue_in[i] : i;
-            const float4 ro = ray_o[pid], rd = ray_d[pid];
             PathState ps;
-            ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
-            ps.mask = mk3(ro.w, rd.w, mask_z[pid]); ps.accu = mk3(0.0f, 0.0f, 0.0f);      // accu stays in memory (shade_bounce, accu_slot)
+            if (FIRST) {
+                pid = i;
+                primary_ray(gen, pid, ps);
+            } else {
+                pid = queue_in[i];
+                const float4 ro = ray_o[pid], rd = ray_d[pid];
+                ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
+                ps.mask = mk3(ro.w, rd.w, mask_z[pid]);
+            }
+            ps.accu = mk3(0.0f, 0.0f, 0.0f);      // accu stays in memory (shade_bounce, accu_slot)
             float tri_t = GPT_F32_MAX; int tri = -1;
             if (has_mesh) { const int2 h = hit[pid]; tri_t = __int_as_float(h.x); tri = h.y; }
             const SceneHit h = finish_scene_hit(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
             const uint32_t s_local = pid / n_wave;
-            // accu[pid] is touched inside only on a miss or an emitting hit; when the path is over its radiance (tracer.cu:305,
-            // or bkColor on a miss :141) stays there until k_wf_collect adds the wave's samples to the per-pixel launch sum
-            const bool cont = shade_bounce(sc, p, s_spheres, s_boxes, h, pix0 + (pid - s_local * n_wave), sample0 + s_local, bounce, ps, accu + pid);
+            // accu[pid] is touched inside only on a miss or an emitting hit (always written at bounce 0); when the path is over its
+            // radiance (tracer.cu:305, or bkColor on a miss :141) stays there until the wave's samples are summed per pixel
+            const bool cont = shade_bounce<FIRST>(sc, p, s_spheres, s_boxes, h, pix0 + (pid - s_local * n_wave), gen.sample0 + s_local, bounce, ps, accu + pid);
             survive = cont && !last_bounce;
             if (survive) {
                 ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x);
@@ -367,10 +218,12 @@ k_wf_shade(const DevScene sc, const RenderParams p, const unsigned long long sam
     }
 }
 
-// Adds the finished paths of a wave to the per-pixel launch sums, samples in increasing global index: the same
-// left-to-right float sum the megakernel keeps in a register, so both pipelines round identically.
+// Launches of SEVERAL waves: adds the finished paths of a wave to the per-pixel launch sums, samples in increasing global
+// index: the same left-to-right float sum the megakernel keeps in a register, so both pipelines round identically.
+// The last block to pass also re-zeroes the wave's queue counters for the next wave.
 __global__ void __launch_bounds__(256)
-k_wf_collect(const float4* __restrict__ accu, const int n_samples, const int pix0, const int n_wave, float4* __restrict__ lsum)
+k_wf_collect(const float4* __restrict__ accu, const int n_samples, const int pix0, const int n_wave, float4* __restrict__ lsum,
+             unsigned int* __restrict__ counters, const int n_counters)
 {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_wave; i += gridDim.x * blockDim.x) {
         float4 s = lsum[pix0 + i];
@@ -380,17 +233,31 @@ k_wf_collect(const float4* __restrict__ accu, const int n_samples, const int pix
         }
         lsum[pix0 + i] = s;
     }
+    if (blockIdx.x == 0) for (int k = threadIdx.x; k < n_counters; k += blockDim.x) counters[k] = 0u;     // every shade kernel of the wave has finished
 }
 
-// depth == 0: every path returns accucolor = 0 (tracer.cu:72,305); nothing to add to lsum.
-// launch sums -> caller's buffer.  LEGACY: running mean + clamp + pack (tracer.cu:386-398).
-template <bool LEGACY>
+// Per-pixel sums of the launch -> caller's buffer.  LEGACY: running mean + clamp + pack (tracer.cu:386-398).
+// DIRECT (the launch was ONE wave covering the frame, the usual case): the pixel's samples are summed here, in increasing
+// global index, straight from the wave's accu[] -- no launch-sum buffer, no collect pass (tracer.cu:374).  Otherwise src = the
+// launch sums k_wf_collect kept.  depth == 0: every path returns accucolor = 0 (tracer.cu:72,305): the launcher takes the
+// launch-sum form with a zeroed buffer.
+template <bool LEGACY, bool DIRECT>
 __global__ void __launch_bounds__(256)
-k_wf_accumulate(const float4* __restrict__ lsum, const int n_pix, const uint32_t sample_count, float4* __restrict__ accum_f4,
-                float* __restrict__ accum_v3, uint32_t* __restrict__ draw, const unsigned long long constant_pdf)
+k_wf_accumulate(const float4* __restrict__ src, const int n_pix, const uint32_t sample_count, float4* __restrict__ accum_f4,
+                float* __restrict__ accum_v3, uint32_t* __restrict__ draw, const unsigned long long constant_pdf,
+                unsigned int* __restrict__ counters, const int n_counters)
 {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pix; i += gridDim.x * blockDim.x) {
-        const float4 s = lsum[i];
+        float4 s;
+        if (DIRECT) {
+            s = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                // starts at +0 like the zeroed launch-sum buffer: same roundings
+            for (uint32_t k = 0; k < sample_count; ++k) {
+                const float4 a = src[(size_t)k * n_pix + i];
+                s.x += a.x; s.y += a.y; s.z += a.z;
+            }
+        } else {
+            s = src[i];
+        }
         if (LEGACY) {
             const float nm1 = (float)(constant_pdf - 1ull), inv = 1.0f / (float)constant_pdf;
             float* a = accum_v3 + 3 * (size_t)i;
@@ -408,6 +275,7 @@ k_wf_accumulate(const float4* __restrict__ lsum, const int n_pix, const uint32_t
             accum_f4[i] = a;
         }
     }
+    if (DIRECT && blockIdx.x == 0) for (int k = threadIdx.x; k < n_counters; k += blockDim.x) counters[k] = 0u;
 }
 
 // ---------------------------------------------------------------- launcher
@@ -476,116 +344,120 @@ size_t gptk_wave_sort_tmp_bytes(size_t capacity)
     return bytes;
 }
 
-cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb,
+// launch configuration of one context (grids follow from the device's SM count and the kernels' occupancy; the knobs are read
+// from the environment once per context)
+void gptk_wave_launch_cfg(WaveLaunchCfg* cfg, int sm_count)
+{
+    auto per_sm = [](const void* k, int threads, int dflt) { int v = 0; return (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k, threads, 0) == cudaSuccess && v >= 1) ? v : dflt; };
+    cfg->sm_count = sm_count;
+    cfg->ext_grid = sm_count * per_sm((const void*)k_wf_extend_ww<true, false, false>, WF_THREADS, 1);
+    cfg->wide_grid = sm_count * per_sm((const void*)k_wf_extend_ww<true, true, false>, WF_THREADS, 1);
+    // shade grid: whole waves of resident CTAs (occupancy of the kernel as built x GPT_SHADE_WAVES), so no partial last wave
+    const char* e = getenv("GPT_SHADE_WAVES");
+    const int waves = e ? atoi(e) : 16;      // measured 1 / 2 / 4 / 8 / 16 / 32 / 64 / one trip per thread: 11.46 / 11.27 / 11.0 / 10.82 / 10.75 / 10.87 / 11.09 / 11.92 ms
+    cfg->shade_grid = waves <= 0 ? 0x7fffffff : sm_count * per_sm((const void*)k_wf_shade<false>, 256, 4) * (waves > 4096 ? 4096 : waves);
+    const int m = wf_knob("GPT_WF_SORT", 3);
+    cfg->sort_mode = m > 9 ? 9 : m;
+    cfg->refill_min = wf_knob("GPT_WF_REFILL_MIN", 8);
+    cfg->node_k_env = getenv("GPT_WF_NODE_K") ? wf_knob("GPT_WF_NODE_K", WF_NODE_K) : 0;
+    const char* w = getenv("GPT_WF_WAVE_PATHS");
+    const long long v = w ? atoll(w) : 0;
+    cfg->wave_cap_env = (size_t)(v < 0 ? 0 : v);
+    cfg->ready = 1;
+}
+
+template <bool PRIMARY>
+static void launch_extend(const DevScene& sc, const RenderParams& p, const WaveLaunchCfg& cfg, const uint32_t* q, unsigned int* n_ptr, unsigned int* fetch,
+                          const WaveBuffers& wb, int node_k, const PrimaryGen& gen, cudaStream_t st)
+{
+    if (sc.wnodes) {
+        if (p.cull) k_wf_extend_ww<true, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
+        else k_wf_extend_ww<false, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
+    } else {
+        if (p.cull) k_wf_extend_ww<true, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
+        else k_wf_extend_ww<false, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
+    }
+}
+
+// wb.counters must be all zero on entry; they are all zero again when the enqueued work has run (the last kernel of every wave
+// re-zeroes them), so a call costs 2 x depth + 1 launches when one wave covers the frame.
+cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb, const WaveLaunchCfg& cfg,
                                   float4* accum_f4, float* accum_v3, uint32_t* draw, unsigned long long constant_pdf,
                                   unsigned long long sample_begin, uint32_t sample_count,
-                                  unsigned long long* stats, int sm_count, cudaStream_t st, unsigned long long* launches,
+                                  unsigned long long* stats, cudaStream_t st, unsigned long long* launches,
                                   KernelTimer* kt)
 {
-    // extend schedule: while-while (default); GPT_WF_EXTEND=pool the pooled-leaf variant, =voted the voted steps (both
-    // bit-identical, both measured slower: profiles/r01_schedules.md)
-    static const int ext_kind = []{ const char* e = getenv("GPT_WF_EXTEND"); if (!e) e = getenv("GPT_WF_VOTED") ? "voted" : "ww";
-                                    return !strcmp(e, "pool") ? 0 : (!strcmp(e, "voted") ? 2 : 1); }();
-    static int ext_grid = 0;
-    if (!ext_grid) {
-        int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ext_kind == 0 ? (const void*)k_wf_extend_pool : ext_kind == 1 ? (const void*)k_wf_extend_ww<true, false> : (const void*)k_wf_extend, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
-        ext_grid = sm_count * per_sm;
-    }
-    // shade grid: whole waves of resident CTAs (occupancy of the kernel as built x GPT_SHADE_WAVES), so no partial last wave
-    static int shade_grid = 0;
-    if (shade_grid == 0) {
-        int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_shade, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
-        const char* e = getenv("GPT_SHADE_WAVES");
-        const int waves = e ? atoi(e) : 16;      // measured 1 / 2 / 4 / 8 / 16 / 32 / 64 / one trip per thread: 11.46 / 11.27 / 11.0 / 10.82 / 10.75 / 10.87 / 11.09 / 11.92 ms
-        shade_grid = waves <= 0 ? 0x7fffffff : sm_count * per_sm * (waves > 4096 ? 4096 : waves);
-    }
-    static int wide_grid = 0;
-    if (!wide_grid) {
-        int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k_wf_extend_ww<true, true>, WF_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
-        wide_grid = sm_count * per_sm;
-    }
-    static const int sort_mode = []{ const int m = wf_knob("GPT_WF_SORT", 3); return m > 9 ? 9 : m; }();
-    static const int refill_min = wf_knob("GPT_WF_REFILL_MIN", 8), tri_min = wf_knob("GPT_WF_TRI_MIN", 12);
+    const int sm_count = cfg.sm_count;
     // node-loop exit policy of k_wf_extend_ww (see there).  Small scenes spend half their steps in leaves and want full leaf
     // phases (k = 3); larger scenes make 15-40 node visits per 1-2 triangle tests, so lanes that hold a leaf should not wait
     // for the rest of the warp to find one.  Measured extend time, k = 3 / 6 / 10 / 16 (profiles/r01_schedules.md #39): bench scene
     // (5 k triangles) 16.5 / - / 17.2 (k = 8) / 19.7; dragon 100 k 16.3 / 15.6 / 15.2 / 15.4; 16 cars 157 k 41.1 / 38.3 / 37.7 / 39.4;
     // dragon 1.6 M 23.3 / 21.3 / 20.7 / 20.9; synthetic 2 M 20.8 / 19.2 / 18.4 / 18.1; 20 M 37.6 / 35.2 / 33.9 / 33.2
-    static const int node_k_env = getenv("GPT_WF_NODE_K") ? wf_knob("GPT_WF_NODE_K", WF_NODE_K) : 0;
-    const int node_k = node_k_env ? node_k_env : (sc.n_tris < (64 << 10) ? WF_NODE_K : (sc.n_tris < (2 << 20) ? 8 : 16));      // 8: between the reference-built dragon's best (6) and the device-built trees' (10)
+    const int node_k = cfg.node_k_env ? cfg.node_k_env : (sc.n_tris < (64 << 10) ? WF_NODE_K : (sc.n_tris < (2 << 20) ? 8 : 16));      // 8: between the reference-built dragon's best (6) and the device-built trees' (10)
     const int n_pix = p.width * p.height;
+    const int n_counters = (int)gptk_wave_counter_count(p.depth);
     // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays
-    // hold (88 B/path).  Big waves matter: every launch has a fixed cost (launch gap + the tail where the
+    // hold (68 B/path).  Big waves matter: every launch has a fixed cost (launch gap + the tail where the
     // persistent extend kernel drains), measured at ~19 us, and a 1080p x 1 spp wave needs 17 launches.
-    static const size_t wave_cap_env = []{ const char* e = getenv("GPT_WF_WAVE_PATHS"); long long v = e ? atoll(e) : 0; return (size_t)(v < 0 ? 0 : v); }();
     size_t cap = wb.capacity;
-    if (wave_cap_env && wave_cap_env < cap) cap = wave_cap_env < 1024 ? 1024 : wave_cap_env;
+    if (cfg.wave_cap_env && cfg.wave_cap_env < cap) cap = cfg.wave_cap_env < 1024 ? 1024 : cfg.wave_cap_env;
     const int wave_pix = (int)((size_t)n_pix < cap ? (size_t)n_pix : cap);
     const uint32_t wave_spp_max = (uint32_t)(cap / (size_t)wave_pix);      // >= 1
     int agrid = (n_pix + 255) / 256; if (agrid > sm_count * 8) agrid = sm_count * 8; if (agrid < 1) agrid = 1;
     const bool legacy = accum_v3 != nullptr;
     const bool has_mesh = sc.n_nodes > 0;
+    // one wave covers the launch: its samples are summed straight from accu[] by the accumulate kernel
+    const bool direct = p.depth > 0 && wave_pix == n_pix && sample_count <= wave_spp_max;
     cudaError_t e;
-    if ((e = cudaMemsetAsync(wb.lsum, 0, sizeof(float4) * (size_t)n_pix, st)) != cudaSuccess) return e;
+    if (!direct && (e = cudaMemsetAsync(wb.lsum, 0, sizeof(float4) * (size_t)n_pix, st)) != cudaSuccess) return e;
     for (int pix0 = 0; pix0 < n_pix && p.depth > 0; pix0 += wave_pix) {
         const int n_wave = n_pix - pix0 < wave_pix ? n_pix - pix0 : wave_pix;
         for (uint32_t s0 = 0; s0 < sample_count; s0 += wave_spp_max) {
             const uint32_t ns = sample_count - s0 < wave_spp_max ? sample_count - s0 : wave_spp_max;
             const size_t n_paths = (size_t)ns * n_wave;
             int grid = (int)((n_paths + 255) / 256); if (grid > sm_count * 8) grid = sm_count * 8; if (grid < 1) grid = 1;
-            int sgrid = (int)((n_paths + 255) / 256); if (sgrid > shade_grid) sgrid = shade_grid; if (sgrid < 1) sgrid = 1;
+            int sgrid = (int)((n_paths + 255) / 256); if (sgrid > cfg.shade_grid) sgrid = cfg.shade_grid; if (sgrid < 1) sgrid = 1;
             int cgrid = (n_wave + 255) / 256; if (cgrid > sm_count * 8) cgrid = sm_count * 8; if (cgrid < 1) cgrid = 1;
-            const unsigned long long sample0 = sample_begin + s0;
-            if ((e = cudaMemsetAsync(wb.counters, 0, sizeof(unsigned int) * gptk_wave_counter_count(p.depth), st)) != cudaSuccess) return e;
-            if (kt) kt->tick(KT_GENERATE, st);
-            k_wf_generate<<<grid, 256, 0, st>>>(p, sample0, (int)ns, pix0, n_wave, wb.ray_o, wb.ray_d, wb.mask_z, wb.accu, wb.counters, stats);
-            *launches += 1;
+            PrimaryGen gen; gen.p = p; gen.sample0 = sample_begin + s0; gen.pix0 = pix0; gen.n_wave = n_wave; gen.n_paths = (unsigned)n_paths;
             for (uint32_t b = 0; b < p.depth; ++b) {
                 const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
                 const uint32_t* q_ext = q_in;       // order in which the extend kernel fetches the rays
                 if (has_mesh && b > 0 && wb.sort_vals) {
                     if (kt) kt->tick(KT_OTHER, st);
-                    k_wf_sort_keys<<<grid, 256, 0, st>>>(sc, q_in, wb.counters + b, (unsigned)n_paths, wb.ray_o, wb.ray_d, wb.sort_keys[0], sort_mode);
+                    k_wf_sort_keys<<<grid, 256, 0, st>>>(sc, q_in, wb.counters + b, (unsigned)n_paths, wb.ray_o, wb.ray_d, wb.sort_keys[0], cfg.sort_mode);
                     size_t tb = wb.sort_tmp_bytes;
                     if ((e = cub::DeviceRadixSort::SortPairs(wb.sort_tmp, tb, (const uint32_t*)wb.sort_keys[0], wb.sort_keys[1], q_in, wb.sort_vals,
-                                                             (long long)n_paths, 0, wf_sort_bits(sort_mode), st)) != cudaSuccess) return e;
+                                                             (long long)n_paths, 0, wf_sort_bits(cfg.sort_mode), st)) != cudaSuccess) return e;
                     *launches += 4;
                     q_ext = wb.sort_vals;
                 }
                 if (has_mesh) {
                     if (kt) kt->tick(KT_EXTEND, st);
-                    if (ext_kind == 0 && !sc.wnodes)
-                        k_wf_extend_pool<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b,
-                                                                          wb.ray_o, wb.ray_d, wb.hit, refill_min);
-                    else if (sc.wnodes) {
-                        if (p.cull) k_wf_extend_ww<true, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min, node_k);
-                        else k_wf_extend_ww<false, true><<<wide_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min, node_k);
-                    } else if (ext_kind == 1) {
-                        if (p.cull) k_wf_extend_ww<true, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min, node_k);
-                        else k_wf_extend_ww<false, false><<<ext_grid, WF_THREADS, 0, st>>>(sc, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb.ray_o, wb.ray_d, wb.hit, refill_min, node_k);
-                    } else
-                        k_wf_extend<<<ext_grid, WF_THREADS, 0, st>>>(sc, p.cull, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b,
-                                                                     wb.ray_o, wb.ray_d, wb.hit, refill_min, tri_min);
+                    if (b == 0) launch_extend<true>(sc, p, cfg, nullptr, wb.counters, wb.counters + p.depth + 1, wb, node_k, gen, st);
+                    else launch_extend<false>(sc, p, cfg, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb, node_k, gen, st);
                     *launches += 1;
                 }
                 if (kt) kt->tick(KT_SHADE, st);
-                k_wf_shade<<<sgrid, 256, 0, st>>>(sc, p, sample0, b, (uint32_t)pix0, (uint32_t)n_wave, q_in, wb.counters, wb.queue[(b + 1u) & 1u],
-                                                 wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
+                if (b == 0) k_wf_shade<true><<<sgrid, 256, 0, st>>>(sc, gen, b, nullptr, wb.counters, wb.queue[1], wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
+                else k_wf_shade<false><<<sgrid, 256, 0, st>>>(sc, gen, b, q_in, wb.counters, wb.queue[(b + 1u) & 1u], wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
                 *launches += 1;
             }
-            if (kt) kt->tick(KT_COLLECT, st);
-            k_wf_collect<<<cgrid, 256, 0, st>>>(wb.accu, (int)ns, pix0, n_wave, wb.lsum);
-            *launches += 1;
+            if (!direct) {
+                if (kt) kt->tick(KT_COLLECT, st);
+                k_wf_collect<<<cgrid, 256, 0, st>>>(wb.accu, (int)ns, pix0, n_wave, wb.lsum, wb.counters, n_counters);
+                *launches += 1;
+            }
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
     }
-    const int grid = agrid;
     if (kt) kt->tick(KT_ACCUMULATE, st);
-    if (legacy) k_wf_accumulate<true><<<grid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, nullptr, accum_v3, draw, constant_pdf);
-    else k_wf_accumulate<false><<<grid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, accum_f4, nullptr, nullptr, 1ull);
+    if (direct) {
+        if (legacy) k_wf_accumulate<true, true><<<agrid, 256, 0, st>>>(wb.accu, n_pix, sample_count, nullptr, accum_v3, draw, constant_pdf, wb.counters, n_counters);
+        else k_wf_accumulate<false, true><<<agrid, 256, 0, st>>>(wb.accu, n_pix, sample_count, accum_f4, nullptr, nullptr, 1ull, wb.counters, n_counters);
+    } else {
+        if (legacy) k_wf_accumulate<true, false><<<agrid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, nullptr, accum_v3, draw, constant_pdf, wb.counters, n_counters);
+        else k_wf_accumulate<false, false><<<agrid, 256, 0, st>>>(wb.lsum, n_pix, sample_count, accum_f4, nullptr, nullptr, 1ull, wb.counters, n_counters);
+    }
     *launches += 1;
     if (kt) kt->tick(KT_END, st);
     return cudaGetLastError();

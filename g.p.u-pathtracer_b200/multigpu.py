@@ -75,17 +75,30 @@ class PeerFrames:
 
     def frame(self, render_fn, frame_begin, frame_spp, total_accum=None, out_rgba8=None, out_rgb_f32=None, stream=None):
         """render_fn(accum_ptr, sample_begin, sample_count) must ADD the slice into the float4 buffer at accum_ptr on
-        `stream`.  Returns this rank's (offset, count)."""
+        `stream`.  Returns this rank's (offset, count).
+
+        `stream`: a torch.cuda.Stream (or None = torch's current stream).  Clear, render, barrier and reduce must all be ordered
+        on ONE stream: the barrier is a torch.distributed collective, which torch issues on ITS current stream, so the whole
+        body runs under torch.cuda.stream(stream).  A raw cudaStream_t handle is accepted only if it is torch's current stream."""
+        import torch
+        if stream is None or isinstance(stream, int):
+            cur = torch.cuda.current_stream()
+            if isinstance(stream, int) and stream != cur.cuda_stream:
+                raise ValueError("PeerFrames.frame: pass a torch.cuda.Stream (a raw handle must be torch's current stream): the barrier "
+                                 "collective runs on torch's current stream and would not order the peers' renders before the reduce")
+            stream = cur
         buf = self.frame_index & 1
         self.frame_index += 1
         off, cnt = sample_slice(frame_spp, self.world, self.rank)
-        self.ctx.frame_clear(buf, stream)
-        if cnt:
-            render_fn(self.ctx.frame_ptr(buf), frame_begin + off, cnt)
-        if self.world > 1:
-            self.dist.all_reduce(self._flag)               # stream-ordered barrier: every rank's render precedes it
-        if self.rank == self.root:
-            self.ctx.reduce_resolve(buf, total_accum, out_rgba8, out_rgb_f32, stream)
+        with torch.cuda.stream(stream):
+            raw = stream.cuda_stream
+            self.ctx.frame_clear(buf, raw)
+            if cnt:
+                render_fn(self.ctx.frame_ptr(buf), frame_begin + off, cnt)
+            if self.world > 1:
+                self.dist.all_reduce(self._flag)               # stream-ordered barrier: every rank's render precedes it
+            if self.rank == self.root:
+                self.ctx.reduce_resolve(buf, total_accum, out_rgba8, out_rgb_f32, raw)
         return off, cnt
 
     def close(self):

@@ -10,8 +10,20 @@
  *
  * Plain C: pointers and sizes only, no C++/torch types.  Every entry returns a gpt_status
  * (0 = ok, negative = error) and never calls exit() (the reference's checkCudaErrors does,
- * utilfun.hpp:81-90).  One frame in flight per context, like the reference (BasicScene.cpp:395).
+ * utilfun.hpp:81-90).
  * There is NO CPU fallback: without a CUDA device every compute entry returns GPT_ERR_CUDA.
+ *
+ * Streams and threads.  A context owns ONE set of scratch buffers (path state, ray queues and their counters, work
+ * cursor, launch sums): ONE stream and ONE host thread may have work of a context in flight at a time, like the
+ * reference's single frame in flight (BasicScene.cpp:395).  Use one context per stream / thread for concurrency;
+ * the library is re-entrant across contexts.  gpt_launch / gpt_render / gpt_resolve / gpt_reduce_resolve only enqueue work
+ * on `stream` EXCEPT that a call may block the host (cudaDeviceSynchronize / cudaStreamSynchronize) when it
+ *   - has to grow the scratch buffers (first call, a larger frame, more samples per call, a deeper path),
+ *   - finds new BVH pointers in kernelInfo and re-packs them (gpt_launch), or builds the 4-wide tree (first render of a scene),
+ *   - is one of the timed calls of the per-scene trial (gpt_trial_info; the first <= 9 render calls of >= 1 Mi paths after a
+ *     scene upload on scenes of >= 64 Ki triangles; GPT_FLAG_NO_TRIAL switches the trial off).
+ * gpt_upload_scene, gpt_build_bvh, gpt_set_triangle_materials, gpt_get_stats, gpt_get_kernel_times, gpt_reset_stats,
+ * gpt_render_frame_host and the gpt_frame_* setup calls always synchronise.
  */
 #ifndef GPT_H
 #define GPT_H
@@ -111,7 +123,10 @@ enum {
     GPT_FLAG_WIDE_BVH   = 1u << 5,   /* always the 4-wide tree */
     GPT_FLAG_BINARY_BVH = 1u << 6,   /* always the binary tree */
     GPT_FLAG_WAVEFRONT  = 1u << 7,   /* always the wavefront pipeline, also for small calls */
-    GPT_FLAG_BUILD_LBVH = 1u << 8    /* gpt_build_bvh: plain Morton radix tree instead of the (default) PLOC clustering */
+    GPT_FLAG_BUILD_LBVH = 1u << 8,   /* gpt_build_bvh: plain Morton radix tree instead of the (default) PLOC clustering */
+    GPT_FLAG_NO_TRIAL   = 1u << 9    /* never run the timed per-scene trial (gpt_trial_info): no render call then synchronises, so
+                                      * calls are strictly asynchronous and can be captured into a CUDA graph; the size defaults
+                                      * decide tree and ray order (also: GPT_NO_TRIAL=1 in the environment) */
 };
 
 typedef struct {
@@ -185,9 +200,17 @@ GPT_API int gpt_copy_to_host(gpt_ctx* ctx, void* dst_host, const void* src_devic
 /* ---- render launch ---- */
 /* Drop-in for launchKernel (tracer.cu:405-415): ONE progressive pass (1 spp) with the reference's
  * exact field meanings: vec3 running mean with per-frame clamp into info->accumBuffer, RGBA8 pack into
- * info->dev_drawRes (tracer.cu:386-398), seed = info->hash.  If the BVH/sphere device pointers in
- * `info` differ from the uploaded scene they are (re-)packed first. Asynchronous on `stream`. */
+ * info->dev_drawRes (tracer.cu:386-398), seed = info->hash.  If the BVH device pointers in `info` differ from
+ * the ones packed last (address or element count of any of the three arrays) they are (re-)packed first; spheres are read
+ * live from info->sphereTex on every launch, like the reference does (tracer.cu:39).
+ * POINTER-IDENTITY RULE: the reference kernel reads dev_triNode / dev_triPtr / dev_triIndicesPtr live on every launch; this
+ * library traverses a re-packed copy and cannot see writes INTO those arrays.  A caller that rewrites them in place (refit,
+ * animation), or frees and re-allocates them and may get the same addresses back, must call gpt_invalidate_scene() before the
+ * next gpt_launch; the INTEGRATION.md adapter does so wherever the reference re-uploads.  Asynchronous on `stream` (see the
+ * header comment for the calls that may block). */
 GPT_API int gpt_launch(gpt_ctx* ctx, const gpt_kernel_info* info, gpt_stream stream);
+/* forget which kernelInfo BVH arrays the packed tree was made from: the next gpt_launch carrying BVH pointers re-packs them */
+GPT_API int gpt_invalidate_scene(gpt_ctx* ctx);
 
 /* Native contract: adds `sample_count` samples with GLOBAL indices [sample_begin, sample_begin+count)
  * to accum_f4 (device, W*H float4 = sum r,g,b + sample count; never clamped).  RNG is keyed by

@@ -32,7 +32,7 @@ def emit(d):
 def time_ours(ctx, info, spp, reps=3):
     W, H = info.width, info.height
     acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
-    for w in range(7):                         # warm-up: allocates the wave buffers and lets the per-scene trial (<= 6 calls) end
+    for w in range(10):                        # warm-up: allocates the wave buffers and lets the per-scene trial (<= 9 calls) end
         ctx.render(info, acc, 0, 10_000_000 + w * spp, spp)
     torch.cuda.synchronize()
     ctx.reset_stats()

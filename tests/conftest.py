@@ -6,9 +6,11 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
-# The library re-orders secondary rays before each extend from GPT_SORT_MIN_TRIS packed triangles up (default 2 Mi; read once,
-# at the first render).  Lowered here so that the 1.2 M-triangle scene of test_gpu_wide.py goes through the sorted pipeline
-# while the 1.0 M-triangle scene of test_gpu_build.py stays on the unsorted one.
+# GPT_SORT_MIN_TRIS = a size threshold for re-ordering the secondary rays before each extend; it REPLACES the library's default
+# policy (a timed trial on scenes of >= 256 Ki packed triangles, gpt_trial_info) and is read once, when the library is loaded.
+# Set here so that the 1.2 M-triangle scene of test_gpu_wide.py goes through the sorted pipeline while the 1.0 M-triangle scene of
+# test_gpu_build.py stays on the unsorted one.  The default policy itself -- all nine trial calls, ray order included -- runs in
+# the subprocesses of test_gpu_wide.py::test_traversal_trial_* and test_gpu_configs.py, which drop every GPT_* variable.
 os.environ.setdefault("GPT_SORT_MIN_TRIS", "1100000")
 # Calls of fewer than GPT_SMALL_FRAME_PATHS paths (default 393216) go to the megakernel.  The parity tests render small frames and
 # mean to exercise the pipeline their flags name, so the switch is off here; tests/test_gpu_parity.py::test_small_calls_* covers it.

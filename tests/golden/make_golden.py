@@ -3,13 +3,14 @@
 
 Needs /root/reference (assets) and oracle/_ref/librefbvh.so (the reference's SplitBVHBuilder +
 CudaBVH compiled in place by oracle/Makefile).  Small scenes are committed under tests/golden/;
-large ones go to tests/golden/_big/ (git-ignored; they still travel to the GPU box).
+the two larger ones (BASELINE configs 2 and 3) are committed too, without the unused Woop array, so that the
+-m gpu parity tests and bench.py's per-config records find them on any box.
 
   cornell        Assets/cornell.obj                                   (BASELINE config 0)
   bunny_cornell  Assets/cornell.obj + Assets/bunny_low.obj translated (0,-15.2,-40)  (config 1)
   sphere_mesh    Assets/sphere.obj (64 faces, 48 quads fan-triangulated) tiny case
-  dragon_cornell Assets/cornell.obj + Assets/dragon.obj (100 000 tris)               (config 2 fallback, _big)
-  gto_sixteen    Assets/gto_sixteen.obj                                              (config 3 base mesh, _big)
+  dragon_cornell Assets/cornell.obj + Assets/dragon.obj (100 000 tris)               (config 2 stand-in; cornell_dragon.obj is a missing blob)
+  gto_sixteen    Assets/gto_sixteen.obj                                              (config 3 base mesh, instanced 4x4 by the tests)
 """
 import os
 import sys
@@ -28,10 +29,11 @@ def build(name, meshes, big=False):
     v, f = objio.merge(meshes)
     t0 = time.time()
     b = reflib.ref_build_bvh(v, f)
-    out_dir = os.path.join(HERE, "_big") if big else HERE
-    os.makedirs(out_dir, exist_ok=True)
-    path = os.path.join(out_dir, "scene_%s.npz" % name)
-    np.savez_compressed(path, verts=v, faces=f, nodes=b["nodes"], tris=b["tris"], woop=b["woop"], indices=b["indices"])
+    path = os.path.join(HERE, "scene_%s.npz" % name)
+    arrays = dict(verts=v, faces=f, nodes=b["nodes"], tris=b["tris"], indices=b["indices"])
+    if not big:
+        arrays["woop"] = b["woop"]          # CudaBVH.cpp:244-262; nothing reads it, kept for the small fixtures only
+    np.savez_compressed(path, **arrays)
     print("%-16s %7d tris  %6d inner nodes  %7d tri slots  build %.2fs  -> %s (%.0f KB)" % (
         name, len(f), b["nodes"].shape[0] // 4, b["tris"].shape[0], time.time() - t0, os.path.relpath(path), os.path.getsize(path) / 1024))
 

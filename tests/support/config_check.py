@@ -1,0 +1,220 @@
+#!/usr/bin/env python
+"""Parity of the CUDA path against the CPU oracle on the scenes of BASELINE.json configs 2, 3 and 4, under the traversal plan the
+library picks by itself (no GPT_* variables in the environment: run as a subprocess by tests/test_gpu_configs.py, or by hand).
+
+  python tests/support/config_check.py <scene> [--rays N] [--pixels N] [--spp N]
+
+Scenes (the same stand-ins profiles/tools/configs_bench.py and bench.py time):
+  cfg2_dragon100k_sbvh  Assets/dragon.obj + cornell.obj on the REFERENCE's SBVH arrays (tests/golden/scene_dragon_cornell.npz), 1080p
+  cfg2_dragon1p6M       the same mesh subdivided 1 -> 16 (1.6 M triangles, for the missing 870 k cornell_dragon.obj), device-built tree, 1080p
+  cfg3_gto16            Assets/gto_sixteen.obj instanced 4 x 4 (157 k triangles), device-built tree, METAL, 3840x2160
+  cfg4_20M              seeded synthetic scene, 20 M triangles, device-built tree, 3840x2160
+  synthetic_<n>         the same generator with n triangles (sizes the CPU suite can afford)
+
+Checks, each against the oracle executing the reference algorithm (cudaUtils.h:256-460, tracer.cu:27-339) on the SAME arrays
+(the fixture's, or the device builder's copied back to the host):
+  rays     nearest hit of N incoherent rays: t, remapped face index and -- on the binary tree -- triangle slot, bit for bit
+  primary  the 1080p primary-hit map (jitter off): geometry type, face index, t, bit for bit
+  pixels   N random pixels of the config's full-size frame x spp samples x depth 8 re-derived sample by sample with orc_sample:
+           the float sums must be bit-identical; rendered repeatedly until the per-scene trial has ended, every call's frame equal
+Prints one JSON object; exit code 0 iff every check passed."""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.dirname(HERE))
+
+
+def make_scene(name, gpt, procedural, scenes):
+    """-> (verts, faces, reference-built arrays or None, width, height, triangle material)"""
+    if name == "cfg2_dragon100k_sbvh":
+        sc = scenes.load_scene("dragon_cornell")
+        return sc["verts"], sc["faces"], sc, 1920, 1080, gpt.DIFF
+    if name == "cfg2_dragon1p6M":
+        sc = scenes.load_scene("dragon_cornell")
+        v, f = procedural.subdivide(sc["verts"], sc["faces"], 2)
+        return v, f, None, 1920, 1080, gpt.DIFF
+    if name == "cfg3_gto16":
+        sc = scenes.load_scene("gto_sixteen")
+        v, f = procedural.instance_grid(sc["verts"], sc["faces"], 4, 4, 0.4, 9.5, -35.0, 15.0)
+        return v, f, None, 3840, 2160, gpt.METAL
+    if name == "cfg4_20M":
+        v, f = procedural.synthetic_scene(20_000_000, seed=1234)
+        return v, f, None, 3840, 2160, gpt.DIFF
+    if name.startswith("synthetic_"):
+        v, f = procedural.synthetic_scene(int(name.split("_", 1)[1]), seed=1234)
+        return v, f, None, 1920, 1080, gpt.DIFF
+    raise SystemExit("unknown scene %r" % name)
+
+
+def incoherent_rays(verts, n, seed):
+    """half aimed through the mesh's bounding box from outside, half secondary-like: origins ON the box's interior, random directions"""
+    rng = np.random.default_rng(seed)
+    lo, hi = verts.min(0).astype(np.float64), verts.max(0).astype(np.float64)
+    c, ext = (lo + hi) / 2, (hi - lo)
+    h = n // 2
+    o1 = c + (rng.random((h, 3)) - 0.5) * ext * 3.0
+    tgt = c + (rng.random((h, 3)) - 0.5) * ext * 1.2
+    d1 = tgt - o1
+    o2 = lo + rng.random((n - h, 3)) * ext
+    d2 = rng.normal(size=(n - h, 3))
+    o, d = np.concatenate([o1, o2]), np.concatenate([d1, d2])
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:32] = [0.0, 0.0, -1.0]          # axis-parallel: the 2^-80 guard of cudaUtils.h:283-286
+    d[32:64] = [1.0, 0.0, 0.0]
+    return np.ascontiguousarray(o, np.float32), np.ascontiguousarray(d, np.float32)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("scene")
+    ap.add_argument("--rays", type=int, default=20000)
+    ap.add_argument("--pixels", type=int, default=256)
+    ap.add_argument("--spp", type=int, default=16)
+    ap.add_argument("--depth", type=int, default=8)
+    ap.add_argument("--flags", type=int, default=0)
+    args = ap.parse_args()
+    import torch
+    import gpt_b200 as gpt
+    from support import procedural, reflib, scenes
+    if not torch.cuda.is_available():
+        raise SystemExit("config_check.py needs a GPU: the product has no CPU path")
+    out = {"scene": args.scene, "env": {k: v for k, v in os.environ.items() if k.startswith("GPT_")}, "ok": False}
+    t0 = time.time()
+    verts, faces, ref_arrays, W, H, mat = make_scene(args.scene, gpt, procedural, scenes)
+    out["triangles"], out["gen_s"] = int(len(faces)), time.time() - t0
+    sph = gpt.default_spheres()
+    ctx = gpt.Context(0, args.flags)
+    built = None
+    if ref_arrays is not None:
+        host = ref_arrays
+        ctx.upload_scene(host["nodes"], host["tris"], host["indices"], sph)
+        out["tree"] = "reference SBVH (SplitBVHBuilder + CudaBVH, fixture)"
+    else:
+        built = ctx.build_bvh(verts, faces)
+        ctx.upload_built(built, sph)
+        host = ctx.built_to_host(built)
+        out["tree"] = "device-built (gpt_build_bvh), depth %d, %d inner nodes, %.1f ms" % (built.depth, built.n_inner_nodes, built.build_ms)
+    host = dict(host, verts=verts, faces=faces)
+    fails = []
+
+    # ---- rays
+    n = args.rays
+    o, d = incoherent_rays(verts, n, 7)
+    tri_o, addr_o, t_o, cnt = scenes.oracle_trace_rays(host, o, d, cull=True)
+    tri = torch.empty(n, dtype=torch.int32, device="cuda"); addr = torch.empty_like(tri)
+    t = torch.empty(n, dtype=torch.float32, device="cuda")
+    ctx.trace_rays(torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda(), n, True, tri, addr, t)
+    torch.cuda.synchronize()
+    tri, addr, t = tri.cpu().numpy(), addr.cpu().numpy(), t.cpu().numpy()
+    wide_nodes = ctx.wide_info()[0]
+    out["rays"] = {"n": n, "hit_fraction": float((t_o < 3e38).mean()), "t_mismatch": int((t != t_o).sum()),
+                   "face_mismatch": int((tri != tri_o).sum()), "slot_mismatch": int((addr != addr_o).sum()),
+                   "tree_in_use": "4-wide" if wide_nodes else "binary", "oracle_max_stack": int(cnt.max_stack),
+                   "oracle_nodes_per_ray": cnt.inner_nodes / n, "oracle_tris_per_ray": cnt.tri_tests / n}
+    if out["rays"]["hit_fraction"] < 0.05:
+        fails.append("rays: too few hits to mean anything")
+    if out["rays"]["t_mismatch"]:
+        fails.append("rays: t differs")
+    # on the wide tree two DIFFERENT triangles with bit-equal t (a ray through a shared edge) may swap: t-ties only, and rare
+    tie_ok = (t == t_o)
+    if wide_nodes:
+        if out["rays"]["face_mismatch"] > max(1, n // 5000) or not tie_ok[tri != tri_o].all():
+            fails.append("rays: face index differs beyond t-ties")
+    elif out["rays"]["face_mismatch"] or out["rays"]["slot_mismatch"]:
+        fails.append("rays: face index / slot differs on the binary tree")
+
+    # ---- primary-hit map, 1080p, jitter off
+    pw, ph = 1920, 1080
+    info = gpt.default_kernel_info(pw, ph)
+    ctx.set_flags(args.flags | gpt.FLAG_NO_JITTER)
+    geom_o, ptri_o, prim_o, pt_o, _ = scenes.oracle_primary(host, sph, info, 0, 0, flags=reflib.ORC_FLAG_NO_JITTER)
+    g = torch.empty(pw * ph, dtype=torch.int32, device="cuda"); pt_i = torch.empty_like(g); pp = torch.empty_like(g)
+    ptt = torch.empty(pw * ph, dtype=torch.float32, device="cuda")
+    ctx.trace_primary(info, 0, 0, g, pt_i, pp, ptt)
+    torch.cuda.synchronize()
+    ctx.set_flags(args.flags)
+    out["primary"] = {"size": [pw, ph], "mesh_pixels": int((geom_o == 0).sum()), "geom_mismatch": int((g.cpu().numpy() != geom_o).sum()),
+                      "face_mismatch": int((pt_i.cpu().numpy() != ptri_o).sum()), "prim_mismatch": int((pp.cpu().numpy() != prim_o).sum()),
+                      "t_mismatch": int((ptt.cpu().numpy() != pt_o).sum())}
+    if out["primary"]["mesh_pixels"] < 1000:
+        fails.append("primary: the mesh is not in view")
+    if any(out["primary"][k] for k in ("geom_mismatch", "face_mismatch", "prim_mismatch", "t_mismatch")):
+        fails.append("primary: hit map differs")
+
+    # ---- full-size frame, random pixels re-derived by the oracle
+    info = gpt.default_kernel_info(W, H)
+    info.depth = args.depth
+    info.triCurrentMat = mat
+    acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
+    frames_equal, calls, first = True, 0, None
+    ctx.reset_stats()
+    while True:
+        acc.zero_()
+        ctx.render(info, acc, 0, 0, args.spp)
+        torch.cuda.synchronize()
+        calls += 1
+        if first is None:
+            first = acc.clone()
+        else:
+            frames_equal = frames_equal and bool(torch.equal(first, acc))
+        pending = ctx.trial_info()[0]
+        if (not pending and calls >= 2) or calls >= 12:
+            break
+    st = ctx.stats()
+    a = first.cpu().numpy()
+    L = reflib.oracle()
+    osph, ns = scenes.orc_spheres(sph)
+    osc = scenes.orc_scene(host, osph, ns)
+    p = scenes.orc_params(info, 0)
+    rgb = (C.c_float * 3)()
+    rng = np.random.default_rng(1)
+    # half of the pixels where the mesh is (the primary map scaled to this frame), half anywhere
+    mesh_px = np.argwhere((geom_o == 0).reshape(ph, pw))
+    bad, worst = 0, 0.0
+    for k in range(args.pixels):
+        if k % 2 == 0 and len(mesh_px):
+            y, x = mesh_px[int(rng.integers(0, len(mesh_px)))]
+            px, py = min(W - 1, int(x * W // pw)), min(H - 1, int(y * H // ph))
+        else:
+            px, py = int(rng.integers(0, W)), int(rng.integers(0, H))
+        s = np.zeros(3, np.float32)
+        for smp in range(args.spp):
+            L.orc_sample(C.byref(osc), C.byref(p), px, py, C.c_uint64(smp), rgb, None)
+            s = (s + np.array(rgb[:], np.float32)).astype(np.float32)
+        if not np.array_equal(s, a[py, px, :3]):
+            bad += 1
+            worst = max(worst, float(np.abs(s - a[py, px, :3]).max()))
+    trial_pending, ns_per_ray = ctx.trial_info()
+    out["pixels"] = {"size": [W, H], "spp": args.spp, "depth": args.depth, "checked": args.pixels, "differing": bad, "worst_abs_diff": worst,
+                     "render_calls": calls, "frames_equal_across_calls": frames_equal, "trial_pending_after": trial_pending,
+                     "trial_ns_per_ray": ns_per_ray, "tree_in_use": "4-wide" if ctx.wide_info()[0] else "binary",
+                     "reorder_state": ctx.reorder_info()[0], "paths": int(st.paths), "rays": int(st.rays),
+                     "count_plane_ok": bool((a[..., 3] == args.spp).all()), "finite": bool(np.isfinite(a).all())}
+    if st.paths != calls * W * H * args.spp:
+        fails.append("pixels: path count")
+    if not (out["pixels"]["count_plane_ok"] and out["pixels"]["finite"] and frames_equal):
+        fails.append("pixels: count plane / finiteness / frames differ between calls")
+    if trial_pending:
+        fails.append("pixels: the per-scene trial never ended")
+    # the wide tree may resolve a bit-equal-t tie between two triangles the other way (same t, same material here): allow one pixel
+    if bad > (1 if ctx.wide_info()[0] else 0):
+        fails.append("pixels: %d of %d differ from the oracle" % (bad, args.pixels))
+    if built is not None:
+        ctx.free_bvh(built)
+    ctx.close()
+    out["fails"], out["ok"], out["total_s"] = fails, not fails, time.time() - t0
+    print(json.dumps(out))
+    return 0 if not fails else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

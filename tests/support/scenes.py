@@ -7,19 +7,15 @@ import numpy as np
 from . import reflib
 
 GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "golden")
-BIG = os.path.join(GOLDEN, "_big")   # git-ignored, regenerated by make_golden.py when /root/reference exists
 
 
 def scene_path(name):
-    for d in (GOLDEN, BIG):
-        p = os.path.join(d, "scene_%s.npz" % name)
-        if os.path.exists(p):
-            return p
-    return None
+    p = os.path.join(GOLDEN, "scene_%s.npz" % name)
+    return p if os.path.exists(p) else None
 
 
 def load_scene(name):
-    """dict(verts, faces, nodes(n,4), tris(n,4), woop(n,4), indices) built by the REFERENCE's SplitBVHBuilder+CudaBVH."""
+    """dict(verts, faces, nodes(n,4), tris(n,4), indices[, woop(n,4)]) built by the REFERENCE's SplitBVHBuilder+CudaBVH."""
     p = scene_path(name)
     if p is None:
         raise FileNotFoundError("scene fixture %s missing (run tests/golden/make_golden.py where /root/reference is mounted)" % name)

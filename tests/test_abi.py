@@ -132,3 +132,21 @@ def test_product_does_not_reference_oracle():
                 assert "liboracle" not in txt and "oracle/" not in txt and "orc_" not in txt, fn
     ldd = subprocess.check_output(["ldd", os.path.join(pkg, "libgpt_b200.so")]).decode()
     assert "oracle" not in ldd and "cpuref" not in ldd and "refbvh" not in ldd
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference not mounted")
+def test_adapter_compiles_against_reference(gpt, tmp_path):
+    """the adapter a maintainer adds (g.p.u-pathtracer_b200/host/tracer_b200.cpp) is compiled against
+    the REFERENCE's own BasicScene.hpp (BasicScene.hpp:32 declares launchKernel) and linked with libgpt_b200.so: it defines
+    BasicScene::launchKernel(const kernelInfo&) and every gpt_* symbol it uses resolves."""
+    deps = "/root/reference/deps"
+    obj, so = str(tmp_path / "tracer_b200.o"), str(tmp_path / "libadapter.so")
+    inc = ["-I" + REF, "-I" + deps + "/glm", "-I" + deps + "/glad/include", "-I" + deps + "/glfw/include", "-I" + deps + "/imgui",
+           "-I" + deps + "/tinyobjloader", "-I/usr/local/cuda/include", "-I" + os.path.join(ROOT, "include")]
+    src = os.path.join(os.path.dirname(gpt.LIB_PATH), "host", "tracer_b200.cpp")
+    subprocess.check_call(["g++", "-std=c++11", "-fPIC", "-w", "-c", src, "-o", obj] + inc)
+    syms = subprocess.check_output(["nm", "-C", obj]).decode()
+    assert re.search(r" T BasicScene::launchKernel\(kernelInfo const&\)", syms), syms
+    assert " U gpt_launch" in syms and " U gpt_invalidate_scene" in syms
+    lib_dir = os.path.dirname(gpt.LIB_PATH)
+    subprocess.check_call(["g++", "-shared", "-o", so, obj, "-L" + lib_dir, "-lgpt_b200", "-Wl,--no-undefined", "-Wl,-rpath," + lib_dir])

@@ -109,7 +109,7 @@ def test_built_tree_is_valid_and_traces_like_the_oracle(gpt, torch_cuda, name, m
         ctx.render(info, acc, 5, 0, 2)
         torch.cuda.synchronize()
         want = scenes.oracle_render(built, gpt.default_spheres(), info, 5, 0, 2)
-        assert np.mean(np.any(acc.cpu().numpy() != want, axis=-1)) <= 1e-3
+        assert np.mean(np.any(acc.cpu().numpy() != want, axis=-1)) == 0.0
         ctx.free_bvh(b)
 
 
@@ -199,7 +199,7 @@ def test_device_input_and_kernelinfo_dropin(gpt, torch_cuda):
         torch.cuda.synchronize()
         want = scenes.oracle_render(dict(sc, **arr), sph, info, gpt.hash64(0), 0, 1)[..., :3]
         got = accum.view(54, 96, 3).cpu().numpy()
-        assert np.mean(np.any(got != np.clip(want, 0, 1), axis=-1)) <= 1e-3
+        assert np.mean(np.any(got != np.clip(want, 0, 1), axis=-1)) == 0.0
         ctx.free_bvh(b)
 
 
