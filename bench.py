@@ -6,12 +6,19 @@ Workload (BASELINE.json configs[1]): Stanford bunny (Assets/bun
 fixture tests/golden/scene_bunny_cornell.npz), the 8 default spheres of BasicScene.cpp:177-218 plus one METAL
 sphere ("mixed diffuse/metal/specular"), 1920x1080, 16 spp per step per GPU, depth 8, default camera.
 
-One step = one progressive frame: every rank traces 16 samples/pixel (disjoint GLOBAL sample indices), the
-float4 sums are reduced onto rank 0 with one NCCL reduce, rank 0 resolves to RGBA8.  Weak scaling: the frame
-carries 16*N spp.  `value` = rays traced by all ranks / device time (max over ranks).
+One step = one progressive frame: every rank traces its slice of the frame's GLOBAL sample indices, the root sums the ranks'
+float4 frames (fused peer-memory reduce + accumulate + resolve kernel; --reduce nccl: one NCCL reduce) and resolves to RGBA8.
+Weak scaling (default): 16 spp per GPU, the frame carries 16*N spp.  --scaling strong (or GPT_BENCH_SCALING=strong): the frame is
+fixed at --frame-spp (default 16) samples whatever N.  `value` = rays traced by all ranks / device time (max over ranks).
 
   python bench.py [--gpus N --steps K --warmup W]        our CUDA path
   python bench.py --impl reference ...                   the reference's CPU tracer (oracle/_ref/libcpuref.so)
+
+The roofline block: `achieved` / `frac` are SURVEY 8-d's ALGORITHMIC bytes of the dominant kernel over its live launch time
+against the measured HBM copy peak (the contract's figure; the scene is cache-resident, so it can exceed 1), and beside it the
+fractions that can bind -- DRAM bytes actually moved, L2 and L1 bytes, issue slots -- each = per-ray counter of a committed ncu
+pass over one frame of this workload (profiles/r02_frame_counters.json) x live rays / live kernel time, against peaks MEASURED in
+this run by micro-benchmarks (gpt_measure_peaks).  `configs` repeats value + fractions for BASELINE configs 2 and 4.
 """
 import argparse
 import ctypes as C
@@ -44,34 +51,66 @@ def emit_line(line):
     out.flush()
 
 
-def load_algo_bytes():
-    """-> (bytes per ray of the whole bounce-loop iteration, bytes per ray of the BVH traversal alone)"""
-    p = os.path.join(ROOT, "profiles", "r01_algorithmic_bytes.json")
-    with open(p) as fh:
-        a = json.load(fh)[WORKLOAD]
-    trav = 64 * a["inner_nodes_per_ray"] + 48 * a["tri_tests_per_ray"] + 16 * a["leaf_terminators_per_ray"] + 4 * a["tri_hits_per_ray"]
-    return a["bytes_per_ray"], trav
+def load_algo_bytes(scene="bench"):
+    """-> dict of the oracle's per-ray counters for a scene (profiles/r02_algorithmic_bytes.json, made by
+    profiles/tools/algo_bytes.py; the round-1 full-frame count of the bench workload as the fallback), or None"""
+    p = os.path.join(ROOT, "profiles", "r02_algorithmic_bytes.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            a = json.load(fh).get(scene)
+        if a:
+            return a
+    if scene == "bench":
+        with open(os.path.join(ROOT, "profiles", "r01_algorithmic_bytes.json")) as fh:
+            a = json.load(fh)[WORKLOAD]
+        a["traversal_bytes_per_ray"] = (64 * a["inner_nodes_per_ray"] + 48 * a["tri_tests_per_ray"] + 16 * a["leaf_terminators_per_ray"]
+                                        + 4 * a["tri_hits_per_ray"])
+        return a
+    return None
 
 
-def load_issue_profile():
-    """warp instructions, lanes per instruction and issue-slot utilisation of one k_wf_extend_ww launch from the same committed
-    ncu capture (profiles/r01_traffic.json), or None."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+def load_frame_counters(scene="bench"):
+    """per-kernel-class counters of one frame, per ray, from the committed ncu counter pass (profiles/tools/ncu_frame.py +
+    ncu_frame_summary.py -> profiles/r02_frame_counters.json), or None"""
+    p = os.path.join(ROOT, "profiles", "r02_frame_counters.json")
     if not os.path.exists(p):
         return None
     with open(p) as fh:
-        d = json.load(fh).get("k_wf_extend_ww", {})
-    return d if "warp_instructions" in d else None
+        return json.load(fh).get(scene)
 
 
-def load_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum of one k_wf_extend_ww launch from the committed `ncu --set full`
-    capture of this same command (profiles/r01_traffic.json), or None."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if not os.path.exists(p):
+def bound_fractions(cls, rays, ms, peaks, hbm):
+    """The limits a kernel class can actually run into: committed per-ray counters x live rays / live time against peaks measured
+    in this run.  cls = one class of load_frame_counters(); every fraction is <= 1 by construction of its peak."""
+    if not cls or not rays or not ms:
         return None
-    with open(p) as fh:
-        return json.load(fh).get("k_wf_extend_ww", {}).get("dram_bytes_per_launch")
+    s = ms * 1e-3
+    out = {"lanes_per_instruction": cls.get("lanes_per_instruction"), "ncu_issue_active_pct": cls.get("issue_active_pct"),
+           "ncu_l1_hit_pct": cls.get("l1_hit_pct"), "ncu_l2_hit_pct": cls.get("l2_hit_pct")}
+
+    def frac(key, peak, unit, scale):
+        if cls.get(key) is None or not peak:
+            return None
+        ach = cls[key] * rays / s / scale
+        return {"per_ray": cls[key], "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak}
+    out["dram"] = frac("dram_bytes_per_ray", hbm, "GB/s", 1e9)
+    out["l2"] = frac("l2_bytes_per_ray", peaks.get("gather_l2_gbs"), "GB/s", 1e9)
+    out["l1"] = frac("l1_bytes_per_ray", peaks.get("gather_l1_gbs"), "GB/s", 1e9)
+    out["issue"] = frac("warp_inst_per_ray", peaks.get("warp_inst_per_s", 0) / 1e12, "T warp-inst/s", 1e12)
+    fr = {k: out[k]["frac"] for k in ("dram", "l2", "l1", "issue") if out.get(k)}
+    if fr:
+        out["binding"] = max(fr, key=fr.get)
+    return out
+
+
+def workload_config(args, world):
+    """the workload description both arms print (the driver compares the two dicts)"""
+    strong = args.scaling == "strong"
+    frame_spp = args.frame_spp if strong else args.spp * world
+    return {"workload": WORKLOAD, "scene": "Assets/cornell.obj + Assets/bunny_low.obj (5000 tris, reference SBVH) + 9 spheres",
+            "width": args.width, "height": args.height, "depth": args.depth, "frame_spp": frame_spp,
+            "spp_per_gpu_per_step": frame_spp / world if strong else args.spp, "scaling": args.scaling,
+            "l2": "256 MiB buffer written between steps (L2 flush); the scene itself (0.5 MB) is cache-resident by design"}
 
 
 def load_scene_arrays():
@@ -320,14 +359,100 @@ def run_reference_arm(args):
         "CpuRayTracer compiled from /root/reference (own scene, tree, RNG, Russian roulette)" if kind == "reference" else "scalar oracle port",
         cpu_model())
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f64" if kind == "reference" else "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "width": args.width, "height": args.height, "spp": args.spp, "depth": args.depth},
+            "config": workload_config(args, max(1, args.gpus)),
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit_line(line)
     return 0
+
+
+# ---------------------------------------------------------------- other BASELINE configs, one record each
+def config_records(gpt, torch, local, args, peaks, hbm, flush):
+    """BASELINE configs 2 and 4 on this GPU at reduced sample counts (throughput per sample does not depend on the count), under the
+    traversal plan the library picks by itself: value, ms, SURVEY 8-d algorithmic bytes per ray (committed oracle counters,
+    profiles/r02_algorithmic_bytes.json), the fractions that can bind (committed ncu counters of the same scene x live time,
+    against the peaks measured in this run) and the reference's own CUDA kernel on the very same arrays."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from support import config_check, procedural, refgpu, scenes
+    refk = refgpu.RefGpuKernel(local) if (refgpu.available() and not args.no_cpu_baseline) else None
+    sph = gpt.default_spheres()
+    out = {}
+    for name, spp, ref_spp in (("cfg2_dragon100k_sbvh", 16, 4), ("cfg2_dragon1p6M", 16, 2), ("cfg4_20M", 4, 1)):
+        t_wall = time.time()
+        verts, faces, ref_arrays, W, H, mat = config_check.make_scene(name, gpt, procedural, scenes)
+        info = gpt.default_kernel_info(W, H)
+        info.depth = args.depth
+        info.triCurrentMat = mat
+        rec = {"triangles": int(len(faces)), "width": W, "height": H, "spp_timed": spp, "depth": args.depth}
+        with gpt.Context(local, gpt.FLAG_TIME_KERNELS) as ctx:
+            built = None
+            if ref_arrays is not None:
+                ctx.upload_scene(ref_arrays["nodes"], ref_arrays["tris"], ref_arrays["indices"], sph)
+                rec["tree"] = "reference SBVH (SplitBVHBuilder + CudaBVH, fixture)"
+            else:
+                built = ctx.build_bvh(verts, faces)
+                ctx.upload_built(built, sph)
+                rec["tree"] = "device-built (gpt_build_bvh): depth %d, %.1f ms" % (built.depth, built.build_ms)
+            acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
+            for w in range(10):                               # buffers + the per-scene trial (<= 9 calls)
+                ctx.render(info, acc, 0, 1_000_000 + w * spp, spp)
+            torch.cuda.synchronize()
+            ctx.reset_stats()
+            reps = 3
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for r in range(reps):
+                flush.zero_()
+                ctx.render(info, acc, 0, r * spp, spp)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            st, kt = ctx.stats(), ctx.kernel_times()
+            rays = float(st.rays) / reps
+            rec.update({"value": rays / ms / 1e3, "unit": "Mrays/s", "ms_per_frame": ms, "rays_per_frame": rays,
+                        "tree_in_use": "4-wide" if ctx.wide_info()[0] else "binary", "ray_reordering": ctx.reorder_info()[0],
+                        "kernel_class_ms": {k: v[0] / reps for k, v in kt.items() if v[1]}})
+            ab = load_algo_bytes(name)
+            if ab:
+                rec["algorithmic_bytes_per_ray"] = {"traversal": ab["traversal_bytes_per_ray"], "whole_bounce": ab["bytes_per_ray"],
+                                                    "inner_nodes": ab["inner_nodes_per_ray"], "tri_tests": ab["tri_tests_per_ray"]}
+                ext_ms = kt["extend"][0] / reps
+                if ext_ms > 0:
+                    ach = ab["traversal_bytes_per_ray"] * rays / (ext_ms * 1e-3) / 1e9
+                    rec["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "kernel": "extend"}
+            fc = (load_frame_counters(name) or {}).get("classes", {})
+            if fc:
+                rec["bounds"] = {"extend": bound_fractions(fc.get("extend"), rays, kt["extend"][0] / reps, peaks, hbm),
+                                 "shade": bound_fractions(fc.get("shade"), rays, kt["shade"][0] / reps, peaks, hbm)}
+            if refk is not None:
+                arr = ref_arrays if ref_arrays is not None else ctx.built_to_host(built)
+                i2 = type(info).from_buffer_copy(info)
+                rs = refgpu.RefScene(torch, i2, arr, sph, local)
+
+                def frames(first, n):
+                    for f in range(n):
+                        i2.hash, i2.constantPdf = gpt.hash64(first + f), f + 1
+                        refk.launch(i2)
+                frames(0, 1)
+                torch.cuda.synchronize()
+                e0.record()
+                frames(1, ref_spp)
+                e1.record()
+                torch.cuda.synchronize()
+                rms = e0.elapsed_time(e1) / ref_spp * spp
+                rec["reference_gpu_kernel"] = {"ms_per_frame": rms, "speedup": rms / ms,
+                                               "what": "reference __global__ trace on the same arrays, %d one-sample launches timed, scaled to %d spp" % (ref_spp, spp)}
+                del rs
+            if built is not None:
+                ctx.free_bvh(built)
+        rec["wall_s"] = time.time() - t_wall
+        out[name] = rec
+    if refk is not None:
+        refk.close()
+    return out
 
 
 # ---------------------------------------------------------------- our arm
@@ -348,7 +473,12 @@ def run_ours(args):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
-    W, H, SPP = args.width, args.height, args.spp
+    W, H = args.width, args.height
+    strong = args.scaling == "strong"
+    FRAME_SPP = args.frame_spp if strong else args.spp * world      # samples of one progressive frame (all ranks together)
+    SPP = args.spp                                                   # single-GPU legs below (e2e, per-bounce, device tree)
+    if strong and FRAME_SPP < world:
+        raise SystemExit("bench.py: --frame-spp %d cannot be split over %d ranks" % (FRAME_SPP, world))
     sc = load_scene_arrays()
     sph = bench_spheres(gpt)
     info = bench_info(gpt, args)
@@ -383,17 +513,48 @@ def run_ours(args):
 
     def step(i, e2e=False):
         flush.zero_()                                                  # L2 flush between timed iterations
-        # weak scaling: every rank renders SPP samples of a SPP*world-sample progressive frame
+        # every rank renders its block of the frame's FRAME_SPP global sample indices (weak: SPP each; strong: FRAME_SPP / world)
         if peer is not None:
-            # fused path: root P2P-reads the peers' frames inside ONE reduce + accumulate + resolve kernel
-            peer.frame(render_ptr, i * SPP * world, SPP * world, total, rgba if rank == 0 else None, None, stream.cuda_stream)
+            # fused path: root P2P-reads the peers' frames inside ONE reduce + accumulate + resolve kernel, on a side stream
+            peer.frame(render_ptr, i * FRAME_SPP, FRAME_SPP, total, rgba if rank == 0 else None, None, stream)
         else:
-            mg.render_progressive_frame(render_fn, frame, total, i * SPP * world, SPP * world, dist=dist)
+            mg.render_progressive_frame(render_fn, frame, total, i * FRAME_SPP, FRAME_SPP, dist=dist)
             if rank == 0:
                 ctx.resolve(total, W, H, rgba, None, stream.cuda_stream)
         if rank == 0 and e2e:
+            if peer is not None:
+                peer.wait_reduced(stream)
             host_rgba.copy_(rgba, non_blocking=True)
             stream.synchronize()
+
+    def reduce_check():
+        """N > 1, untimed: one frame through the multi-GPU path (every rank its slice, root sums the ranks) against the SAME global
+        sample range rendered by rank 0 alone.  Sample indices are global, so the two frames hold the same samples; they differ
+        only in the association of the float sums.  Raises on mismatch."""
+        n = FRAME_SPP
+        chk = torch.zeros(H, W, 4, dtype=torch.float32, device=dev) if rank == 0 else None
+        if peer is not None:
+            peer.frame(render_ptr, 0, n, chk, None, None, stream)
+            if rank == 0:
+                peer.wait_reduced(stream)
+        else:
+            mg.render_progressive_frame(render_fn, frame, chk, 0, n, dist=dist)
+        torch.cuda.synchronize(dev)
+        res = None
+        if rank == 0:
+            alone = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
+            ctx.render(info, alone, args.seed, 0, n, stream.cuda_stream)
+            torch.cuda.synchronize(dev)
+            diff = float((chk[..., :3] - alone[..., :3]).abs().max().item())
+            count_ok = bool(torch.equal(chk[..., 3], alone[..., 3]) and float(alone[..., 3].min().item()) == float(n))
+            tol = 2e-6 * n * max(1.0, float(alone[..., :3].max().item()) / n)
+            res = {"frame_spp": n, "ranks": world, "max_abs_diff": diff, "tolerance": tol, "count_plane_exact": count_ok,
+                   "mean_radiance_alone": float(alone[..., :3].sum().item()) / (3.0 * W * H * n),
+                   "what": "peer-reduced float4 frame of all ranks vs the same global sample range rendered by rank 0 alone"}
+            if not (count_ok and diff <= tol):
+                raise SystemExit("bench.py: multi-GPU frame differs from the single-GPU render of the same samples: %r" % (res,))
+        k_events.clear()
+        return res
 
     def sync_all():
         torch.cuda.synchronize(dev)
@@ -407,6 +568,8 @@ def run_ours(args):
         t0.record(stream)
         for i in range(n_steps):
             step(first + i, e2e)
+        if peer is not None and rank == 0:
+            peer.wait_reduced(stream)              # the last frame's reduce runs on the root's side stream: it belongs to the timed region
         t1.record(stream)
         sync_all()
         ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
@@ -414,6 +577,7 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    check = reduce_check() if world > 1 else None
     for i in range(args.warmup):
         step(i)
     sync_all()
@@ -464,7 +628,14 @@ def run_ours(args):
             peaks = json.load(open(pk))
             hbm = float(peaks.get("hbm_gbs", hbm))
             peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
-        bpr, bpr_trav = load_algo_bytes()
+        ab = load_algo_bytes("bench")
+        bpr, bpr_trav = ab["bytes_per_ray"], ab["traversal_bytes_per_ray"]
+        fc = load_frame_counters("bench") or {}
+        fcls = fc.get("classes", {})
+        try:
+            live_peaks = ctx.measure_peaks()
+        except Exception as ex:
+            live_peaks = {"unavailable": repr(ex)}
         pass_avg_ms = float(np.mean(kernel_ms))
         pass_bytes = bpr * float(st.rays) / max(1, len(kernel_ms)) + ACCUM_BYTES_PER_PIXEL_PER_LAUNCH * W * H
         pass_achieved = pass_bytes / (pass_avg_ms * 1e-3) / 1e9
@@ -474,56 +645,53 @@ def run_ours(args):
             # dominant kernel: the BVH traversal.  Its algorithmic bytes are the traversal terms of SURVEY 8-d's formula
             # (nodes, triangles, terminators, index remap); the 44 B x spheres term belongs to k_wf_shade.
             k_total_ms, n_ext = ktimes["extend"]
-            kname, k_avg_ms, rays_per_launch, k_bytes_per_ray = "k_wf_extend_ww", k_total_ms / n_ext, float(st.rays) / n_ext, bpr_trav
+            kname, k_avg_ms, rays_per_launch, k_bytes_per_ray = "k_wf_extend_" + os.environ.get("GPT_WF_EXTEND", "pq"), k_total_ms / n_ext, float(st.rays) / n_ext, bpr_trav
         achieved = k_bytes_per_ray * rays_per_launch / (k_avg_ms * 1e-3) / 1e9
+        ext_ms, shade_ms = ktimes["extend"][0], ktimes["shade"][0]
+        dram_launch = fcls.get("extend", {}).get("dram_bytes_per_ray")
         line = {
             "metric": METRIC, "value": total_rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "scene": "Assets/cornell.obj + Assets/bunny_low.obj (5000 tris, reference SBVH) + 9 spheres",
-                       "width": W, "height": H, "spp_per_gpu_per_step": SPP, "frame_spp": SPP * world, "depth": args.depth,
-                       "pipeline": args.pipeline,
-                       "collective": "none" if world == 1 else ("none on the data path: root reads the peers' float4 frames over NVLink inside the fused "
-                                     "reduce+accumulate+resolve kernel (CUDA IPC); one 4-byte NCCL all_reduce per step as a stream-ordered barrier"
-                                     if peer is not None else "1 NCCL reduce(float4 accum) per step"),
-                       "l2": "256 MiB buffer written between steps (L2 flush); scene itself (0.5 MB) is cache-resident by design",
-                       "rays_per_step": total_rays / args.steps, "ms_per_frame_16spp": ms / args.steps},
+            "config": workload_config(args, world),
+            "run": {"pipeline": args.pipeline, "extend_schedule": os.environ.get("GPT_WF_EXTEND", "pq (pooled leaf phases)"),
+                    "collective": "none" if world == 1 else ("none on the data path: root reads the peers' float4 frames over NVLink inside the fused "
+                                  "reduce+accumulate+resolve kernel (CUDA IPC) on a side stream; one 4-byte NCCL all_reduce per step as a stream-ordered barrier"
+                                  if peer is not None else "1 NCCL reduce(float4 accum) per step"),
+                    "rays_per_step": total_rays / args.steps, "ms_per_frame": ms / args.steps},
             "e2e": {"value": e2e_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 296,
                     "d2h_bytes_per_step": W * H * 4, "ms_per_step": e2e_ms / args.steps,
                     "what": "gpt_render_frame_host: kernelInfo by value in, RGBA8 frame to pinned host memory out, sync per step"
-                            if world == 1 else "render + NCCL reduce + resolve + RGBA8 D2H to pinned host on rank 0, sync per step"},
+                            if world == 1 else ("every rank renders its slice; " + ("fused peer-memory reduce + accumulate + resolve on the root" if peer is not None
+                                                else "NCCL reduce + accumulate + resolve") + "; RGBA8 D2H to pinned host on rank 0, sync per step")},
             "gpu_launches": launches,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": load_traffic(),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                         "traffic": dram_launch * rays_per_launch if dram_launch else None,
                          "kernel": kname, "kernel_ms_avg": k_avg_ms, "kernel_share_of_step": k_total_ms / ms,
                          "algorithmic_bytes_per_ray": k_bytes_per_ray, "rays_per_launch": rays_per_launch,
                          "algorithmic_bytes_per_launch": k_bytes_per_ray * rays_per_launch, "peak_source": peak_src,
+                         "note": "the contract's figure: SURVEY 8-d algorithmic bytes / live launch time against the measured HBM copy peak.  The packed scene "
+                                 "(0.4 MB) is L1/L2 resident, those bytes never reach DRAM and the fraction may exceed 1: it bounds nothing here.  `traffic` = DRAM "
+                                 "bytes one launch really moves (ray state).  The fractions that can bind are under `bounds`.",
+                         "peaks_measured_this_run": live_peaks,
+                         "bounds": {"extend": bound_fractions(fcls.get("extend"), float(st.rays), ext_ms, live_peaks, hbm),
+                                    "shade": bound_fractions(fcls.get("shade"), float(st.rays), shade_ms, live_peaks, hbm),
+                                    "what": "per kernel class: committed ncu per-ray counters (profiles/r02_frame_counters.json: one frame of this workload, "
+                                            "every launch) x live rays / live class time, against peaks measured in this run by gpt_measure_peaks: DRAM bytes vs "
+                                            "the HBM copy peak, L2 / L1 bytes vs random 64-byte gather bandwidth from an L2- / L1-resident working set, warp "
+                                            "instructions vs the measured issue rate; `binding` = the largest fraction"},
                          "whole_pass": {"achieved": pass_achieved, "frac": pass_achieved / hbm, "bytes_per_ray": bpr, "ms_avg": pass_avg_ms,
-                                        "what": "all kernels of one gpt_render pass (generate, extend, shade, collect, accumulate)"},
+                                        "what": "all kernels of one gpt_render pass (extend, shade, accumulate), algorithmic bytes incl. 44 B x spheres"},
                          "kernel_class_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]},
-                         "kernel_class_launches_per_step": {k: v[1] / args.steps for k, v in ktimes.items() if v[1]},
-                         "note": "scene (0.4 MB packed) is L1/L2 resident: algorithmic bytes are served by cache, so the fraction can exceed 1 "
-                                 "of HBM peak; the binding resource is issue slots x SIMT efficiency (profiles/)"},
+                         "kernel_class_launches_per_step": {k: v[1] / args.steps for k, v in ktimes.items() if v[1]}},
             "clocks": sampler.summary(),
         }
-        ip = load_issue_profile()
-        if ip is not None and kname == "k_wf_extend_ww":
-            # second view of the same kernel: the resource that actually binds it.  Peak = 4 warp instructions per SM per clock.
-            sm_count = torch.cuda.get_device_properties(0).multi_processor_count
-            mhz = (line["clocks"] or {}).get("sm_mhz") or 1965.0
-            peak = sm_count * 4 * mhz * 1e6
-            per_ray = ip["warp_instructions"] / 33177011.875
-            ach = per_ray * rays_per_launch / (k_avg_ms * 1e-3)
-            line["roofline"]["issue"] = {"bound": "issue slots", "warp_instructions_per_ray": per_ray, "lanes_per_instruction": ip["lanes_per_instruction"],
-                                         "achieved": ach / 1e12, "peak": peak / 1e12, "unit": "T warp-inst/s", "frac": ach / peak,
-                                         "ncu_issue_active_pct": ip["issue_active_pct"],
-                                         "what": "warp instructions per ray from the committed ncu capture x rays per launch / live launch time, against "
-                                                 "SMs x 4 schedulers x SM clock; the fraction the HBM figure cannot show"}
+        if check is not None:
+            line["reduce_check"] = check
         # SURVEY 8-d "secondary figure": traversal steps/s = (inner nodes + triangle tests) per ray (oracle counters on the reference
         # arrays, profiles/r01_algorithmic_bytes.json) x rays/s, and rays/s per bounce index (coherent primaries vs incoherent
         # secondaries) from depth-limited renders of the same samples: bounce b = render(depth b+1) - render(depth b)
         try:
-            with open(os.path.join(ROOT, "profiles", "r01_algorithmic_bytes.json")) as fh:
-                ab = json.load(fh)[WORKLOAD]
             steps_per_ray = ab["inner_nodes_per_ray"] + ab["tri_tests_per_ray"]
             line["traversal_steps"] = {"per_ray": steps_per_ray, "value": steps_per_ray * line["value"] / 1e3, "unit": "G steps/s",
                                        "what": "(inner-node visits + triangle tests) of the reference algorithm per ray x rays/s"}
@@ -552,7 +720,7 @@ def run_ours(args):
                     pb.append({"bounce": b, "rays": dr, "ms": dt, "Mrays_s": dr / (dt * 1e-3) / 1e6 if dt > 0 else None})
                     prev = c
                 line["per_bounce"] = {"rows": pb, "what": "differences of depth-limited renders of the same 16 samples (bounce 0 also carries "
-                                      "generate + collect + accumulate); no L2 flush between repetitions"}
+                                      "the accumulate pass); no L2 flush between repetitions"}
             except Exception as ex:
                 line["per_bounce"] = {"unavailable": repr(ex)}
         if world == 1 and args.pipeline != "mega":
@@ -585,6 +753,47 @@ def run_ours(args):
                     c2.free_bvh(built)
             except Exception as ex:
                 line["device_built_tree"] = {"unavailable": repr(ex)}
+        if world == 1 and args.pipeline != "mega":
+            # opt-in GPT_FLAG_FAST (MUFU shading arithmetic; statistical parity, tests/test_gpu_refkernel.py "/FAST" cases): same steps
+            try:
+                with gpt.Context(local, gpt.FLAG_FAST) as c3:
+                    c3.upload_scene(sc["nodes"], sc["tris"], sc["indices"], sph)
+                    f2 = torch.zeros_like(frame)
+                    for i in range(max(3, args.warmup)):
+                        c3.render(info, f2, args.seed, i * SPP, SPP, stream.cuda_stream)
+                    torch.cuda.synchronize(dev)
+                    c3.reset_stats()
+                    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    t0.record(stream)
+                    for i in range(args.steps):
+                        flush.zero_()
+                        f2.zero_()
+                        c3.render(info, f2, args.seed, (i + 8) * SPP, SPP, stream.cuda_stream)
+                        c3.resolve(f2, W, H, rgba, None, stream.cuda_stream)
+                    t1.record(stream)
+                    torch.cuda.synchronize(dev)
+                    ms3 = t0.elapsed_time(t1)
+                    rays3 = float(c3.stats().rays)
+                    # the same samples in both modes: what the changed arithmetic does to a 16-spp frame
+                    frame.zero_(); f2.zero_()
+                    ctx.render(info, frame, args.seed, 0, SPP, stream.cuda_stream)
+                    c3.render(info, f2, args.seed, 0, SPP, stream.cuda_stream)
+                    torch.cuda.synchronize(dev)
+                    a, b = frame[..., :3] / SPP, f2[..., :3] / SPP
+                    line["fast_mode"] = {"value": rays3 / (ms3 * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms3 / args.steps,
+                                         "parity": {"contract": "statistical, against the reference's GPU kernel at 1024 spp (tests/test_gpu_refkernel.py, cases "
+                                                                "'/FAST': mean z^2 <= 1.6, |mean z| <= 0.05, box-filtered RMSE <= 1e-3); primary hits identical",
+                                                    "same_samples_vs_compat": {"mean_radiance_compat": float(a.mean().item()), "mean_radiance_fast": float(b.mean().item()),
+                                                                               "rmse": float(((a - b) ** 2).mean().sqrt().item()),
+                                                                               "pixels_differing_by_more_than_1e-3": float(((a - b).abs().amax(dim=-1) > 1e-3).float().mean().item())}},
+                                         "what": "GPT_FLAG_FAST: rsqrt normalisation and hardware sin/cos/pow/reciprocal in the shade kernel; traversal unchanged; opt-in"}
+            except Exception as ex:
+                line["fast_mode"] = {"unavailable": repr(ex)}
+        if world == 1 and not args.no_configs:
+            try:
+                line["configs"] = config_records(gpt, torch, local, args, live_peaks, hbm, flush)
+            except Exception as ex:      # a secondary leg must never take the headline down
+                line["configs"] = {"unavailable": repr(ex)}
         if world == 1 and not args.no_cpu_baseline:
             base, port = cpu_baseline(gpt, sc, args)
             line["cpu_baseline"] = base
@@ -619,6 +828,10 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--pipeline", default="wavefront", choices=["mega", "wavefront"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the per-config records (BASELINE configs 2 and 4)")
+    ap.add_argument("--scaling", default=os.environ.get("GPT_BENCH_SCALING", "weak"), choices=["weak", "strong"],
+                    help="multi-GPU: weak = --spp samples per GPU per step (default); strong = a fixed frame of --frame-spp samples split over the GPUs")
+    ap.add_argument("--frame-spp", type=int, default=int(os.environ.get("GPT_BENCH_FRAME_SPP", "16")), help="samples of the fixed frame under --scaling strong")
     ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"], help="multi-GPU frame reduce: fused P2P kernel (default) or torch.distributed.reduce")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

@@ -30,6 +30,7 @@ FLAG_WIDE_BVH = 1 << 5        # always traverse the 4-wide quantised tree (SURVE
 FLAG_BINARY_BVH = 1 << 6      # always traverse the binary tree as uploaded
 FLAG_WAVEFRONT = 1 << 7       # always the wavefront pipeline (default: megakernel for calls under GPT_SMALL_FRAME_PATHS paths)
 FLAG_BUILD_LBVH = 1 << 8      # build_bvh: Morton radix tree instead of PLOC clustering
+FLAG_FAST = 1 << 10           # opt-in fast shading arithmetic (statistical parity, not bit-exact)
 FLAG_NO_TRIAL = 1 << 9        # no timed per-scene trial: render calls never synchronise (graph capture, strict asynchrony)
 K_GENERATE, K_EXTEND, K_SHADE, K_COLLECT, K_ACCUMULATE, K_RESOLVE, K_OTHER = range(7)
 
@@ -86,6 +87,10 @@ class BuiltBVH(C.Structure):  # gpt_built_bvh
                 ("depth", C.c_uint32), ("build_ms", C.c_float)]
 
 
+class Peaks(C.Structure):  # gpt_peaks
+    _fields_ = [("gather_l1_gbs", C.c_double), ("gather_l2_gbs", C.c_double), ("gather_hbm_gbs", C.c_double), ("warp_inst_per_s", C.c_double)]
+
+
 class KernelTimes(C.Structure):
     _fields_ = [("ms", C.c_double * 8), ("launches", C.c_uint64 * 8)]
 
@@ -96,7 +101,7 @@ assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 # every symbol include/gpt.h declares (tests check the library exports each one)
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
            "gpt_upload_scene", "gpt_launch", "gpt_invalidate_scene", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
-           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info",
+           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_measure_peaks", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
            "gpt_reduce_resolve_ptrs", "gpt_frame_free",
@@ -135,6 +140,7 @@ def load_library():
     L.gpt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
     L.gpt_reset_stats.argtypes = [C.c_void_p]
     L.gpt_get_kernel_times.argtypes = [C.c_void_p, C.POINTER(KernelTimes)]
+    L.gpt_measure_peaks.argtypes = [C.c_void_p, C.POINTER(Peaks)]
     L.gpt_wide_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.gpt_reorder_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.gpt_trial_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double)]
@@ -495,6 +501,12 @@ class Context:
         self._ck(self._L.gpt_get_kernel_times(self._h, C.byref(t)), "gpt_get_kernel_times")
         names = ["generate", "extend", "shade", "collect", "accumulate", "resolve", "other"]
         return {n: (t.ms[i], int(t.launches[i])) for i, n in enumerate(names)}
+
+    def measure_peaks(self):
+        """micro-benchmarked peaks of this device (gpt_measure_peaks): dict of gather GB/s per memory level and warp instructions/s"""
+        pk = Peaks()
+        self._ck(self._L.gpt_measure_peaks(self._h, C.byref(pk)), "gpt_measure_peaks")
+        return {k: getattr(pk, k) for k, _ in Peaks._fields_}
 
     def reset_stats(self):
         self._ck(self._L.gpt_reset_stats(self._h), "gpt_reset_stats")

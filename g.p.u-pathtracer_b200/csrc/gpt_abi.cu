@@ -168,7 +168,7 @@ static const long long k_env_small_frame = []{ const char* e = getenv("GPT_SMALL
 static bool use_megakernel(const gpt_ctx* c, size_t n_paths)
 {
     if (c->flags & GPT_FLAG_MEGAKERNEL) return true;
-    if (c->flags & GPT_FLAG_WAVEFRONT) return false;
+    if (c->flags & (GPT_FLAG_WAVEFRONT | GPT_FLAG_FAST)) return false;      // the fast arithmetic exists in the pipeline's shade kernel only
     return (long long)n_paths < k_env_small_frame;
 }
 
@@ -327,7 +327,8 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "device re-pack", e);
     if (r.bad_layout) {
         char buf[160];
-        if (r.bad_layout == 5) snprintf(buf, sizeof(buf), "BVH has %d or more inner levels: deeper than the %d-entry traversal stack (cudaUtils.h:22)", GPT_STACK_SIZE, GPT_STACK_SIZE);
+        if (r.bad_layout == 6) snprintf(buf, sizeof(buf), "scene too large: more than %d triangle references after spatial splits", (1 << GPT_LEAF_FIRST_BITS) - 2);
+        else if (r.bad_layout == 5) snprintf(buf, sizeof(buf), "BVH has %d or more inner levels: deeper than the %d-entry traversal stack (cudaUtils.h:22)", GPT_STACK_SIZE, GPT_STACK_SIZE);
         else snprintf(buf, sizeof(buf), "malformed BVH arrays (code %d): not a CudaBVH BVHLayout_Compact tree", r.bad_layout);
         return fail(c, GPT_ERR_LAYOUT, buf);
     }
@@ -493,6 +494,7 @@ static int make_params(gpt_ctx* c, const gpt_kernel_info* info, uint64_t seed, R
     p->phong = info->phongExpo;
     p->seed = seed;
     p->flags = c->flags & (GPT_FLAG_NO_JITTER | GPT_FLAG_METAL_FIXED | GPT_FLAG_COUNT_BOUNCES);
+    if (c->flags & GPT_FLAG_FAST) p->flags |= RP_FAST;
     return GPT_OK;
 }
 
@@ -791,6 +793,17 @@ int gpt_get_kernel_times(gpt_ctx* c, gpt_kernel_times* out)
     CU(c, cudaDeviceSynchronize());
     c->timer.collect(c->kt_ms, c->kt_n);
     for (int i = 0; i < 8; ++i) { out->ms[i] = c->kt_ms[i]; out->launches[i] = c->kt_n[i]; }
+    return GPT_OK;
+}
+
+int gpt_measure_peaks(gpt_ctx* c, gpt_peaks* out)
+{
+    if (!c || !out) return GPT_ERR_INVALID;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());
+    cudaError_t e = gptk_measure_peaks(c->sm_count, &out->gather_l1_gbs, &out->gather_l2_gbs, &out->gather_hbm_gbs, &out->warp_inst_per_s);
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "gpt_measure_peaks", e);
+    c->launches += 16;
     return GPT_OK;
 }
 

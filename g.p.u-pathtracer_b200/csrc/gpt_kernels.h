@@ -68,6 +68,9 @@ struct BuildResult { float4* nodes; size_t n_node_vec4; float4* tris; size_t n_t
 cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, size_t n_tris, int max_leaf, int ploc_radius,
                             BuildResult* out, cudaStream_t st);
 
+// device peaks measured by micro-benchmarks (gpt_peaks.cu; diagnostics for bench.py's roofline)
+cudaError_t gptk_measure_peaks(int sm_count, double* l1_gbs, double* l2_gbs, double* hbm_gbs, double* warp_inst_per_s);
+
 // 4-wide quantised BVH collapsed on the device from the packed binary nodes (gpt_wide.cu).
 // status: 0 ok, 1 non-finite / inverted box (not quantisable), 2 internal, 3 not a tree
 struct WideResult { float4* wnodes; int n_wide; int levels; int status; int launches; };
@@ -87,7 +90,7 @@ struct WaveBuffers {
 size_t gptk_wave_counter_count(unsigned int depth);
 size_t gptk_wave_sort_tmp_bytes(size_t capacity);
 // per-context launch configuration of the pipeline (grids from the kernels' occupancy on this device, environment knobs)
-struct WaveLaunchCfg { int ready, sm_count, ext_grid, wide_grid, shade_grid, sort_mode, refill_min, node_k_env; size_t wave_cap_env; };
+struct WaveLaunchCfg { int ready, sm_count, ext_grid, wide_grid, pq_grid, pq_wide_grid, shade_grid, sort_mode, refill_min, node_k_env, pooled, hold_k_env, pq_refill_min; size_t wave_cap_env; };
 void gptk_wave_launch_cfg(WaveLaunchCfg* cfg, int sm_count);
 // wb.counters must be all zero on entry and are all zero again once the enqueued work has run
 cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb, const WaveLaunchCfg& cfg,

@@ -111,3 +111,22 @@ __device__ __forceinline__ float det_powf(float x, float y)
     q = fmaf(q, g, 1.0f);
     return __uint_as_float(__float_as_uint(q) + ((uint32_t)(int)zi << 23));
 }
+
+
+// ---- GPT_FLAG_FAST arithmetic (opt-in; held to north_star's statistical tolerance, NOT bit-exact to the oracle) ------------
+// The compat contract pins IEEE sqrt + divide normalisations and FMA-only sin/cos/pow polynomials so that the CPU oracle can be
+// matched bit for bit.  FAST swaps them for the special-function unit: MUFU.RSQ / RCP / SIN / COS / EX2 / LG2 (1-2 ulp), and lets
+// the remaining products contract.  The traversal (nearest hit, face index) is NOT affected: only shading arithmetic changes.
+template <bool FAST> __device__ __forceinline__ f3 norm3_t(f3 a)
+{
+    if (FAST) { const float inv = rsqrtf(dot3(a, a)); return scale3(a, inv); }
+    return normalize3(a);
+}
+template <bool FAST> __device__ __forceinline__ float sqrt_t(float x) { return FAST ? __fmul_rn(x, rsqrtf(fmaxf(x, 1e-30f))) : sqrtf(x); }
+template <bool FAST> __device__ __forceinline__ float fdiv_t(float a, float b) { return FAST ? __fdividef(a, b) : a / b; }
+template <bool FAST> __device__ __forceinline__ void sincos2pi_t(float u, float& s, float& c)
+{
+    if (FAST) { __sincosf(6.2831853071795864769f * (u - rintf(u)), &s, &c); }      // argument reduced to [-pi, pi] for MUFU.SIN / COS
+    else sincos2pi(u, s, c);
+}
+template <bool FAST> __device__ __forceinline__ float pow_t(float x, float y) { return FAST ? __powf(x, y) : det_powf(x, y); }

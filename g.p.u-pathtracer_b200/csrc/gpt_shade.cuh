@@ -59,7 +59,8 @@ __device__ __forceinline__ f3 box_normal(const float* bx, f3 p)
 // hit fma(mask, 0, accu) == accu bit for bit for a finite mask, so the slot is neither read nor written.
 // FIRST (bounce 0 of the wavefront pipeline): the accumulated colour is still 0 (tracer.cu:69) and the slot holds nothing yet:
 // it is written unconditionally, never read.
-template <bool FIRST = false>
+// FAST: GPT_FLAG_FAST arithmetic (gpt_math.cuh): same formulas, special-function unit instead of the IEEE / polynomial forms.
+template <bool FIRST = false, bool FAST = false>
 __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderParams& p,
                                              const float* s_spheres, const float* s_boxes,
                                              const SceneHit h, const uint32_t pixel, const uint64_t sample,
@@ -77,14 +78,14 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
     f3 n, nl, objcol, emit; int mat;
     if (h.geom == GEO_SPHERE) {                                          // :113-122
         const float* s = s_spheres + 11 * h.prim;
-        n = normalize3(sub3(hitpos, mk3(s[0], s[1], s[2])));
+        n = norm3_t<FAST>(sub3(hitpos, mk3(s[0], s[1], s[2])));
         nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
         emit = mk3(s[4], s[5], s[6]); objcol = mk3(s[7], s[8], s[9]); mat = __float_as_int(s[10]);
     } else if (h.geom == GEO_TRI) {                                      // :123-139
         const float4 b = __ldg(sc.tris + 3 * h.prim + 1);
         const float4 c = __ldg(sc.tris + 3 * h.prim + 2);
         // cross(v0-v1, v0-v2) == cross(e1, e2) bit for bit (negation is exact)   cudaUtils.h:432
-        n = normalize3(cross3(mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z)));
+        n = norm3_t<FAST>(cross3(mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z)));
         nl = n;                                                          // Q4: not face-forwarded
         emit = ld3(p.emi); objcol = ld3(p.col); mat = p.tri_mat;
         if (sc.n_faces) {                                                // N4: per-face material table
@@ -119,59 +120,59 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
     f3 nextdir;
     if (mat == MAT_DIFF) {                                               // :156-186 (Q5)
         f3 nt = (fabsf(nl.x) > fabsf(nl.y)) ? mk3(nl.z, 0.0f, -nl.x) : mk3(0.0f, -nl.z, nl.y);
-        nt = normalize3(nt);
-        const f3 nb = normalize3(cross3(nl, nt));
-        float sn, cs; sincos2pi(u.x, sn, cs);
+        nt = norm3_t<FAST>(nt);
+        const f3 nb = norm3_t<FAST>(cross3(nl, nt));
+        float sn, cs; sincos2pi_t<FAST>(u.x, sn, cs);
         const float f2 = u.y;                                            // sin(theta), uniform (cudaUtils.h:185-192)
-        const f3 rv = mk3(cs * f2, sqrtf(fmaf(-f2, f2, 1.0f)), sn * f2);
+        const f3 rv = mk3(cs * f2, sqrt_t<FAST>(fmaf(-f2, f2, 1.0f)), sn * f2);
         nextdir = mk3(fmaf(nt.x, rv.z, fmaf(nl.x, rv.y, nb.x * rv.x)),
                       fmaf(nt.y, rv.z, fmaf(nl.y, rv.y, nb.y * rv.x)),
                       fmaf(nt.z, rv.z, fmaf(nl.z, rv.y, nb.z * rv.x)));
-        nextdir = normalize3(nextdir);
+        nextdir = norm3_t<FAST>(nextdir);
         hitpos = mad3(nl, 0.001f, hitpos);
         ps.mask = mul3(ps.mask, objcol);
     } else if (mat == MAT_SPEC) {                                        // :190-203 (Q6)
         // :194 'dir - nl * dot * 2.0f' the way nvcc emits it for the reference: pr = rn(nl*k), 2*pr formed as fma(k, nl, pr), plain subtract
         const float k = dot3(nl, ps.d);
         const f3 pr = scale3(nl, k);
-        nextdir = normalize3(mk3(ps.d.x - fmaf(k, nl.x, pr.x), ps.d.y - fmaf(k, nl.y, pr.y), ps.d.z - fmaf(k, nl.z, pr.z)));
+        nextdir = norm3_t<FAST>(mk3(ps.d.x - fmaf(k, nl.x, pr.x), ps.d.y - fmaf(k, nl.y, pr.y), ps.d.z - fmaf(k, nl.z, pr.z)));
         hitpos = mad3(nl, 0.001f, hitpos);
         ps.mask = mul3(ps.mask, objcol);
     } else if (mat == MAT_REFR) {                                        // :205-256 (Q7)
         const bool into = dot3(n, nl) > 0.0f;
         const float nc = p.air, ntr = p.glass;
-        const float nnt = into ? nc / ntr : ntr / nc;
+        const float nnt = into ? fdiv_t<FAST>(nc, ntr) : fdiv_t<FAST>(ntr, nc);
         const float ddn = dot3(ps.d, nl);
         const float cos2t = fmaf(-(nnt * nnt), fmaf(-ddn, ddn, 1.0f), 1.0f);        // :212, contracted as in the reference's SASS
         if (cos2t < 0.0f) {
             const float k = dot3(n, ps.d) * 2.0f;
-            nextdir = normalize3(mad3(n, -k, ps.d));
+            nextdir = norm3_t<FAST>(mad3(n, -k, ps.d));
         } else {
-            const float s = (into ? 1.0f : -1.0f) * fmaf(ddn, nnt, sqrtf(cos2t));
-            const f3 tdir = normalize3(mad3(n, -s, scale3(ps.d, nnt)));
+            const float s = (into ? 1.0f : -1.0f) * fmaf(ddn, nnt, sqrt_t<FAST>(cos2t));
+            const f3 tdir = norm3_t<FAST>(mad3(n, -s, scale3(ps.d, nnt)));
             const float R0 = ((ntr - nc) * (ntr - nc)) / (ntr + nc) * (ntr + nc);   // :230 precedence kept
             const float c = 1.0f - (into ? -ddn : dot3(tdir, n));
             const float Re = fmaf((1.0f - R0) * c * c * c * c, c, R0);           // :232, last product fused into the sum
             const float Tr = 1.0f - Re;
             const float P = 0.25f + 0.5f * Re;
-            const float RP = Re / P, TP = Tr / (1.0f - P);
+            const float RP = fdiv_t<FAST>(Re, P), TP = fdiv_t<FAST>(Tr, 1.0f - P);
             if (u.x < 0.2f) {                                            // :239 constant, not P
                 ps.mask = scale3(ps.mask, RP);
                 const float k = dot3(n, ps.d) * 2.0f;
-                nextdir = normalize3(mad3(n, -k, ps.d));
+                nextdir = norm3_t<FAST>(mad3(n, -k, ps.d));
             } else {
                 ps.mask = scale3(ps.mask, TP);
-                nextdir = normalize3(tdir);
+                nextdir = norm3_t<FAST>(tdir);
             }
         }
         hitpos = mad3(nl, 0.001f, hitpos);
     } else {                                                             // METAL :257-293 (Q1)
-        float sphi, cphi; sincos2pi(u.x, sphi, cphi);
-        const float cosT = det_powf(1.0f - u.y, 1.0f / (p.phong + 1.0f));
-        const float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));
+        float sphi, cphi; sincos2pi_t<FAST>(u.x, sphi, cphi);
+        const float cosT = pow_t<FAST>(1.0f - u.y, fdiv_t<FAST>(1.0f, p.phong + 1.0f));
+        const float sinT = sqrt_t<FAST>(fmaf(-cosT, cosT, 1.0f));
         const float k = dot3(nl, ps.d) * 2.0f;
-        const f3 w1 = normalize3(mad3(nl, -k, ps.d));
-        const f3 uu = normalize3(cross3(fabsf(w1.x) >= 0.1f ? mk3(0, 1, 0) : mk3(1, 0, 0), w1));
+        const f3 w1 = norm3_t<FAST>(mad3(nl, -k, ps.d));
+        const f3 uu = norm3_t<FAST>(cross3(fabsf(w1.x) >= 0.1f ? mk3(0, 1, 0) : mk3(1, 0, 0), w1));
         const f3 vv = cross3(w1, uu);
         const float a = cphi * sinT, b = sphi * sinT;
         if (p.flags & RP_METAL_FIXED) {
@@ -182,7 +183,7 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
             const float wc = (float)p.width * cosT;                      // :280 `w` = int image width
             nextdir = mk3(fmaf(vv.x, b, uu.x * a) + wc, fmaf(vv.y, b, uu.y * a) + wc, fmaf(vv.z, b, uu.z * a) + wc);
         }
-        nextdir = normalize3(nextdir);
+        nextdir = norm3_t<FAST>(nextdir);
         hitpos = mad3(nl, 0.0001f, hitpos);
         ps.mask = mul3(ps.mask, objcol);
     }

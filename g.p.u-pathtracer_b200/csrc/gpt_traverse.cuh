@@ -78,8 +78,9 @@ __device__ __forceinline__ bool trav_wants_node(const TravState& s) { return (un
 __device__ __forceinline__ bool trav_wants_tri(const TravState& s) { return s.leaf < 0; }
 __device__ __forceinline__ bool trav_finished(const TravState& s) { return s.node == GPT_SENTINEL && s.leaf >= 0; }
 
-// One inner-node visit: cudaUtils.h:305-369.  Requires trav_wants_node(s).
-__device__ __forceinline__ void node_step(const float4* __restrict__ nodes, TravState& s, int* stack)
+// One inner-node visit, cudaUtils.h:305-360: the child to go to next (inner node >= 0, leaf < 0, or what the stack gives back),
+// the far child pushed.  Requires trav_wants_node(s).
+__device__ __forceinline__ int node_next(const float4* __restrict__ nodes, TravState& s, int* stack)
 {
     const int node = s.node;
     const float4 n0 = __ldg(nodes + node);
@@ -111,8 +112,15 @@ __device__ __forceinline__ void node_step(const float4* __restrict__ nodes, Trav
             ++s.sp; stack[s.sp] = far_child;
         }
     }
+    return next;
+}
+
+// One inner-node visit with the reference's leaf handling, cudaUtils.h:305-369.
+__device__ __forceinline__ void node_step(const float4* __restrict__ nodes, TravState& s, int* stack)
+{
+    int next = node_next(nodes, s, stack);
     if (next < 0 && s.leaf >= 0) {           // first leaf: postpone it and keep descending (:362-369)
-        s.leaf = next; s.tri_cur = ~next;
+        s.leaf = next; s.tri_cur = GPT_LEAF_FIRST(~next);
         next = stack[s.sp]; --s.sp;
     }
     s.node = next;
@@ -125,7 +133,7 @@ __device__ __forceinline__ void node_step(const float4* __restrict__ nodes, Trav
 // masking the bytes in with LOP3 at two scales instead was 2 % slower).
 static __constant__ unsigned gpt_w4_magic = 0x4B000000u;
 #define W4_CSWAP(ka, ca, kb, cb) { const bool sw_ = kb < ka; const float tk_ = sw_ ? ka : kb; const int tc_ = sw_ ? ca : cb; ka = sw_ ? kb : ka; ca = sw_ ? cb : ca; kb = tk_; cb = tc_; }
-__device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravState& s, int* stack)
+__device__ __forceinline__ int node4_next(const float4* __restrict__ wn, TravState& s, int* stack)
 {
     const int node = s.node;
     const float4 h = __ldg(wn + node);
@@ -170,8 +178,13 @@ __device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravSt
         if (k2 < inf) { ++s.sp; stack[s.sp] = c2; }
         if (k1 < inf) { ++s.sp; stack[s.sp] = c1; }
     }
+    return next;
+}
+__device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravState& s, int* stack)
+{
+    int next = node4_next(wn, s, stack);
     if (next < 0 && s.leaf >= 0) {           // first leaf: postpone it and keep descending
-        s.leaf = next; s.tri_cur = ~next;
+        s.leaf = next; s.tri_cur = GPT_LEAF_FIRST(~next);
         next = stack[s.sp]; --s.sp;
     }
     s.node = next;
@@ -189,7 +202,7 @@ __device__ __forceinline__ void tri_step(const float4* __restrict__ tris, TravSt
     if (t > 0.0f && t < s.t) { s.t = t; s.tri = ti; }        // :428, strict: first visited wins ties
     if (__float_as_int(c.w) == 0) {                          // last triangle of the leaf (no triangle follows)
         s.leaf = s.node;                                     // :440 another leaf was reached meanwhile?
-        if (s.node < 0) { s.tri_cur = ~s.node; s.node = stack[s.sp]; --s.sp; }
+        if (s.node < 0) { s.tri_cur = GPT_LEAF_FIRST(~s.node); s.node = stack[s.sp]; --s.sp; }
     } else {
         s.tri_cur = ti + 1;
     }
@@ -224,7 +237,7 @@ __device__ __forceinline__ void leaf_step_culled(const float4* __restrict__ tris
         first += k;
     }
     s.leaf = s.node;                                         // :440 another leaf was reached meanwhile?
-    if (s.node < 0) { s.tri_cur = ~s.node; s.node = stack[s.sp]; --s.sp; }
+    if (s.node < 0) { s.tri_cur = GPT_LEAF_FIRST(~s.node); s.node = stack[s.sp]; --s.sp; }
 }
 
 __device__ __forceinline__ TriHit traverse_bvh(const float4* __restrict__ nodes, const float4* __restrict__ tris,
@@ -264,6 +277,7 @@ __device__ __forceinline__ TriHit traverse_bvh4(const float4* __restrict__ wnode
 }
 
 // Sphere::intersect, CommomStructs.hpp:23-31; s = 11 floats (posRad, emi, col, mat)
+template <bool FAST = false>
 __device__ __forceinline__ float sphere_test(const float* s, const f3 o, const f3 d)
 {
     const f3 op = sub3(mk3(s[0], s[1], s[2]), o);
@@ -271,7 +285,7 @@ __device__ __forceinline__ float sphere_test(const float* s, const f3 o, const f
     const float disc = fmaf(s[3], s[3], fmaf(b, b, -dot3(op, op)));      // contraction as in the reference's SASS
     // branch-free: the warp pays for the square root whenever any lane needs it, so every lane may as well
     // take it; the selected values are the same as in the early-out form
-    const float sq = sqrtf(fmaxf(disc, 0.0f));
+    const float sq = sqrt_t<FAST>(fmaxf(disc, 0.0f));
     const float t0 = b - sq, t1 = b + sq;
     const float t = t0 > 0.01f ? t0 : (t1 > 0.01f ? t1 : 0.0f);
     return disc < 0.0f ? 0.0f : t;
@@ -294,6 +308,7 @@ __device__ __forceinline__ float box_test(const float* bx, const f3 o, const f3 
 struct SceneHit { float t; int geom; int prim; };   // prim = packed tri / sphere / box index
 
 // sphere sweep (cudaUtils.h:221-236) + boxes on top of a finished BVH result
+template <bool FAST = false>
 __device__ __forceinline__ SceneHit finish_scene_hit(const DevScene& sc, const float* s_spheres, const float* s_boxes,
                                                      const float tri_t, const int tri, const f3 o, const f3 d)
 {
@@ -304,7 +319,7 @@ __device__ __forceinline__ SceneHit finish_scene_hit(const DevScene& sc, const f
     constexpr int sphere_unroll = SPHERE_UNROLL;
 #pragma unroll sphere_unroll
     for (int i = 0; i < sc.n_spheres; ++i) {
-        const float t = sphere_test(s_spheres + 11 * i, o, d);
+        const float t = sphere_test<FAST>(s_spheres + 11 * i, o, d);
         if (t != 0.0f && t < h.t && t > 0.01f) { h.t = t; h.geom = GEO_SPHERE; h.prim = i; }
     }
     for (int i = 0; i < sc.n_boxes; ++i) {

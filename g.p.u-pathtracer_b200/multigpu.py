@@ -53,7 +53,9 @@ class PeerFrames:
     library-owned, IPC-exported frame buffer; the root reads all peers' buffers over NVLink inside ONE kernel that
     sums the ranks in rank order, adds the frame into the running sum and resolves it (gpt_reduce_resolve).  The only
     collective left per frame is a one-element all_reduce used as a stream-ordered barrier ("the peers' renders are
-    done"); double buffering makes the next frame's clear safe while the root may still be reading.
+    done"); double buffering makes the next frame's clear safe while the root may still be reading.  With more than one
+    rank the root runs that kernel on a SIDE stream behind an event, so its own next render overlaps the
+    reduce; read the outputs after wait_reduced().
 
     ctx: gpt_b200.Context; dist: an initialised torch.distributed (NCCL) or None for a single rank."""
 
@@ -64,6 +66,8 @@ class PeerFrames:
         self.rank = dist.get_rank() if dist is not None else 0
         self.width, self.height = int(width), int(height)
         self.frame_index = 0
+        self._side = None                  # root: the stream the fused reduce runs on, so that the next frame's render overlaps it
+        self._reduced = [None, None]       # root: event per frame buffer, recorded behind its reduce
         handle = ctx.frame_alloc(width, height, 2)
         self._flag = torch.zeros(1, dtype=torch.int32, device=device)
         if self.world > 1:
@@ -96,10 +100,35 @@ class PeerFrames:
             if cnt:
                 render_fn(self.ctx.frame_ptr(buf), frame_begin + off, cnt)
             if self.world > 1:
+                # The root's reduce of the PREVIOUS frame runs on the side stream; the peers clear that frame's buffer again once
+                # they are past THIS barrier, so the root must not enter it before that reduce has finished.  Issued here -- behind
+                # this frame's render -- the wait costs nothing unless the reduce is slower than a render.
+                if self.rank == self.root and self._reduced[buf ^ 1] is not None:
+                    stream.wait_event(self._reduced[buf ^ 1])
                 self.dist.all_reduce(self._flag)               # stream-ordered barrier: every rank's render precedes it
             if self.rank == self.root:
-                self.ctx.reduce_resolve(buf, total_accum, out_rgba8, out_rgb_f32, raw)
+                if self.world > 1:
+                    if self._side is None:
+                        self._side = torch.cuda.Stream()
+                    ready = torch.cuda.Event()
+                    ready.record(stream)
+                    self._side.wait_event(ready)
+                    self.ctx.reduce_resolve(buf, total_accum, out_rgba8, out_rgb_f32, self._side.cuda_stream)
+                    done = torch.cuda.Event()
+                    done.record(self._side)
+                    self._reduced[buf] = done
+                else:
+                    self.ctx.reduce_resolve(buf, total_accum, out_rgba8, out_rgb_f32, raw)
         return off, cnt
+
+    def wait_reduced(self, stream=None):
+        """Root: make `stream` (default: torch's current stream) wait for the reduces issued so far -- call before reading
+        total_accum / out_rgba8 / out_rgb_f32 on it.  A no-op for a single rank (the reduce ran on the caller's stream)."""
+        import torch
+        stream = stream if stream is not None else torch.cuda.current_stream()
+        for ev in self._reduced:
+            if ev is not None:
+                stream.wait_event(ev)
 
     def close(self):
         if self.world > 1:

@@ -124,6 +124,11 @@ enum {
     GPT_FLAG_BINARY_BVH = 1u << 6,   /* always the binary tree */
     GPT_FLAG_WAVEFRONT  = 1u << 7,   /* always the wavefront pipeline, also for small calls */
     GPT_FLAG_BUILD_LBVH = 1u << 8,   /* gpt_build_bvh: plain Morton radix tree instead of the (default) PLOC clustering */
+    GPT_FLAG_FAST       = 1u << 10,  /* OPT-IN fast shading arithmetic, held to north_star's statistical tolerance (1024-spp image against
+                                      * the reference's GPU kernel: per-pixel z-scores, box-filtered RMSE <= 1e-3) instead of bit-exactness
+                                      * with the oracle: rsqrt normalisation, hardware sin/cos/pow/reciprocal (MUFU) in the shade kernel.
+                                      * Nearest hits -- t, face index, the primary-hit map -- are unchanged (the traversal is not touched).
+                                      * Off by default: gpt_launch / gpt_render stay bit-exact unless the caller sets it. */
     GPT_FLAG_NO_TRIAL   = 1u << 9    /* never run the timed per-scene trial (gpt_trial_info): no render call then synchronises, so
                                       * calls are strictly asynchronous and can be captured into a CUDA graph; the size defaults
                                       * decide tree and ray order (also: GPT_NO_TRIAL=1 in the environment) */
@@ -276,6 +281,12 @@ GPT_API int gpt_reorder_info(gpt_ctx* ctx, int* state, double* ns_per_ray_path_o
  * [2] the faster tree with rays re-ordered; 0 = not measured (candidate forced, closed, or not reached yet). */
 GPT_API int gpt_trial_info(gpt_ctx* ctx, int* pending, double ns_per_ray[3]);
 GPT_API int gpt_get_kernel_times(gpt_ctx* ctx, gpt_kernel_times* out);  /* synchronises; see GPT_FLAG_TIME_KERNELS */
+/* Peaks of THIS device measured by micro-benchmarks (about 0.2 s, needs 2 GiB of free device memory; synchronises): the
+ * denominators bench.py's roofline fractions are stated against.  gather_*: GB/s of random 64-byte fetches (4 x LDG.128, the shape
+ * of one BVH node fetch) from a working set resident in L1 (64 KiB) / in L2 (16 MiB) / only in HBM (2 GiB), issued from the extend
+ * kernel's launch shape; warp_inst_per_s: warp instructions issued per second with all four schedulers of every SM busy. */
+typedef struct { double gather_l1_gbs, gather_l2_gbs, gather_hbm_gbs, warp_inst_per_s; } gpt_peaks;
+GPT_API int gpt_measure_peaks(gpt_ctx* ctx, gpt_peaks* out);
 
 /* ---- host-side helpers mirroring the reference's scene setup (no GPU needed) ---- */
 GPT_API uint64_t gpt_hash64(uint64_t key);                                   /* uf::hash, utilfun.cpp:380-389 */

@@ -67,8 +67,9 @@ def run(name, v, f, W, H, spp_total, mat, per_gpu=16):
         e0.record(stream)
         frames = 0
         for s in range(0, spp_total, per_frame):
-            peer.frame(render_ptr, s, min(per_frame, spp_total - s), total, rgba, None, stream.cuda_stream)
+            peer.frame(render_ptr, s, min(per_frame, spp_total - s), total, rgba, None, stream)
             if rank == 0:
+                peer.wait_reduced(stream)          # the reduce runs on the root's side stream
                 host.copy_(rgba, non_blocking=True)
             frames += 1
         e1.record(stream)
