@@ -599,7 +599,7 @@ def run_ours(args):
     if world == 1:
         def e2e_step(i):
             flush.zero_()
-            ctx.render_frame_host(info, args.seed, i * SPP, SPP, host_rgba, None)     # gpt_render_frame_host: host buffers
+            ctx.render_frame_host(info, args.seed, i * FRAME_SPP, FRAME_SPP, host_rgba, None)     # gpt_render_frame_host: host buffers
         for i in range(2):
             e2e_step(i)
         sync_all()

@@ -110,7 +110,7 @@ static void free_wave(gpt_ctx* c)
     WaveBuffers& w = c->wave;
     cudaFree(w.ray_o); cudaFree(w.ray_d); cudaFree(w.mask_z); cudaFree(w.accu); cudaFree(w.lsum); cudaFree(w.hit);
     cudaFree(w.queue[0]); cudaFree(w.queue[1]); cudaFree(w.counters);
-    cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp);
+    cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp); cudaFree(w.defer_q);
     w = WaveBuffers{}; c->wave_pixels = 0; c->wave_counters = 0;
 }
 
@@ -132,6 +132,8 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     CU(c, cudaMalloc(&w.hit, want * sizeof(int2)));
     CU(c, cudaMalloc(&w.queue[0], want * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], want * sizeof(uint32_t)));
     CU(c, cudaMalloc(&w.lsum, n_pix * sizeof(float4)));
+    w.defer_region = gptk_wave_defer_region(want);
+    CU(c, cudaMalloc(&w.defer_q, 4 * w.defer_region * sizeof(uint4)));
     CU(c, cudaMalloc(&w.counters, nc * sizeof(unsigned int)));
     CU(c, cudaMemset(w.counters, 0, nc * sizeof(unsigned int)));       // kept zero between calls by the pipeline's last kernel
     w.capacity = want;
@@ -327,8 +329,7 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "device re-pack", e);
     if (r.bad_layout) {
         char buf[160];
-        if (r.bad_layout == 6) snprintf(buf, sizeof(buf), "scene too large: more than %d triangle references after spatial splits", (1 << GPT_LEAF_FIRST_BITS) - 2);
-        else if (r.bad_layout == 5) snprintf(buf, sizeof(buf), "BVH has %d or more inner levels: deeper than the %d-entry traversal stack (cudaUtils.h:22)", GPT_STACK_SIZE, GPT_STACK_SIZE);
+        if (r.bad_layout == 5) snprintf(buf, sizeof(buf), "BVH has %d or more inner levels: deeper than the %d-entry traversal stack (cudaUtils.h:22)", GPT_STACK_SIZE, GPT_STACK_SIZE);
         else snprintf(buf, sizeof(buf), "malformed BVH arrays (code %d): not a CudaBVH BVHLayout_Compact tree", r.bad_layout);
         return fail(c, GPT_ERR_LAYOUT, buf);
     }

@@ -54,7 +54,7 @@ __global__ void k_write_packed(const float4* __restrict__ ref_nodes, int n_inner
         // "-0.0 hazard"); it points at the shared null triangle appended behind the last real one.
         int slot = ~c, k = 0;
         const int cnt = offsets[i + 1] - base;                  // triangles in this leaf (pass 1)
-        packed_child = (__float_as_uint(ref_tris[~c].x) == LEAF_TERM) ? ~GPT_LEAF_ENCODE(n_total, 1) : ~GPT_LEAF_ENCODE(base, cnt);
+        packed_child = (__float_as_uint(ref_tris[~c].x) == LEAF_TERM) ? ~n_total : ~base;
         while (__float_as_uint(ref_tris[slot].x) != LEAF_TERM) {
             const float4 v0 = ref_tris[slot], v1 = ref_tris[slot + 1], v2 = ref_tris[slot + 2];
             const int orig = ((size_t)slot < n_indices) ? ref_indices[slot] : -1;
@@ -121,7 +121,6 @@ cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float
         CK(cudaMemcpyAsync(&h_total, offsets + n_child, sizeof(int), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         if (h_bad) { out->bad_layout = h_bad; goto done; }
-        if ((long long)h_total + 1 >= (1ll << GPT_LEAF_FIRST_BITS)) { out->bad_layout = 6; goto done; }      // leaf pointers carry 27 bits of triangle index
         CK(cudaMalloc(&out->nodes, sizeof(float4) * 4 * (size_t)n_inner));
         CK(cudaMalloc(&out->tris, sizeof(float4) * 3 * ((size_t)h_total + 1)));
         k_write_packed<<<(n_child + 127) / 128, 128, 0, st>>>(ref_nodes, n_inner, ref_tris, ref_indices, n_indices, offsets, h_total, out->nodes, out->tris);

@@ -7,11 +7,7 @@
 //           [1] = c1.lo.x c1.hi.x c1.lo.y c1.hi.y     (:220)
 //           [2] = c0.lo.z c0.hi.z c1.lo.z c1.hi.z     (:221)
 //           [3] = int child0, child1, 0, 0            child >= 0: float4 index of an inner node
-//                                                     child <  0: ~(index of the leaf's first packed triangle | size field << 27)
-//                                                                 size field = min(triangles in the leaf, 16) - 1: the pooled
-//                                                                 leaf phase of k_wf_extend_pq lays (ray, triangle) pairs out
-//                                                                 without touching the triangles; 15 = "16 or more, read the
-//                                                                 real count from the first triangle" (GPT_LEAF_* below)
+//                                                     child <  0: ~(index of the leaf's first packed triangle)
 //   tris  : float4[3] per triangle reference (48 B), leaf after leaf, NO terminator slots
 //           [0] = v0.xyz , bits(original OBJ face index)      (the remap gpuTriIndices[hit], cudaUtils.h:452-456)
 //           [1] = (v1-v0).xyz , bits(slot address in the caller's array) (the reference's pre-remap hitIndex)
@@ -22,11 +18,6 @@
 #include "gpt_math.cuh"
 
 #define GPT_SENTINEL 0x76543210          // bottom-of-stack marker (same value as cudaUtils.h:21)
-// leaf pointer p < 0: x = ~p = first packed triangle (27 bits) | size field (4 bits)
-#define GPT_LEAF_FIRST_BITS 27
-#define GPT_LEAF_FIRST(x) ((x) & 0x07ffffff)
-#define GPT_LEAF_SIZE_FIELD(x) ((unsigned)(x) >> GPT_LEAF_FIRST_BITS)
-#define GPT_LEAF_ENCODE(first, cnt) ((first) | (((cnt) > 16 ? 16 : (cnt)) - 1) << GPT_LEAF_FIRST_BITS)
 #define GPT_STACK_SIZE 64                // cudaUtils.h:22; builder MaxDepth 64 (SplitBVHBuilder.hpp:15)
 #define GPT_W4_EMPTY 0x7fffffff           // unused child slot of a wide node (gpt_wide.cu)
 #define GPT_W4_STACK 96                  // traversal stack of the wide tree: <= 3 pushes per wide level

@@ -120,7 +120,7 @@ __device__ __forceinline__ void node_step(const float4* __restrict__ nodes, Trav
 {
     int next = node_next(nodes, s, stack);
     if (next < 0 && s.leaf >= 0) {           // first leaf: postpone it and keep descending (:362-369)
-        s.leaf = next; s.tri_cur = GPT_LEAF_FIRST(~next);
+        s.leaf = next; s.tri_cur = ~next;
         next = stack[s.sp]; --s.sp;
     }
     s.node = next;
@@ -184,7 +184,7 @@ __device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravSt
 {
     int next = node4_next(wn, s, stack);
     if (next < 0 && s.leaf >= 0) {           // first leaf: postpone it and keep descending
-        s.leaf = next; s.tri_cur = GPT_LEAF_FIRST(~next);
+        s.leaf = next; s.tri_cur = ~next;
         next = stack[s.sp]; --s.sp;
     }
     s.node = next;
@@ -202,7 +202,7 @@ __device__ __forceinline__ void tri_step(const float4* __restrict__ tris, TravSt
     if (t > 0.0f && t < s.t) { s.t = t; s.tri = ti; }        // :428, strict: first visited wins ties
     if (__float_as_int(c.w) == 0) {                          // last triangle of the leaf (no triangle follows)
         s.leaf = s.node;                                     // :440 another leaf was reached meanwhile?
-        if (s.node < 0) { s.tri_cur = GPT_LEAF_FIRST(~s.node); s.node = stack[s.sp]; --s.sp; }
+        if (s.node < 0) { s.tri_cur = ~s.node; s.node = stack[s.sp]; --s.sp; }
     } else {
         s.tri_cur = ti + 1;
     }
@@ -237,7 +237,7 @@ __device__ __forceinline__ void leaf_step_culled(const float4* __restrict__ tris
         first += k;
     }
     s.leaf = s.node;                                         // :440 another leaf was reached meanwhile?
-    if (s.node < 0) { s.tri_cur = GPT_LEAF_FIRST(~s.node); s.node = stack[s.sp]; --s.sp; }
+    if (s.node < 0) { s.tri_cur = ~s.node; s.node = stack[s.sp]; --s.sp; }
 }
 
 __device__ __forceinline__ TriHit traverse_bvh(const float4* __restrict__ nodes, const float4* __restrict__ tris,

@@ -72,8 +72,10 @@ __device__ __forceinline__ void primary_ray(const PrimaryGen& g, const uint32_t 
 
 // Persistent while-while traversal kernel (cudaUtils.h:256-460).  All lanes of a warp meet at the top of the outer loop once
 // per "descend to the next leaf + test that leaf" round; idle lanes are re-armed there from the bounce's queue with one
-// warp-aggregated atomic.  Two other schedules were built and measured slower in round 1 (voted single steps, pooled leaves:
-// profiles/r01_schedules.md #6, #13; the code is in the history).
+// warp-aggregated atomic.  Five other schedules were built, checked bit-identical and measured slower -- round 1: voted single
+// steps, pooled leaves per round (profiles/r01_schedules.md #6, #13); round 2: re-arming inside the node loop, and leaf phases
+// pooled over the warp with one or three postponed leaves per lane (profiles/r02_schedules.md #43-#46: 25-60 % slower although
+// a CPU replay of the warp schedule had predicted a gain) -- the code is in the history.
 #ifndef WF_WIDE_MIN_BLOCKS
 #define WF_WIDE_MIN_BLOCKS 10   // 48 registers, no spills; measured +2 % (2 M triangles) to +6 % (20 M) over 8 (profiles/r01_schedules.md #28)
 #endif
@@ -137,7 +139,7 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
                     tri_step(sc.tris, ts, stack, o, d, do_cull);
                     // a second leaf was postponed while this one waited: leave it for the next round (measured
                     // faster than draining it here: the round ends sooner for the rest of the warp)
-                    if (ts.leaf < 0 && ts.tri_cur == GPT_LEAF_FIRST(~ts.leaf)) break;
+                    if (ts.leaf < 0 && ts.tri_cur == ~ts.leaf) break;
                 }
             }
             if (trav_finished(ts)) {
@@ -148,258 +150,158 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
     }
 }
 
-// ---- pooled schedule (default from round 2; GPT_WF_EXTEND=ww selects the kernel above) -----------------------------------
-// Why: in k_wf_extend_ww every lane walks its OWN leaf, so a leaf phase costs max-leaf-size trips while the lanes without a leaf,
-// or with a short one, idle, and a lane that has met its second leaf idles through the rest of the node phase.  Measured (ncu,
-// round 1): 17 of 32 lanes per instruction on the 5 k-triangle bench scene, 8-11 on multi-million-triangle scenes; a CPU replay
-// of the warp schedule on real secondary rays (profiles/tools/warp_sim.cpp, profiles/r02_schedules.md) put the triangle phases
-// at 5-13 lanes and pointed at this schedule (-15 % warp instructions per ray on the bench scene, -30 % from 100 k triangles up):
-//   * a lane POSTPONES up to three leaves (+ the one it stalls on) and keeps descending: the node phase keeps its lanes;
-//   * finished lanes are re-armed from the queue INSIDE the node loop, as soon as `refill_min` of them idle;
-//   * the leaf phase starts when `hold_k` lanes hold leaves (or nobody can descend) and is POOLED: the warp's pending
-//     (ray, triangle) pairs are laid end to end in shared memory (leaf sizes ride in the leaf pointers, so nothing is fetched for
-//     that) and handed out 32 at a time, every lane testing one pair with the owner's ray read from shared memory.
-// Same nearest hit, same tie-breaking as the reference loop (cudaUtils.h:400-446): a lane's leaves are tested in the order it met
-// them and the winner is the lexicographic minimum of (t, position in that order) over the pairs with 0 < t < hitT -- what the
-// sequential strict `t < hitT` update yields.  Postponing more leaves only delays the shrinking of hitT: subtrees the reference
-// culls may be visited, but everything in them lies behind the final hit (their entry distance exceeded an earlier hitT).
-#ifndef WF_PQ_MIN_BLOCKS
-#define WF_PQ_MIN_BLOCKS 10
-#endif
-#ifndef WF_DEFAULT_SCHEDULE
-#define WF_DEFAULT_SCHEDULE 0     // 0 = ww (measured fastest so far), 3 / 1 = pooled with 3 / 1 postponed leaves, 2 = in-loop re-arming
-#endif
-#define WF_PQ_CAP 256            // pairs laid out per chunk and warp
-#define WF_PQ_MAXQ 3             // leaves a lane may postpone (the one it stalls on comes on top)
-struct PqShared {
-    float4 ray[WF_THREADS / 32][32][2];              // o.xyz + hitT, d.xyz + unused: the lane's ray, written when it is armed
-    int leafq[WF_THREADS / 32][WF_PQ_MAXQ + 1][32];  // postponed leaves (x = ~pointer) per lane, oldest first
-    unsigned item[WF_THREADS / 32][WF_PQ_CAP];       // owner lane << 27 | packed triangle
-    unsigned long long best[WF_THREADS / 32][32];    // bits(t) << 32 | position of the pair: min = nearest, first met
-};
-
-__device__ __forceinline__ int pq_leaf_count(const float4* __restrict__ tris, const int x)
-{
-    const int f = (int)GPT_LEAF_SIZE_FIELD(x);
-    return f < 15 ? f + 1 : __float_as_int(__ldg(tris + 3 * GPT_LEAF_FIRST(x) + 2).w) + 1;      // 16 or more: the first triangle knows
-}
-
-// MQ: leaves a lane postpones before it stalls (1 = the reference's single postponed leaf, cudaUtils.h:362-369).
-// POOLED: leaf phase pooled over the warp (above) or every lane walking its own leaves (the schedule of k_wf_extend_ww with the
-// re-arming moved into the node loop).
-template <bool CULL, bool WIDE, bool PRIMARY, int MQ, bool POOLED>
-__global__ void __launch_bounds__(WF_THREADS, WF_PQ_MIN_BLOCKS)
-k_wf_extend_pq(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
-               unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
-               int2* __restrict__ hit, const int refill_min, const int hold_k, const PrimaryGen gen)
-{
-    __shared__ PqShared sm;
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const unsigned n = PRIMARY ? gen.n_paths : *n_ptr;
-    float4* my_ray = sm.ray[warp][lane];
-    int* my_q = &sm.leafq[warp][0][lane];           // entry k at my_q[32 * k]
-    unsigned* items = sm.item[warp];
-    int stack[WIDE ? GPT_W4_STACK : GPT_STACK_SIZE];
-    TravState ts;
-    int nq = 0;
-    uint32_t pid = 0;
-    bool active = false, exhausted = false;
-    ts.node = GPT_SENTINEL; ts.leaf = 0; ts.sp = 0; ts.t = GPT_F32_MAX; ts.tri = -1; ts.tri_cur = 0;
-    ts.idx = ts.idy = ts.idz = 1.0f; ts.oodx = ts.oody = ts.oodz = 0.0f;
-
-    while (true) {
-        // ------------------------------------------------------------ node phase
-        while (true) {
-            const unsigned m_idle = __ballot_sync(GPT_FULL_MASK, !active);
-            if (m_idle != 0u && !exhausted && (__popc(m_idle) >= refill_min || m_idle == GPT_FULL_MASK)) {
-                unsigned base = 0;
-                const int leader = __ffs(m_idle) - 1;
-                if ((int)lane == leader) base = atomicAdd(fetch, (unsigned)__popc(m_idle));
-                base = __shfl_sync(GPT_FULL_MASK, base, leader);
-                if (base + (unsigned)__popc(m_idle) >= n) exhausted = true;
-                if (!active) {
-                    const unsigned j = base + (unsigned)__popc(m_idle & lt_mask);
-                    if (j < n) {
-                        f3 o, d;
-                        if (PRIMARY) {
-                            pid = j;
-                            PathState ps; primary_ray(gen, pid, ps);
-                            o = ps.o; d = ps.d;
-                        } else {
-                            pid = queue[j];
-                            const float4 ro = ray_o[pid], rd = ray_d[pid];
-                            o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
-                        }
-                        trav_init(ts, stack, o, d, true);
-                        my_ray[0] = make_float4(o.x, o.y, o.z, GPT_F32_MAX);
-                        my_ray[1] = make_float4(d.x, d.y, d.z, 0.0f);
-                        nq = 0;
-                        active = true;
-                    }
-                }
-            }
-            // the leaf met in the previous trip (or handed back by the stack) is postponed here: ONE copy of this code per trip
-            if (active && ts.node < 0 && nq < MQ) {
-                my_q[32 * nq] = ~ts.node; ++nq;
-                ts.node = stack[ts.sp]; --ts.sp;
-            }
-            const bool wn = active && trav_wants_node(ts);
-            const unsigned m_node = __ballot_sync(GPT_FULL_MASK, wn);
-            const unsigned m_hold = __ballot_sync(GPT_FULL_MASK, active && nq > 0);
-            if (m_node == 0u || __popc(m_hold) >= hold_k) break;
-            if (wn) {
-                ts.node = WIDE ? node4_next(sc.wnodes, ts, stack) : node_next(sc.nodes, ts, stack);      // < 0: a leaf, postponed next trip or stalled on
-                if (ts.node == GPT_SENTINEL && nq == 0) {
-                    hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
-                    active = false;
-                }
-            }
-        }
-        if (__ballot_sync(GPT_FULL_MASK, active) == 0u) break;      // nothing armed and nothing left to fetch
-        // ------------------------------------------------------------ leaf phase
-        if (active && ts.node < 0) {                                 // the leaf the lane stalled on joins the phase
-            my_q[32 * nq] = ~ts.node; ++nq;
-            ts.node = stack[ts.sp]; --ts.sp;
-        }
-        if (!active) nq = 0;
-        if (!POOLED) {
-            // every lane walks its own leaves, in the order it met them (cudaUtils.h:400-446)
-            const float4 ro = my_ray[0], rd = my_ray[1];
-            const f3 o = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
-            for (int k = 0; k < nq; ++k) {
-                const int x = my_q[32 * k];
-                int ti = GPT_LEAF_FIRST(x);
-                for (;;) {
-                    const float4 a = __ldg(sc.tris + 3 * ti), b = __ldg(sc.tris + 3 * ti + 1), c = __ldg(sc.tris + 3 * ti + 2);
-                    const float t = tri_test(a, b, c, o, d, CULL);
-                    if (t > 0.0f && t < ts.t) { ts.t = t; ts.tri = ti; }
-                    if (__float_as_int(c.w) == 0) break;
-                    ++ti;
-                }
-            }
-        } else {
-            int mine = 0;
-            for (int k = 0; k < nq; ++k) mine += pq_leaf_count(sc.tris, my_q[32 * k]);
-            int incl = mine;
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(GPT_FULL_MASK, incl, off); if ((int)lane >= off) incl += v; }
-            const int total = __shfl_sync(GPT_FULL_MASK, incl, 31);
-            const int excl = incl - mine;
-            if (active) my_ray[0].w = ts.t;              // hitT the pairs are filtered against
-            unsigned long long* best = sm.best[warp];
-            best[lane] = ~0ull;
-            for (int base = 0; base < total; base += WF_PQ_CAP) {
-                __syncwarp();
-                // lay this chunk's pairs out: each owner writes its own, in the order it met them
-                {
-                    int g = excl - base;                 // position of the lane's next pair inside the chunk
-                    for (int k = 0; k < nq; ++k) {
-                        const int x = my_q[32 * k];
-                        const int f = GPT_LEAF_FIRST(x), c = pq_leaf_count(sc.tris, x);
-#pragma unroll 1
-                        for (int i = 0; i < c; ++i, ++g) if ((unsigned)g < (unsigned)WF_PQ_CAP) items[g] = (lane << 27) | (unsigned)(f + i);
-                    }
-                }
-                __syncwarp();
-                const int n_chunk = total - base < WF_PQ_CAP ? total - base : WF_PQ_CAP;
-#pragma unroll 1
-                for (int j = (int)lane; j < n_chunk; j += 32) {
-                    const unsigned it = items[j];
-                    const unsigned own = it >> 27;
-                    const int ti = (int)(it & 0x07ffffffu);
-                    const float4 ro = sm.ray[warp][own][0], rd = sm.ray[warp][own][1];
-                    const float4 a = __ldg(sc.tris + 3 * ti), b = __ldg(sc.tris + 3 * ti + 1), c = __ldg(sc.tris + 3 * ti + 2);
-                    const float t = tri_test(a, b, c, mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z), CULL);
-                    // positive floats order like their bit patterns; ties go to the pair met first
-                    if (t > 0.0f && t < ro.w) atomicMin(best + own, ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(unsigned)j);
-                }
-                __syncwarp();
-                const unsigned long long k = best[lane];
-                if (k != ~0ull) {                        // strictly nearer than everything tested before: cudaUtils.h:428
-                    ts.t = __uint_as_float((unsigned)(k >> 32));
-                    ts.tri = (int)(items[(unsigned)(k & 0xffffffffull)] & 0x07ffffffu);
-                    my_ray[0].w = ts.t;
-                    best[lane] = ~0ull;
-                }
-            }
-        }
-        nq = 0;
-        if (active && ts.node == GPT_SENTINEL) {
-            hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
-            active = false;
-        }
-    }
-}
-
 // One thread per path alive at bounce `bounce`: the rest of the bounce-loop body (tracer.cu:98-296), the path's radiance when
 // it ends (tracer.cu:305 / :141, left in accu[pid]), and compaction of the survivors.
 // FIRST: bounce 0 -- every path of the wave is alive, the ray is the camera ray of the path id (recomputed, not loaded), the
 // mask is 1 (tracer.cu:68) and the accumulated colour starts at 0 (:69), so the slot is WRITTEN here, never read.
 // FAST: GPT_FLAG_FAST shading arithmetic (gpt_math.cuh) -- opt-in, statistically equal, not bit-equal.
+//
+// Minority materials (defer_min > 0).  The four material branches of tracer.cu:156-293 cost 60-300 instructions each and a warp
+// pays for every branch any of its lanes takes: with 3 % of the paths on a METAL sphere two warps in three run the METAL branch
+// for one or two lanes (ncu, round 1: 24 of 32 lanes per instruction on the bench scene against 28.6 on a one-material scene).
+// So a lane whose material is held by fewer than defer_min lanes of its warp -- and is not the warp's largest class -- does not
+// shade here: it appends (path, hit) to its material's deferred queue, and k_wf_shade_deferred shades those queues afterwards,
+// one material per CTA row, in dense warps.  Same arithmetic per path, same samples: images are bit-identical; only the order
+// of the next bounce's queue changes.
+struct ShadeIo {
+    const uint32_t* queue_in; unsigned int* counters; uint32_t* queue_out;
+    float4* ray_o; float4* ray_d; const int2* hit; float* mask_z; float4* accu;
+    uint4* defer_q; unsigned int* n_defer;      // 4 regions of defer_cap entries / 4 counters of this bounce; nullptr = no deferral
+    unsigned defer_cap;
+};
+
+template <bool FIRST>
+__device__ __forceinline__ void shade_load_path(const PrimaryGen& gen, const ShadeIo& io, const uint32_t pid, PathState& ps)
+{
+    if (FIRST) primary_ray(gen, pid, ps);
+    else {
+        const float4 ro = io.ray_o[pid], rd = io.ray_d[pid];
+        ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
+        ps.mask = mk3(ro.w, rd.w, io.mask_z[pid]);
+    }
+    ps.accu = mk3(0.0f, 0.0f, 0.0f);      // accu stays in memory (shade_bounce, accu_slot)
+}
+
+// shading of one path + the survivor's state; returns whether it goes on to the next bounce
+template <bool FIRST, bool FAST>
+__device__ __forceinline__ bool shade_finish_path(const DevScene& sc, const PrimaryGen& gen, const ShadeIo& io, const float* s_spheres, const float* s_boxes,
+                                                  const SceneHit h, const uint32_t pid, const uint32_t bounce, const bool last_bounce, PathState& ps)
+{
+    const uint32_t n_wave = (uint32_t)gen.n_wave;
+    const uint32_t s_local = pid / n_wave;
+    // accu[pid] is touched inside only on a miss or an emitting hit (always written at bounce 0); when the path is over its
+    // radiance (tracer.cu:305, or bkColor on a miss :141) stays there until the wave's samples are summed per pixel
+    const bool cont = shade_bounce<FIRST, FAST>(sc, gen.p, s_spheres, s_boxes, h, (uint32_t)gen.pix0 + (pid - s_local * n_wave), gen.sample0 + s_local, bounce, ps, io.accu + pid);
+    const bool survive = cont && !last_bounce;
+    if (survive) {
+        io.ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x);
+        io.ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y);
+        io.mask_z[pid] = ps.mask.z;
+    }
+    return survive;
+}
+
+// survivors of a warp -> the next bounce's queue: one atomic per warp
+__device__ __forceinline__ void shade_compact(const bool survive, const uint32_t pid, unsigned int* n_out, uint32_t* queue_out, const unsigned lane)
+{
+    const unsigned m = __ballot_sync(GPT_FULL_MASK, survive);
+    if (m) {
+        unsigned base = 0;
+        const int leader = __ffs(m) - 1;
+        if ((int)lane == leader) base = atomicAdd(n_out, (unsigned)__popc(m));
+        base = __shfl_sync(GPT_FULL_MASK, base, leader);
+        if (survive) queue_out[base + (unsigned)__popc(m & ((1u << lane) - 1u))] = pid;
+    }
+}
+
 template <bool FIRST, bool FAST>
 __global__ void __launch_bounds__(256, SHADE_MIN_BLOCKS)
-k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce,
-           const uint32_t* __restrict__ queue_in, unsigned int* __restrict__ counters,
-           uint32_t* __restrict__ queue_out, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
-           const int2* __restrict__ hit, float* __restrict__ mask_z, float4* __restrict__ accu,
+k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const ShadeIo io, const int defer_min,
            unsigned long long* __restrict__ stats)
 {
     __shared__ SmemPrims sm;
     const float* s_spheres; const float* s_boxes;
     stage_prims(sc, sm, s_spheres, s_boxes);
     const RenderParams& p = gen.p;
-    const unsigned n = FIRST ? gen.n_paths : counters[bounce];
-    unsigned int* n_out = counters + bounce + 1;
+    const unsigned n = FIRST ? gen.n_paths : io.counters[bounce];
+    unsigned int* n_out = io.counters + bounce + 1;
     const unsigned lane = threadIdx.x & 31u;
     const bool has_mesh = sc.n_nodes > 0;
     const bool last_bounce = bounce + 1u >= p.depth;
-    const uint32_t n_wave = (uint32_t)gen.n_wave, pix0 = (uint32_t)gen.pix0;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         atomicAdd(&stats[0], (unsigned long long)n);
         if (FIRST) atomicAdd(&stats[1], (unsigned long long)n);
         if ((p.flags & RP_COUNT_BOUNCES) && bounce < 16) atomicAdd(&stats[2 + bounce], (unsigned long long)n);
     }
-    // whole warps iterate together so the compaction ballot below is warp-uniform
+    // whole warps iterate together so the ballots below are warp-uniform
+    const unsigned n_round = (n + 31u) & ~31u;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+        bool survive = false, valid = i < n;
+        uint32_t pid = 0;
+        PathState ps;
+        SceneHit h; h.t = GPT_F32_MAX; h.geom = GEO_NONE; h.prim = -1;
+        if (valid) {
+            pid = FIRST ? i : io.queue_in[i];
+            shade_load_path<FIRST>(gen, io, pid, ps);
+            float tri_t = GPT_F32_MAX; int tri = -1;
+            if (has_mesh) { const int2 hh = io.hit[pid]; tri_t = __int_as_float(hh.x); tri = hh.y; }
+            h = finish_scene_hit<FAST>(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
+        }
+        if (defer_min > 0) {
+            const int mat = valid ? hit_material(sc, p, s_spheres, s_boxes, h) : -1;
+            const unsigned m0 = __ballot_sync(GPT_FULL_MASK, mat == 0), m1 = __ballot_sync(GPT_FULL_MASK, mat == 1);
+            const unsigned m2 = __ballot_sync(GPT_FULL_MASK, mat == 2), m3 = __ballot_sync(GPT_FULL_MASK, mat == 3);
+            const int c0 = __popc(m0), c1 = __popc(m1), c2 = __popc(m2), c3 = __popc(m3);
+            const int c_max = max(max(c0, c1), max(c2, c3));
+            const unsigned m_mine = mat == 0 ? m0 : mat == 1 ? m1 : mat == 2 ? m2 : m3;
+            const int c_mine = __popc(m_mine);
+            if (mat >= 0 && c_mine < defer_min && c_mine < c_max) {
+                // one atomic per (warp, material): the lowest lane of the class reserves the run
+                unsigned base = 0;
+                const int leader = __ffs(m_mine) - 1;
+                if ((int)lane == leader) base = atomicAdd(io.n_defer + mat, (unsigned)c_mine);
+                base = __shfl_sync(m_mine, base, leader);
+                const unsigned slot = base + (unsigned)__popc(m_mine & ((1u << lane) - 1u));
+                if (slot < io.defer_cap) {
+                    io.defer_q[(size_t)mat * io.defer_cap + slot] = make_uint4(pid, __float_as_uint(h.t), (unsigned)h.geom, (unsigned)h.prim);
+                    valid = false;               // shaded later, in a dense warp
+                }                                // (a full region cannot happen by construction; if it did the path is shaded here)
+            }
+        }
+        if (valid) survive = shade_finish_path<FIRST, FAST>(sc, gen, io, s_spheres, s_boxes, h, pid, bounce, last_bounce, ps);
+        shade_compact(survive, pid, n_out, io.queue_out, lane);
+    }
+}
+
+// The deferred queues of k_wf_shade: blockIdx.y = material, so a warp shades ONE material.
+template <bool FIRST, bool FAST>
+__global__ void __launch_bounds__(256, SHADE_MIN_BLOCKS)
+k_wf_shade_deferred(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const ShadeIo io)
+{
+    const unsigned mat = blockIdx.y;
+    unsigned n = io.n_defer[mat];
+    if (n > io.defer_cap) n = io.defer_cap;
+    if (blockIdx.x * blockDim.x >= ((n + 31u) & ~31u)) return;      // uniform per CTA: nothing for it
+    __shared__ SmemPrims sm;
+    const float* s_spheres; const float* s_boxes;
+    stage_prims(sc, sm, s_spheres, s_boxes);
+    unsigned int* n_out = io.counters + bounce + 1;
+    const unsigned lane = threadIdx.x & 31u;
+    const bool last_bounce = bounce + 1u >= gen.p.depth;
+    const uint4* q = io.defer_q + (size_t)mat * io.defer_cap;
     const unsigned n_round = (n + 31u) & ~31u;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
         bool survive = false;
         uint32_t pid = 0;
         if (i < n) {
+            const uint4 e = q[i];
+            pid = e.x;
             PathState ps;
-            if (FIRST) {
-                pid = i;
-                primary_ray(gen, pid, ps);
-            } else {
-                pid = queue_in[i];
-                const float4 ro = ray_o[pid], rd = ray_d[pid];
-                ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
-                ps.mask = mk3(ro.w, rd.w, mask_z[pid]);
-            }
-            ps.accu = mk3(0.0f, 0.0f, 0.0f);      // accu stays in memory (shade_bounce, accu_slot)
-            float tri_t = GPT_F32_MAX; int tri = -1;
-            if (has_mesh) { const int2 h = hit[pid]; tri_t = __int_as_float(h.x); tri = h.y; }
-            const SceneHit h = finish_scene_hit<FAST>(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
-            const uint32_t s_local = pid / n_wave;
-            // accu[pid] is touched inside only on a miss or an emitting hit (always written at bounce 0); when the path is over its
-            // radiance (tracer.cu:305, or bkColor on a miss :141) stays there until the wave's samples are summed per pixel
-            const bool cont = shade_bounce<FIRST, FAST>(sc, p, s_spheres, s_boxes, h, pix0 + (pid - s_local * n_wave), gen.sample0 + s_local, bounce, ps, accu + pid);
-            survive = cont && !last_bounce;
-            if (survive) {
-                ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x);
-                ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y);
-                mask_z[pid] = ps.mask.z;
-            }
+            shade_load_path<FIRST>(gen, io, pid, ps);
+            SceneHit h; h.t = __uint_as_float(e.y); h.geom = (int)e.z; h.prim = (int)e.w;
+            survive = shade_finish_path<FIRST, FAST>(sc, gen, io, s_spheres, s_boxes, h, pid, bounce, last_bounce, ps);
         }
-        // ---- compaction: one atomic per warp ----
-        const unsigned m = __ballot_sync(GPT_FULL_MASK, survive);
-        if (m) {
-            unsigned base = 0;
-            const int leader = __ffs(m) - 1;
-            if ((int)lane == leader) base = atomicAdd(n_out, (unsigned)__popc(m));
-            base = __shfl_sync(GPT_FULL_MASK, base, leader);
-            if (survive) queue_out[base + (unsigned)__popc(m & ((1u << lane) - 1u))] = pid;
-        }
+        shade_compact(survive, pid, n_out, io.queue_out, lane);
     }
 }
 
@@ -471,7 +373,9 @@ static int wf_knob(const char* name, int dflt)
     return v < 1 ? 1 : (v > 32 ? 32 : v);
 }
 
-size_t gptk_wave_counter_count(unsigned int depth) { return 2 * ((size_t)depth + 1); }
+// [0, depth]: paths alive per bounce; [depth+1, 2depth+1]: extend fetch cursors; then 4 deferred-queue counters per bounce
+size_t gptk_wave_counter_count(unsigned int depth) { return 6 * ((size_t)depth + 1); }
+size_t gptk_wave_defer_region(size_t capacity) { return capacity / 32 * 6 + 4096; }      // a class is deferred only below 6 lanes of 32
 
 // ---- optional ray reordering (GPT_WF_SORT): secondary rays are incoherent; sorting the queue by a key made of the
 // origin's cell (7 bits per axis of the mesh bounds, Morton order) and the direction's octant puts rays that walk the
@@ -537,13 +441,6 @@ void gptk_wave_launch_cfg(WaveLaunchCfg* cfg, int sm_count)
     cfg->sm_count = sm_count;
     cfg->ext_grid = sm_count * per_sm((const void*)k_wf_extend_ww<true, false, false>, WF_THREADS, 1);
     cfg->wide_grid = sm_count * per_sm((const void*)k_wf_extend_ww<true, true, false>, WF_THREADS, 1);
-    // extend schedule (GPT_WF_EXTEND): ww = the plain while-while loop (k_wf_extend_ww); p3 / p1 = pooled leaf phases with three /
-    // one postponed leaves per lane; r1 = in-loop re-arming with per-lane leaf phases (k_wf_extend_pq)
-    { const char* x = getenv("GPT_WF_EXTEND"); cfg->pooled = !x ? WF_DEFAULT_SCHEDULE : !strcmp(x, "p3") ? 3 : !strcmp(x, "p1") ? 1 : !strcmp(x, "r1") ? 2 : 0; }
-    cfg->pq_grid = sm_count * per_sm(cfg->pooled == 3 ? (const void*)k_wf_extend_pq<true, false, false, 3, true> : cfg->pooled == 1 ? (const void*)k_wf_extend_pq<true, false, false, 1, true> : (const void*)k_wf_extend_pq<true, false, false, 1, false>, WF_THREADS, 1);
-    cfg->pq_wide_grid = sm_count * per_sm(cfg->pooled == 3 ? (const void*)k_wf_extend_pq<true, true, false, 3, true> : cfg->pooled == 1 ? (const void*)k_wf_extend_pq<true, true, false, 1, true> : (const void*)k_wf_extend_pq<true, true, false, 1, false>, WF_THREADS, 1);
-    { const char* h = getenv("GPT_WF_HOLD_K"); cfg->hold_k_env = (h && atoi(h) > 0) ? wf_knob("GPT_WF_HOLD_K", 20) : 0; }      // 0 / unset: by scene size
-    cfg->pq_refill_min = wf_knob("GPT_WF_PQ_REFILL_MIN", 4);
     // shade grid: whole waves of resident CTAs (occupancy of the kernel as built x GPT_SHADE_WAVES), so no partial last wave
     const char* e = getenv("GPT_SHADE_WAVES");
     const int waves = e ? atoi(e) : 16;      // measured 1 / 2 / 4 / 8 / 16 / 32 / 64 / one trip per thread: 11.46 / 11.27 / 11.0 / 10.82 / 10.75 / 10.87 / 11.09 / 11.92 ms
@@ -551,6 +448,7 @@ void gptk_wave_launch_cfg(WaveLaunchCfg* cfg, int sm_count)
     const int m = wf_knob("GPT_WF_SORT", 3);
     cfg->sort_mode = m > 9 ? 9 : m;
     cfg->refill_min = wf_knob("GPT_WF_REFILL_MIN", 8);
+    { const char* x = getenv("GPT_SHADE_DEFER_MIN"); const int v = x ? atoi(x) : 6; cfg->defer_min = v < 0 ? 0 : (v > 6 ? 6 : v); }      // 0 = off; the regions hold up to 6 of 32
     cfg->node_k_env = getenv("GPT_WF_NODE_K") ? wf_knob("GPT_WF_NODE_K", WF_NODE_K) : 0;
     const char* w = getenv("GPT_WF_WAVE_PATHS");
     const long long v = w ? atoll(w) : 0;
@@ -562,20 +460,6 @@ template <bool PRIMARY>
 static void launch_extend(const DevScene& sc, const RenderParams& p, const WaveLaunchCfg& cfg, const uint32_t* q, unsigned int* n_ptr, unsigned int* fetch,
                           const WaveBuffers& wb, int node_k, const PrimaryGen& gen, cudaStream_t st)
 {
-    if (cfg.pooled) {
-        // leaves held in the warp that start a leaf phase: pooled phases want them full, per-lane phases the reference's few stragglers
-        const int hold_k = cfg.hold_k_env ? cfg.hold_k_env : (cfg.pooled == 3 ? 20 : 16);
-        const int grid = sc.wnodes ? cfg.pq_wide_grid : cfg.pq_grid;
-#define PQ_LAUNCH(C, Wd, M, P) k_wf_extend_pq<C, Wd, PRIMARY, M, P><<<grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.pq_refill_min, hold_k, gen)
-#define PQ_PICK(M, P) { if (sc.wnodes) { if (p.cull) PQ_LAUNCH(true, true, M, P); else PQ_LAUNCH(false, true, M, P); } \
-                        else { if (p.cull) PQ_LAUNCH(true, false, M, P); else PQ_LAUNCH(false, false, M, P); } }
-        if (cfg.pooled == 3) PQ_PICK(3, true)
-        else if (cfg.pooled == 1) PQ_PICK(1, true)
-        else PQ_PICK(1, false)
-#undef PQ_PICK
-#undef PQ_LAUNCH
-        return;
-    }
     if (sc.wnodes) {
         if (p.cull) k_wf_extend_ww<true, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
         else k_wf_extend_ww<false, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
@@ -644,14 +528,32 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                     *launches += 1;
                 }
                 if (kt) kt->tick(KT_SHADE, st);
+                ShadeIo io;
+                io.queue_in = q_in; io.counters = wb.counters; io.queue_out = wb.queue[(b + 1u) & 1u];
+                io.ray_o = wb.ray_o; io.ray_d = wb.ray_d; io.hit = wb.hit; io.mask_z = wb.mask_z; io.accu = wb.accu;
+                io.defer_q = wb.defer_q; io.n_defer = wb.counters + 2 * (p.depth + 1) + 4 * b; io.defer_cap = (unsigned)wb.defer_region;
+                // minority materials are shaded afterwards in dense warps (k_wf_shade): pays from a few hundred thousand paths per launch
+                const int defer_min = (wb.defer_q && n_paths >= ((size_t)256 << 10)) ? cfg.defer_min : 0;
                 if (p.flags & RP_FAST) {
-                    if (b == 0) k_wf_shade<true, true><<<sgrid, 256, 0, st>>>(sc, gen, b, nullptr, wb.counters, wb.queue[1], wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
-                    else k_wf_shade<false, true><<<sgrid, 256, 0, st>>>(sc, gen, b, q_in, wb.counters, wb.queue[(b + 1u) & 1u], wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
+                    if (b == 0) k_wf_shade<true, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, defer_min, stats);
+                    else k_wf_shade<false, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, defer_min, stats);
                 } else {
-                    if (b == 0) k_wf_shade<true, false><<<sgrid, 256, 0, st>>>(sc, gen, b, nullptr, wb.counters, wb.queue[1], wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
-                    else k_wf_shade<false, false><<<sgrid, 256, 0, st>>>(sc, gen, b, q_in, wb.counters, wb.queue[(b + 1u) & 1u], wb.ray_o, wb.ray_d, wb.hit, wb.mask_z, wb.accu, stats);
+                    if (b == 0) k_wf_shade<true, false><<<sgrid, 256, 0, st>>>(sc, gen, b, io, defer_min, stats);
+                    else k_wf_shade<false, false><<<sgrid, 256, 0, st>>>(sc, gen, b, io, defer_min, stats);
                 }
                 *launches += 1;
+                if (defer_min > 0) {
+                    int dg = (int)((wb.defer_region + 255) / 256); if (dg > cfg.shade_grid / 4) dg = cfg.shade_grid / 4; if (dg < 1) dg = 1;
+                    const dim3 dgrid((unsigned)dg, 4u);
+                    if (p.flags & RP_FAST) {
+                        if (b == 0) k_wf_shade_deferred<true, true><<<dgrid, 256, 0, st>>>(sc, gen, b, io);
+                        else k_wf_shade_deferred<false, true><<<dgrid, 256, 0, st>>>(sc, gen, b, io);
+                    } else {
+                        if (b == 0) k_wf_shade_deferred<true, false><<<dgrid, 256, 0, st>>>(sc, gen, b, io);
+                        else k_wf_shade_deferred<false, false><<<dgrid, 256, 0, st>>>(sc, gen, b, io);
+                    }
+                    *launches += 1;
+                }
             }
             if (!direct) {
                 if (kt) kt->tick(KT_COLLECT, st);
