@@ -110,7 +110,7 @@ static void free_wave(gpt_ctx* c)
     WaveBuffers& w = c->wave;
     cudaFree(w.ray_o); cudaFree(w.ray_d); cudaFree(w.mask_z); cudaFree(w.accu); cudaFree(w.lsum); cudaFree(w.hit);
     cudaFree(w.queue[0]); cudaFree(w.queue[1]); cudaFree(w.counters);
-    cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp); cudaFree(w.defer_q);
+    cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp);
     w = WaveBuffers{}; c->wave_pixels = 0; c->wave_counters = 0;
 }
 
@@ -132,8 +132,6 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     CU(c, cudaMalloc(&w.hit, want * sizeof(int2)));
     CU(c, cudaMalloc(&w.queue[0], want * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], want * sizeof(uint32_t)));
     CU(c, cudaMalloc(&w.lsum, n_pix * sizeof(float4)));
-    w.defer_region = gptk_wave_defer_region(want);
-    CU(c, cudaMalloc(&w.defer_q, 4 * w.defer_region * sizeof(uint4)));
     CU(c, cudaMalloc(&w.counters, nc * sizeof(unsigned int)));
     CU(c, cudaMemset(w.counters, 0, nc * sizeof(unsigned int)));       // kept zero between calls by the pipeline's last kernel
     w.capacity = want;

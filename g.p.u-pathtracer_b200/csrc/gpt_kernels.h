@@ -86,14 +86,11 @@ struct WaveBuffers {
     size_t capacity;            // paths the per-path arrays hold (lsum: one per pixel of the frame)
     // optional ray reordering before each secondary extend (GPT_WF_SORT): all nullptr = off
     uint32_t* sort_keys[2]; uint32_t* sort_vals; void* sort_tmp; size_t sort_tmp_bytes;
-    // deferred shading of minority materials (k_wf_shade / k_wf_shade_deferred): 4 regions of defer_region entries; nullptr = off
-    uint4* defer_q; size_t defer_region;
 };
-size_t gptk_wave_defer_region(size_t capacity);
 size_t gptk_wave_counter_count(unsigned int depth);
 size_t gptk_wave_sort_tmp_bytes(size_t capacity);
 // per-context launch configuration of the pipeline (grids from the kernels' occupancy on this device, environment knobs)
-struct WaveLaunchCfg { int ready, sm_count, ext_grid, wide_grid, shade_grid, sort_mode, refill_min, node_k_env, defer_min; size_t wave_cap_env; };
+struct WaveLaunchCfg { int ready, sm_count, ext_grid, wide_grid, shade_grid, sort_mode, refill_min, node_k_env; size_t wave_cap_env; };
 void gptk_wave_launch_cfg(WaveLaunchCfg* cfg, int sm_count);
 // wb.counters must be all zero on entry and are all zero again once the enqueued work has run
 cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, const WaveBuffers& wb, const WaveLaunchCfg& cfg,

@@ -52,24 +52,6 @@ __device__ __forceinline__ f3 box_normal(const float* bx, f3 p)
     return mk3(0, 0, 1);
 }
 
-// The Mat a hit will be shaded with (tracer.cu:121,134; per-face table: gpt_set_triangle_materials) -- the same lookups
-// shade_bounce makes, for the shade kernel's minority-material deferral; -1 for a miss.
-__device__ __forceinline__ int hit_material(const DevScene& sc, const RenderParams& p, const float* s_spheres, const float* s_boxes, const SceneHit h)
-{
-    if (h.geom == GEO_NONE) return -1;
-    if (h.geom == GEO_SPHERE) return __float_as_int(s_spheres[11 * h.prim + 10]) & 3;
-    if (h.geom == GEO_BOX) return __float_as_int(s_boxes[13 * h.prim + 12]) & 3;
-    int mat = p.tri_mat;
-    if (sc.n_faces) {
-        const int face = __float_as_int(__ldg(sc.tris + 3 * h.prim).w);
-        if ((unsigned)face < (unsigned)sc.n_faces) {
-            const int m = __ldg(sc.face_mat + face);
-            if ((unsigned)m < (unsigned)sc.n_tri_mats) mat = __float_as_int(__ldg(sc.tri_mats + 7 * (size_t)m + 6));
-        }
-    }
-    return mat & 3;      // shade_bounce treats everything that is not DIFF / SPEC / REFR as METAL; classes only steer scheduling
-}
-
 // One bounce of tracer.cu:112-296.  Returns false when the path ended on a miss (ps.accu then holds
 // the background colour, Q2); true when the path continues with the new ray in ps.
 // accu_slot != nullptr (wavefront pipeline): the accumulated colour lives in memory and ps.accu is not used.  It changes

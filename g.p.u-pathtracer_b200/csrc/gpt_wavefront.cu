@@ -155,19 +155,9 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
 // FIRST: bounce 0 -- every path of the wave is alive, the ray is the camera ray of the path id (recomputed, not loaded), the
 // mask is 1 (tracer.cu:68) and the accumulated colour starts at 0 (:69), so the slot is WRITTEN here, never read.
 // FAST: GPT_FLAG_FAST shading arithmetic (gpt_math.cuh) -- opt-in, statistically equal, not bit-equal.
-//
-// Minority materials (defer_min > 0).  The four material branches of tracer.cu:156-293 cost 60-300 instructions each and a warp
-// pays for every branch any of its lanes takes: with 3 % of the paths on a METAL sphere two warps in three run the METAL branch
-// for one or two lanes (ncu, round 1: 24 of 32 lanes per instruction on the bench scene against 28.6 on a one-material scene).
-// So a lane whose material is held by fewer than defer_min lanes of its warp -- and is not the warp's largest class -- does not
-// shade here: it appends (path, hit) to its material's deferred queue, and k_wf_shade_deferred shades those queues afterwards,
-// one material per CTA row, in dense warps.  Same arithmetic per path, same samples: images are bit-identical; only the order
-// of the next bounce's queue changes.
 struct ShadeIo {
     const uint32_t* queue_in; unsigned int* counters; uint32_t* queue_out;
     float4* ray_o; float4* ray_d; const int2* hit; float* mask_z; float4* accu;
-    uint4* defer_q; unsigned int* n_defer;      // 4 regions of defer_cap entries / 4 counters of this bounce; nullptr = no deferral
-    unsigned defer_cap;
 };
 
 template <bool FIRST>
@@ -216,7 +206,7 @@ __device__ __forceinline__ void shade_compact(const bool survive, const uint32_t
 
 template <bool FIRST, bool FAST>
 __global__ void __launch_bounds__(256, SHADE_MIN_BLOCKS)
-k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const ShadeIo io, const int defer_min,
+k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const ShadeIo io,
            unsigned long long* __restrict__ stats)
 {
     __shared__ SmemPrims sm;
@@ -247,60 +237,7 @@ k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const
             if (has_mesh) { const int2 hh = io.hit[pid]; tri_t = __int_as_float(hh.x); tri = hh.y; }
             h = finish_scene_hit<FAST>(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
         }
-        if (defer_min > 0) {
-            const int mat = valid ? hit_material(sc, p, s_spheres, s_boxes, h) : -1;
-            const unsigned m0 = __ballot_sync(GPT_FULL_MASK, mat == 0), m1 = __ballot_sync(GPT_FULL_MASK, mat == 1);
-            const unsigned m2 = __ballot_sync(GPT_FULL_MASK, mat == 2), m3 = __ballot_sync(GPT_FULL_MASK, mat == 3);
-            const int c0 = __popc(m0), c1 = __popc(m1), c2 = __popc(m2), c3 = __popc(m3);
-            const int c_max = max(max(c0, c1), max(c2, c3));
-            const unsigned m_mine = mat == 0 ? m0 : mat == 1 ? m1 : mat == 2 ? m2 : m3;
-            const int c_mine = __popc(m_mine);
-            if (mat >= 0 && c_mine < defer_min && c_mine < c_max) {
-                // one atomic per (warp, material): the lowest lane of the class reserves the run
-                unsigned base = 0;
-                const int leader = __ffs(m_mine) - 1;
-                if ((int)lane == leader) base = atomicAdd(io.n_defer + mat, (unsigned)c_mine);
-                base = __shfl_sync(m_mine, base, leader);
-                const unsigned slot = base + (unsigned)__popc(m_mine & ((1u << lane) - 1u));
-                if (slot < io.defer_cap) {
-                    io.defer_q[(size_t)mat * io.defer_cap + slot] = make_uint4(pid, __float_as_uint(h.t), (unsigned)h.geom, (unsigned)h.prim);
-                    valid = false;               // shaded later, in a dense warp
-                }                                // (a full region cannot happen by construction; if it did the path is shaded here)
-            }
-        }
         if (valid) survive = shade_finish_path<FIRST, FAST>(sc, gen, io, s_spheres, s_boxes, h, pid, bounce, last_bounce, ps);
-        shade_compact(survive, pid, n_out, io.queue_out, lane);
-    }
-}
-
-// The deferred queues of k_wf_shade: blockIdx.y = material, so a warp shades ONE material.
-template <bool FIRST, bool FAST>
-__global__ void __launch_bounds__(256, SHADE_MIN_BLOCKS)
-k_wf_shade_deferred(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const ShadeIo io)
-{
-    const unsigned mat = blockIdx.y;
-    unsigned n = io.n_defer[mat];
-    if (n > io.defer_cap) n = io.defer_cap;
-    if (blockIdx.x * blockDim.x >= ((n + 31u) & ~31u)) return;      // uniform per CTA: nothing for it
-    __shared__ SmemPrims sm;
-    const float* s_spheres; const float* s_boxes;
-    stage_prims(sc, sm, s_spheres, s_boxes);
-    unsigned int* n_out = io.counters + bounce + 1;
-    const unsigned lane = threadIdx.x & 31u;
-    const bool last_bounce = bounce + 1u >= gen.p.depth;
-    const uint4* q = io.defer_q + (size_t)mat * io.defer_cap;
-    const unsigned n_round = (n + 31u) & ~31u;
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
-        bool survive = false;
-        uint32_t pid = 0;
-        if (i < n) {
-            const uint4 e = q[i];
-            pid = e.x;
-            PathState ps;
-            shade_load_path<FIRST>(gen, io, pid, ps);
-            SceneHit h; h.t = __uint_as_float(e.y); h.geom = (int)e.z; h.prim = (int)e.w;
-            survive = shade_finish_path<FIRST, FAST>(sc, gen, io, s_spheres, s_boxes, h, pid, bounce, last_bounce, ps);
-        }
         shade_compact(survive, pid, n_out, io.queue_out, lane);
     }
 }
@@ -373,9 +310,7 @@ static int wf_knob(const char* name, int dflt)
     return v < 1 ? 1 : (v > 32 ? 32 : v);
 }
 
-// [0, depth]: paths alive per bounce; [depth+1, 2depth+1]: extend fetch cursors; then 4 deferred-queue counters per bounce
-size_t gptk_wave_counter_count(unsigned int depth) { return 6 * ((size_t)depth + 1); }
-size_t gptk_wave_defer_region(size_t capacity) { return capacity / 32 * 6 + 4096; }      // a class is deferred only below 6 lanes of 32
+size_t gptk_wave_counter_count(unsigned int depth) { return 2 * ((size_t)depth + 1); }
 
 // ---- optional ray reordering (GPT_WF_SORT): secondary rays are incoherent; sorting the queue by a key made of the
 // origin's cell (7 bits per axis of the mesh bounds, Morton order) and the direction's octant puts rays that walk the
@@ -448,7 +383,6 @@ void gptk_wave_launch_cfg(WaveLaunchCfg* cfg, int sm_count)
     const int m = wf_knob("GPT_WF_SORT", 3);
     cfg->sort_mode = m > 9 ? 9 : m;
     cfg->refill_min = wf_knob("GPT_WF_REFILL_MIN", 8);
-    { const char* x = getenv("GPT_SHADE_DEFER_MIN"); const int v = x ? atoi(x) : 6; cfg->defer_min = v < 0 ? 0 : (v > 6 ? 6 : v); }      // 0 = off; the regions hold up to 6 of 32
     cfg->node_k_env = getenv("GPT_WF_NODE_K") ? wf_knob("GPT_WF_NODE_K", WF_NODE_K) : 0;
     const char* w = getenv("GPT_WF_WAVE_PATHS");
     const long long v = w ? atoll(w) : 0;
@@ -531,29 +465,14 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                 ShadeIo io;
                 io.queue_in = q_in; io.counters = wb.counters; io.queue_out = wb.queue[(b + 1u) & 1u];
                 io.ray_o = wb.ray_o; io.ray_d = wb.ray_d; io.hit = wb.hit; io.mask_z = wb.mask_z; io.accu = wb.accu;
-                io.defer_q = wb.defer_q; io.n_defer = wb.counters + 2 * (p.depth + 1) + 4 * b; io.defer_cap = (unsigned)wb.defer_region;
-                // minority materials are shaded afterwards in dense warps (k_wf_shade): pays from a few hundred thousand paths per launch
-                const int defer_min = (wb.defer_q && n_paths >= ((size_t)256 << 10)) ? cfg.defer_min : 0;
                 if (p.flags & RP_FAST) {
-                    if (b == 0) k_wf_shade<true, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, defer_min, stats);
-                    else k_wf_shade<false, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, defer_min, stats);
+                    if (b == 0) k_wf_shade<true, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, stats);
+                    else k_wf_shade<false, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, stats);
                 } else {
-                    if (b == 0) k_wf_shade<true, false><<<sgrid, 256, 0, st>>>(sc, gen, b, io, defer_min, stats);
-                    else k_wf_shade<false, false><<<sgrid, 256, 0, st>>>(sc, gen, b, io, defer_min, stats);
+                    if (b == 0) k_wf_shade<true, false><<<sgrid, 256, 0, st>>>(sc, gen, b, io, stats);
+                    else k_wf_shade<false, false><<<sgrid, 256, 0, st>>>(sc, gen, b, io, stats);
                 }
                 *launches += 1;
-                if (defer_min > 0) {
-                    int dg = (int)((wb.defer_region + 255) / 256); if (dg > cfg.shade_grid / 4) dg = cfg.shade_grid / 4; if (dg < 1) dg = 1;
-                    const dim3 dgrid((unsigned)dg, 4u);
-                    if (p.flags & RP_FAST) {
-                        if (b == 0) k_wf_shade_deferred<true, true><<<dgrid, 256, 0, st>>>(sc, gen, b, io);
-                        else k_wf_shade_deferred<false, true><<<dgrid, 256, 0, st>>>(sc, gen, b, io);
-                    } else {
-                        if (b == 0) k_wf_shade_deferred<true, false><<<dgrid, 256, 0, st>>>(sc, gen, b, io);
-                        else k_wf_shade_deferred<false, false><<<dgrid, 256, 0, st>>>(sc, gen, b, io);
-                    }
-                    *launches += 1;
-                }
             }
             if (!direct) {
                 if (kt) kt->tick(KT_COLLECT, st);
