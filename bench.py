@@ -94,8 +94,12 @@ def bound_fractions(cls, rays, ms, peaks, hbm):
         ach = cls[key] * rays / s / scale
         return {"per_ray": cls[key], "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak}
     out["dram"] = frac("dram_bytes_per_ray", hbm, "GB/s", 1e9)
-    out["l2"] = frac("l2_bytes_per_ray", peaks.get("gather_l2_gbs"), "GB/s", 1e9)
-    out["l1"] = frac("l1_bytes_per_ray", peaks.get("gather_l1_gbs"), "GB/s", 1e9)
+    # ceilings = coalesced streaming out of that level; the random-64-byte-gather rates (the traversal's access shape) ride along
+    out["l2"] = frac("l2_bytes_per_ray", peaks.get("stream_l2_gbs"), "GB/s", 1e9)
+    out["l1"] = frac("l1_bytes_per_ray", peaks.get("stream_l1_gbs"), "GB/s", 1e9)
+    for k, g in (("l2", "gather_l2_gbs"), ("l1", "gather_l1_gbs")):
+        if out.get(k) and peaks.get(g):
+            out[k]["frac_of_random_gather_rate"] = out[k]["achieved"] / peaks[g]
     out["issue"] = frac("warp_inst_per_ray", peaks.get("warp_inst_per_s", 0) / 1e12, "T warp-inst/s", 1e12)
     fr = {k: out[k]["frac"] for k in ("dram", "l2", "l1", "issue") if out.get(k)}
     if fr:
@@ -678,8 +682,8 @@ def run_ours(args):
                                     "shade": bound_fractions(fcls.get("shade"), float(st.rays), shade_ms, live_peaks, hbm),
                                     "what": "per kernel class: committed ncu per-ray counters (profiles/r02_frame_counters.json: one frame of this workload, "
                                             "every launch) x live rays / live class time, against peaks measured in this run by gpt_measure_peaks: DRAM bytes vs "
-                                            "the HBM copy peak, L2 / L1 bytes vs random 64-byte gather bandwidth from an L2- / L1-resident working set, warp "
-                                            "instructions vs the measured issue rate; `binding` = the largest fraction"},
+                                            "the HBM copy peak, L2 / L1 bytes (lts__t_bytes / l1tex__t_bytes) vs coalesced streaming out of an L2- / L1-resident working set, "
+                                            "warp instructions vs the measured issue rate; `binding` = the largest fraction"},
                          "whole_pass": {"achieved": pass_achieved, "frac": pass_achieved / hbm, "bytes_per_ray": bpr, "ms_avg": pass_avg_ms,
                                         "what": "all kernels of one gpt_render pass (extend, shade, accumulate), algorithmic bytes incl. 44 B x spheres"},
                          "kernel_class_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]},

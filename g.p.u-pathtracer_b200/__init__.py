@@ -88,7 +88,8 @@ class BuiltBVH(C.Structure):  # gpt_built_bvh
 
 
 class Peaks(C.Structure):  # gpt_peaks
-    _fields_ = [("gather_l1_gbs", C.c_double), ("gather_l2_gbs", C.c_double), ("gather_hbm_gbs", C.c_double), ("warp_inst_per_s", C.c_double)]
+    _fields_ = [("gather_l1_gbs", C.c_double), ("gather_l2_gbs", C.c_double), ("gather_hbm_gbs", C.c_double), ("warp_inst_per_s", C.c_double),
+                ("stream_l1_gbs", C.c_double), ("stream_l2_gbs", C.c_double)]
 
 
 class KernelTimes(C.Structure):

@@ -800,7 +800,8 @@ int gpt_measure_peaks(gpt_ctx* c, gpt_peaks* out)
     if (!c || !out) return GPT_ERR_INVALID;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaDeviceSynchronize());
-    cudaError_t e = gptk_measure_peaks(c->sm_count, &out->gather_l1_gbs, &out->gather_l2_gbs, &out->gather_hbm_gbs, &out->warp_inst_per_s);
+    cudaError_t e = gptk_measure_peaks(c->sm_count, &out->gather_l1_gbs, &out->gather_l2_gbs, &out->gather_hbm_gbs, &out->warp_inst_per_s,
+                                       &out->stream_l1_gbs, &out->stream_l2_gbs);
     if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "gpt_measure_peaks", e);
     c->launches += 16;
     return GPT_OK;

@@ -69,7 +69,8 @@ cudaError_t gptk_build_lbvh(const float* verts, size_t n_verts, const int* tri, 
                             BuildResult* out, cudaStream_t st);
 
 // device peaks measured by micro-benchmarks (gpt_peaks.cu; diagnostics for bench.py's roofline)
-cudaError_t gptk_measure_peaks(int sm_count, double* l1_gbs, double* l2_gbs, double* hbm_gbs, double* warp_inst_per_s);
+cudaError_t gptk_measure_peaks(int sm_count, double* l1_gbs, double* l2_gbs, double* hbm_gbs, double* warp_inst_per_s,
+                               double* stream_l1_gbs, double* stream_l2_gbs);
 
 // 4-wide quantised BVH collapsed on the device from the packed binary nodes (gpt_wide.cu).
 // status: 0 ok, 1 non-finite / inverted box (not quantisable), 2 internal, 3 not a tree

@@ -23,6 +23,21 @@ k_peak_gather(const float4* __restrict__ buf, const unsigned mask, const int ite
     if (acc.x == 123.456f) sink[0] = acc;      // never true for the zeroed buffer: keeps the loads alive
 }
 
+// coalesced 16-byte loads sweeping a working set again and again: the hard ceiling of a cache level's bandwidth
+__global__ void __launch_bounds__(256)
+k_peak_stream(const float4* __restrict__ buf, const unsigned mask, const int iters, float4* __restrict__ sink)
+{
+    unsigned idx = blockIdx.x * 8191u * blockDim.x + threadIdx.x;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+    for (int i = 0; i < iters; ++i) {
+        const float4 a = __ldg(buf + (idx & mask));
+        acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+        idx += blockDim.x;
+    }
+    if (acc.x == 123.456f) sink[0] = acc;
+}
+
 __global__ void __launch_bounds__(128)
 k_peak_issue(const int iters, const float seed, float* __restrict__ sink)
 {
@@ -57,10 +72,12 @@ static cudaError_t time_kernel(cudaEvent_t e0, cudaEvent_t e1, float* best_ms, i
 
 struct GatherArg { const float4* buf; unsigned mask; int iters; int grid; float4* sink; };
 static void launch_gather(void* p) { GatherArg* a = (GatherArg*)p; k_peak_gather<<<a->grid, 128>>>(a->buf, a->mask, a->iters, a->sink); }
+static void launch_stream(void* p) { GatherArg* a = (GatherArg*)p; k_peak_stream<<<a->grid, 256>>>(a->buf, a->mask, a->iters, a->sink); }
 struct IssueArg { int iters; int grid; float* sink; };
 static void launch_issue(void* p) { IssueArg* a = (IssueArg*)p; k_peak_issue<<<a->grid, 128>>>(a->iters, 1.0f, a->sink); }
 
-cudaError_t gptk_measure_peaks(int sm_count, double* l1_gbs, double* l2_gbs, double* hbm_gbs, double* warp_inst_per_s)
+cudaError_t gptk_measure_peaks(int sm_count, double* l1_gbs, double* l2_gbs, double* hbm_gbs, double* warp_inst_per_s,
+                               double* stream_l1_gbs, double* stream_l2_gbs)
 {
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     float4* buf = nullptr; float4* sink = nullptr;
@@ -83,6 +100,13 @@ cudaError_t gptk_measure_peaks(int sm_count, double* l1_gbs, double* l2_gbs, dou
         g.mask = (unsigned)(big / 64 - 1); g.iters = 256;
         CK(time_kernel(e0, e1, &ms, 3, launch_gather, &g));
         *hbm_gbs = threads * g.iters * 64.0 / (ms * 1e-3) / 1e9;
+        // streaming ceilings: every CTA sweeps its own 32 KiB window (L1), all CTAs sweep the same 16 MiB (L2; L1 holds 0.2 % of it)
+        GatherArg s1 = {buf, (unsigned)((32u << 10) / 16 - 1), 8192, sm_count * 8, sink};
+        CK(time_kernel(e0, e1, &ms, 3, launch_stream, &s1));
+        *stream_l1_gbs = (double)s1.grid * 256.0 * s1.iters * 16.0 / (ms * 1e-3) / 1e9;
+        GatherArg s2 = {buf, (unsigned)(((size_t)16 << 20) / 16 - 1), 2048, sm_count * 8, sink};
+        CK(time_kernel(e0, e1, &ms, 3, launch_stream, &s2));
+        *stream_l2_gbs = (double)s2.grid * 256.0 * s2.iters * 16.0 / (ms * 1e-3) / 1e9;
         IssueArg ia = {2048, sm_count * 16, reinterpret_cast<float*>(sink)};
         CK(time_kernel(e0, e1, &ms, 3, launch_issue, &ia));
         *warp_inst_per_s = ((double)ia.grid * 4.0) * ((double)ia.iters * 64.0) / (ms * 1e-3);     // 4 warps per CTA, 64 FFMA per trip

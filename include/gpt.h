@@ -284,8 +284,9 @@ GPT_API int gpt_get_kernel_times(gpt_ctx* ctx, gpt_kernel_times* out);  /* synch
 /* Peaks of THIS device measured by micro-benchmarks (about 0.2 s, needs 2 GiB of free device memory; synchronises): the
  * denominators bench.py's roofline fractions are stated against.  gather_*: GB/s of random 64-byte fetches (4 x LDG.128, the shape
  * of one BVH node fetch) from a working set resident in L1 (64 KiB) / in L2 (16 MiB) / only in HBM (2 GiB), issued from the extend
- * kernel's launch shape; warp_inst_per_s: warp instructions issued per second with all four schedulers of every SM busy. */
-typedef struct { double gather_l1_gbs, gather_l2_gbs, gather_hbm_gbs, warp_inst_per_s; } gpt_peaks;
+ * kernel's launch shape; warp_inst_per_s: warp instructions issued per second with all four schedulers of every SM busy;
+ * stream_*: GB/s of coalesced 16-byte loads sweeping an L1- / L2-resident working set (the ceiling of that level). */
+typedef struct { double gather_l1_gbs, gather_l2_gbs, gather_hbm_gbs, warp_inst_per_s, stream_l1_gbs, stream_l2_gbs; } gpt_peaks;
 GPT_API int gpt_measure_peaks(gpt_ctx* ctx, gpt_peaks* out);
 
 /* ---- host-side helpers mirroring the reference's scene setup (no GPU needed) ---- */
