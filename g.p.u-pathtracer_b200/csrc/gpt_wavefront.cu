@@ -24,6 +24,18 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #define WF_THREADS 128
+// Path state (ray, mask, hit, queue entries) is touched ONCE per kernel, the scene again and again: with WF_STREAM the state goes
+// through the streaming (evict-first) load / store forms so that it does not push tree nodes and triangles out of L1 / L2.
+#ifndef WF_STREAM
+#define WF_STREAM 0
+#endif
+#if WF_STREAM
+#define WF_LD(p) __ldcs(p)
+#define WF_ST(p, v) __stcs((p), (v))
+#else
+#define WF_LD(p) (*(p))
+#define WF_ST(p, v) (*(p) = (v))
+#endif
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 5
 #endif
@@ -114,8 +126,8 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
                         PathState ps; primary_ray(gen, pid, ps);
                         o = ps.o; d = ps.d;
                     } else {
-                        pid = queue[j];
-                        const float4 ro = ray_o[pid], rd = ray_d[pid];
+                        pid = WF_LD(queue + j);
+                        const float4 ro = WF_LD(ray_o + pid), rd = WF_LD(ray_d + pid);
                         o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
                     }
                     trav_init(ts, stack, o, d, true);
@@ -143,7 +155,7 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
                 }
             }
             if (trav_finished(ts)) {
-                hit[pid] = make_int2(__float_as_int(ts.t), ts.tri);
+                WF_ST(hit + pid, make_int2(__float_as_int(ts.t), ts.tri));
                 active = false;
             }
         }
@@ -165,9 +177,9 @@ __device__ __forceinline__ void shade_load_path(const PrimaryGen& gen, const Sha
 {
     if (FIRST) primary_ray(gen, pid, ps);
     else {
-        const float4 ro = io.ray_o[pid], rd = io.ray_d[pid];
+        const float4 ro = WF_LD(io.ray_o + pid), rd = WF_LD(io.ray_d + pid);
         ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
-        ps.mask = mk3(ro.w, rd.w, io.mask_z[pid]);
+        ps.mask = mk3(ro.w, rd.w, WF_LD(io.mask_z + pid));
     }
     ps.accu = mk3(0.0f, 0.0f, 0.0f);      // accu stays in memory (shade_bounce, accu_slot)
 }
@@ -184,9 +196,9 @@ __device__ __forceinline__ bool shade_finish_path(const DevScene& sc, const Prim
     const bool cont = shade_bounce<FIRST, FAST>(sc, gen.p, s_spheres, s_boxes, h, (uint32_t)gen.pix0 + (pid - s_local * n_wave), gen.sample0 + s_local, bounce, ps, io.accu + pid);
     const bool survive = cont && !last_bounce;
     if (survive) {
-        io.ray_o[pid] = make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x);
-        io.ray_d[pid] = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y);
-        io.mask_z[pid] = ps.mask.z;
+        WF_ST(io.ray_o + pid, make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x));
+        WF_ST(io.ray_d + pid, make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y));
+        WF_ST(io.mask_z + pid, ps.mask.z);
     }
     return survive;
 }
@@ -200,7 +212,7 @@ __device__ __forceinline__ void shade_compact(const bool survive, const uint32_t
         const int leader = __ffs(m) - 1;
         if ((int)lane == leader) base = atomicAdd(n_out, (unsigned)__popc(m));
         base = __shfl_sync(GPT_FULL_MASK, base, leader);
-        if (survive) queue_out[base + (unsigned)__popc(m & ((1u << lane) - 1u))] = pid;
+        if (survive) WF_ST(queue_out + (base + (unsigned)__popc(m & ((1u << lane) - 1u))), pid);
     }
 }
 
@@ -231,10 +243,10 @@ k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const
         PathState ps;
         SceneHit h; h.t = GPT_F32_MAX; h.geom = GEO_NONE; h.prim = -1;
         if (valid) {
-            pid = FIRST ? i : io.queue_in[i];
+            pid = FIRST ? i : WF_LD(io.queue_in + i);
             shade_load_path<FIRST>(gen, io, pid, ps);
             float tri_t = GPT_F32_MAX; int tri = -1;
-            if (has_mesh) { const int2 hh = io.hit[pid]; tri_t = __int_as_float(hh.x); tri = hh.y; }
+            if (has_mesh) { const int2 hh = WF_LD(io.hit + pid); tri_t = __int_as_float(hh.x); tri = hh.y; }
             h = finish_scene_hit<FAST>(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
         }
         if (valid) survive = shade_finish_path<FIRST, FAST>(sc, gen, io, s_spheres, s_boxes, h, pid, bounce, last_bounce, ps);
