@@ -179,7 +179,7 @@ k_primary(const DevScene sc, const RenderParams p, const unsigned long long samp
         start_path(p, px, py, (uint32_t)pixel, sample, ps);
         const SceneHit h = intersect_scene(sc, s_spheres, s_boxes, ps.o, ps.d, p.cull != 0);
         if (geom) geom[pixel] = h.geom;
-        if (tri_idx) tri_idx[pixel] = h.geom == GEO_TRI ? __float_as_int(__ldg(sc.tris + 3 * h.prim).w) : -1;
+        if (tri_idx) tri_idx[pixel] = h.geom == GEO_TRI ? __float_as_int(tri_row_a(sc.tris, h.prim).w) : -1;
         if (prim_idx) prim_idx[pixel] = (h.geom == GEO_SPHERE || h.geom == GEO_BOX) ? h.prim : -1;
         if (t_out) t_out[pixel] = h.t;
     }
@@ -196,8 +196,8 @@ k_trace_rays(const DevScene sc, const float* __restrict__ o, const float* __rest
             const f3 ro = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), rd = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
             h = sc.wnodes ? traverse_bvh4(sc.wnodes, sc.tris, ro, rd, cull != 0) : traverse_bvh(sc.nodes, sc.tris, ro, rd, cull != 0);
         }
-        if (tri_idx) tri_idx[i] = h.tri >= 0 ? __float_as_int(__ldg(sc.tris + 3 * h.tri).w) : -1;
-        if (tri_addr) tri_addr[i] = h.tri >= 0 ? __float_as_int(__ldg(sc.tris + 3 * h.tri + 1).w) : -1;
+        if (tri_idx) tri_idx[i] = h.tri >= 0 ? __float_as_int(tri_row_a(sc.tris, h.tri).w) : -1;
+        if (tri_addr) tri_addr[i] = h.tri >= 0 ? __float_as_int(__ldg(sc.tris + GPT_TRI_STRIDE * (size_t)h.tri + GPT_TRI_B).w) : -1;
         if (t_out) t_out[i] = h.t;
     }
 }

@@ -17,6 +17,25 @@
 
 struct f3 { float x, y, z; };
 
+// One 64-byte record (a BVH node) as TWO 256-bit loads through the read-only path (LDG.E.256, new on sm_100) instead of four
+// 128-bit ones: a divergent warp costs the L1 one tag look-up ("wavefront") per lane and per load INSTRUCTION, and the extend
+// kernel runs at ~0.9 of the rate at which L1 serves such gathers (bench.py roofline.bounds), so halving the loads per node
+// halves that cost.  GPT_LD256=0 keeps the four LDG.128 (A/B).  p must be 32-byte aligned (nodes are 64-byte aligned).
+#ifndef GPT_LD256
+#define GPT_LD256 1
+#endif
+__device__ __forceinline__ void ldg_node64(const float4* __restrict__ p, float4& a, float4& b, float4& c, float4& d)
+{
+#if GPT_LD256
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w), "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "l"(p + 2));
+#else
+    a = __ldg(p); b = __ldg(p + 1); c = __ldg(p + 2); d = __ldg(p + 3);
+#endif
+}
+
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
 __device__ __forceinline__ f3 add3(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
 __device__ __forceinline__ f3 sub3(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }

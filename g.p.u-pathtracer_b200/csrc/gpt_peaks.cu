@@ -1,7 +1,7 @@
 // gpt_peaks.cu -- micro-benchmarks that measure, on the device the context runs on, the peaks the traversal kernels are
 // actually bounded by (gpt_measure_peaks; bench.py states its roofline fractions against THESE, not against data-sheet figures):
-//   gather bandwidth  random 64-byte fetches (4 x LDG.128 through the read-only path, the shape of one BVH node fetch,
-//                     gpt_traverse.cuh node_step) from a working set that fits L1 (64 KB), fits L2 (24 MB), or only HBM (2 GB);
+//   gather bandwidth  random 64-byte fetches (ldg_node64: 2 x LDG.256 through the read-only path, the BVH node fetch of
+//                     gpt_traverse.cuh node_next) from a working set that fits L1 (64 KB), fits L2 (24 MB), or only HBM (2 GB);
 //                     independent addresses, 128-thread CTAs at the extend kernel's grid (SMs x 10)
 //   issue rate        eight independent FFMA chains per thread: warp instructions issued per second with every scheduler busy
 //                     (= SMs x 4 schedulers x SM clock when nothing stalls)
@@ -17,7 +17,8 @@ k_peak_gather(const float4* __restrict__ buf, const unsigned mask, const int ite
     for (int i = 0; i < iters; ++i) {
         idx = idx * 1664525u + 1013904223u;
         const float4* p = buf + 4 * (size_t)((idx >> 7) & mask);
-        const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3);
+        float4 a, b, c, d;
+        ldg_node64(p, a, b, c, d);                 // the node fetch of gpt_traverse.cuh, same load instructions
         acc.x += a.x + b.x; acc.y += a.y + c.y; acc.z += b.z + d.z; acc.w += c.w + d.w;
     }
     if (acc.x == 123.456f) sink[0] = acc;      // never true for the zeroed buffer: keeps the loads alive

@@ -58,10 +58,11 @@ __global__ void k_write_packed(const float4* __restrict__ ref_nodes, int n_inner
         while (__float_as_uint(ref_tris[slot].x) != LEAF_TERM) {
             const float4 v0 = ref_tris[slot], v1 = ref_tris[slot + 1], v2 = ref_tris[slot + 2];
             const int orig = ((size_t)slot < n_indices) ? ref_indices[slot] : -1;
-            float4* dst = tris + 3 * (size_t)(base + k);
+            float4* dst = tris + GPT_TRI_STRIDE * (size_t)(base + k);
             dst[0] = make_float4(v0.x, v0.y, v0.z, __int_as_float(orig));
-            dst[1] = make_float4(v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, __int_as_float(slot));
-            dst[2] = make_float4(v2.x - v0.x, v2.y - v0.y, v2.z - v0.z, __int_as_float(cnt - 1 - k));
+            dst[GPT_TRI_B] = make_float4(v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, __int_as_float(slot));
+            dst[GPT_TRI_B + 1] = make_float4(v2.x - v0.x, v2.y - v0.y, v2.z - v0.z, __int_as_float(cnt - 1 - k));
+
             ++k; slot += 3;
         }
     }
@@ -74,9 +75,11 @@ __global__ void k_write_packed(const float4* __restrict__ ref_nodes, int n_inner
     reinterpret_cast<int*>(nodes + 4 * node + 3)[i & 1] = packed_child;
     if ((i & 1) == 0) { reinterpret_cast<int*>(nodes + 4 * node + 3)[2] = 0; reinterpret_cast<int*>(nodes + 4 * node + 3)[3] = 0; }
     if (i == 0) {   // null triangle: zero area -> det == 0 -> never hit; 0 triangles follow it in its leaf
-        tris[3 * (size_t)n_total + 0] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-        tris[3 * (size_t)n_total + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-        tris[3 * (size_t)n_total + 2] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+        float4* nt = tris + GPT_TRI_STRIDE * (size_t)n_total;
+        nt[0] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        nt[GPT_TRI_B] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        nt[GPT_TRI_B + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+
     }
 }
 
@@ -122,7 +125,7 @@ cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float
         CK(cudaStreamSynchronize(st));
         if (h_bad) { out->bad_layout = h_bad; goto done; }
         CK(cudaMalloc(&out->nodes, sizeof(float4) * 4 * (size_t)n_inner));
-        CK(cudaMalloc(&out->tris, sizeof(float4) * 3 * ((size_t)h_total + 1)));
+        CK(cudaMalloc(&out->tris, sizeof(float4) * GPT_TRI_STRIDE * ((size_t)h_total + 1)));
         k_write_packed<<<(n_child + 127) / 128, 128, 0, st>>>(ref_nodes, n_inner, ref_tris, ref_indices, n_indices, offsets, h_total, out->nodes, out->tris);
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(st));

@@ -63,3 +63,14 @@ struct RenderParams {
 };
 
 __device__ __forceinline__ f3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
+
+// Packed-triangle addressing: 48 B per triangle, rows (v0 | e1 | e2) = three LDG.128; the two edge rows first -- the determinant
+// test (cudaUtils.h:145-153) needs only them.  (A 64-byte layout whose edge rows come with one 256-bit load was measured 1-2 %
+// slower on every scene: profiles/r02_schedules.md #52.)
+#define GPT_TRI_STRIDE 3
+#define GPT_TRI_B 1
+__device__ __forceinline__ float4 tri_row_a(const float4* __restrict__ tris, const int ti) { return __ldg(tris + GPT_TRI_STRIDE * (size_t)ti); }
+__device__ __forceinline__ void tri_rows_bc(const float4* __restrict__ tris, const int ti, float4& b, float4& c)
+{
+    b = __ldg(tris + GPT_TRI_STRIDE * (size_t)ti + 1); c = __ldg(tris + GPT_TRI_STRIDE * (size_t)ti + 2);
+}

@@ -82,14 +82,14 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
         emit = mk3(s[4], s[5], s[6]); objcol = mk3(s[7], s[8], s[9]); mat = __float_as_int(s[10]);
     } else if (h.geom == GEO_TRI) {                                      // :123-139
-        const float4 b = __ldg(sc.tris + 3 * h.prim + 1);
-        const float4 c = __ldg(sc.tris + 3 * h.prim + 2);
+        float4 b, c;
+        tri_rows_bc(sc.tris, h.prim, b, c);
         // cross(v0-v1, v0-v2) == cross(e1, e2) bit for bit (negation is exact)   cudaUtils.h:432
         n = norm3_t<FAST>(cross3(mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z)));
         nl = n;                                                          // Q4: not face-forwarded
         emit = ld3(p.emi); objcol = ld3(p.col); mat = p.tri_mat;
         if (sc.n_faces) {                                                // N4: per-face material table
-            const int face = __float_as_int(__ldg(sc.tris + 3 * h.prim).w);
+            const int face = __float_as_int(tri_row_a(sc.tris, h.prim).w);
             if ((unsigned)face < (unsigned)sc.n_faces) {
                 const int m = __ldg(sc.face_mat + face);
                 if ((unsigned)m < (unsigned)sc.n_tri_mats) {

@@ -83,10 +83,9 @@ __device__ __forceinline__ bool trav_finished(const TravState& s) { return s.nod
 __device__ __forceinline__ int node_next(const float4* __restrict__ nodes, TravState& s, int* stack)
 {
     const int node = s.node;
-    const float4 n0 = __ldg(nodes + node);
-    const float4 n1 = __ldg(nodes + node + 1);
-    const float4 nz = __ldg(nodes + node + 2);
-    const int4 ch = __ldg(reinterpret_cast<const int4*>(nodes + node + 3));
+    float4 n0, n1, nz, chf;
+    ldg_node64(nodes + node, n0, n1, nz, chf);
+    const int4 ch = make_int4(__float_as_int(chf.x), __float_as_int(chf.y), 0, 0);
     const float c0lox = fmaf(n0.x, s.idx, -s.oodx), c0hix = fmaf(n0.y, s.idx, -s.oodx);
     const float c0loy = fmaf(n0.z, s.idy, -s.oody), c0hiy = fmaf(n0.w, s.idy, -s.oody);
     const float c1lox = fmaf(n1.x, s.idx, -s.oodx), c1hix = fmaf(n1.y, s.idx, -s.oodx);
@@ -136,10 +135,11 @@ static __constant__ unsigned gpt_w4_magic = 0x4B000000u;
 __device__ __forceinline__ int node4_next(const float4* __restrict__ wn, TravState& s, int* stack)
 {
     const int node = s.node;
-    const float4 h = __ldg(wn + node);
-    const uint4 qa = __ldg(reinterpret_cast<const uint4*>(wn + node + 1));
-    const uint2 qb = __ldg(reinterpret_cast<const uint2*>(wn + node + 2));
-    const int4 ch = __ldg(reinterpret_cast<const int4*>(wn + node + 3));
+    float4 h, qaf, qbf, chf;
+    ldg_node64(wn + node, h, qaf, qbf, chf);
+    const uint4 qa = make_uint4(__float_as_uint(qaf.x), __float_as_uint(qaf.y), __float_as_uint(qaf.z), __float_as_uint(qaf.w));
+    const uint2 qb = make_uint2(__float_as_uint(qbf.x), __float_as_uint(qbf.y));
+    const int4 ch = make_int4(__float_as_int(chf.x), __float_as_int(chf.y), __float_as_int(chf.z), __float_as_int(chf.w));
     const unsigned eb = __float_as_uint(h.w);
     // plane = origin + q * 2^e  =>  t = (plane - o) / d = q * s + b  with s = 2^e / d, b = (origin - o) / d.  The byte q is
     // dropped into the mantissa of 2^23 (one PRMT, selector immediate, 2^23 kept in a register) and the 2^23 * s it
@@ -195,9 +195,9 @@ __device__ __forceinline__ void tri_step(const float4* __restrict__ tris, TravSt
                                          const f3 o, const f3 d, const bool cull)
 {
     const int ti = s.tri_cur;
-    const float4 a = __ldg(tris + 3 * ti);
-    const float4 b = __ldg(tris + 3 * ti + 1);
-    const float4 c = __ldg(tris + 3 * ti + 2);
+    float4 b, c;
+    tri_rows_bc(tris, ti, b, c);
+    const float4 a = tri_row_a(tris, ti);
     const float t = tri_test(a, b, c, o, d, cull);
     if (t > 0.0f && t < s.t) { s.t = t; s.tri = ti; }        // :428, strict: first visited wins ties
     if (__float_as_int(c.w) == 0) {                          // last triangle of the leaf (no triangle follows)
@@ -221,8 +221,8 @@ __device__ __forceinline__ void leaf_step_culled(const float4* __restrict__ tris
     while (more) {
         unsigned m = 0u; int k = 0;
         do {
-            const float4 b = __ldg(tris + 3 * (first + k) + 1);
-            const float4 c = __ldg(tris + 3 * (first + k) + 2);
+            float4 b, c;
+            tri_rows_bc(tris, first + k, b, c);
             const float det = dot3(mk3(b.x, b.y, b.z), cross3(d, mk3(c.x, c.y, c.z)));
             if (!(det < 0.00001f)) m |= 1u << k;             // culling: det < -eps and -eps <= det < eps both miss
             more = __float_as_int(c.w) != 0;                 // triangles that follow in this leaf
@@ -231,7 +231,9 @@ __device__ __forceinline__ void leaf_step_culled(const float4* __restrict__ tris
         while (m) {
             const int ti = first + __ffs(m) - 1;
             m &= m - 1u;
-            const float t = tri_test(__ldg(tris + 3 * ti), __ldg(tris + 3 * ti + 1), __ldg(tris + 3 * ti + 2), o, d, true);
+            float4 b, c;
+            tri_rows_bc(tris, ti, b, c);
+            const float t = tri_test(tri_row_a(tris, ti), b, c, o, d, true);
             if (t > 0.0f && t < s.t) { s.t = t; s.tri = ti; }   // :428, strict: first visited wins ties
         }
         first += k;
