@@ -108,7 +108,7 @@ static void free_scene(gpt_ctx* c)
 static void free_wave(gpt_ctx* c)
 {
     WaveBuffers& w = c->wave;
-    cudaFree(w.ray_o); cudaFree(w.ray_d); cudaFree(w.mask_z); cudaFree(w.accu); cudaFree(w.lsum); cudaFree(w.hit);
+    cudaFree(w.ray); cudaFree(w.mask_z); cudaFree(w.accu); cudaFree(w.lsum); cudaFree(w.hit);
     cudaFree(w.queue[0]); cudaFree(w.queue[1]); cudaFree(w.counters);
     cudaFree(w.sort_keys[0]); cudaFree(w.sort_keys[1]); cudaFree(w.sort_vals); cudaFree(w.sort_tmp);
     w = WaveBuffers{}; c->wave_pixels = 0; c->wave_counters = 0;
@@ -127,7 +127,7 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     if (want < c->wave.capacity) want = c->wave.capacity;
     free_wave(c);
     WaveBuffers& w = c->wave;
-    CU(c, cudaMalloc(&w.ray_o, want * sizeof(float4))); CU(c, cudaMalloc(&w.ray_d, want * sizeof(float4)));
+    CU(c, cudaMalloc(&w.ray, 2 * want * sizeof(float4)));
     CU(c, cudaMalloc(&w.mask_z, want * sizeof(float)));  CU(c, cudaMalloc(&w.accu, want * sizeof(float4)));
     CU(c, cudaMalloc(&w.hit, want * sizeof(int2)));
     CU(c, cudaMalloc(&w.queue[0], want * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], want * sizeof(uint32_t)));

@@ -79,7 +79,7 @@ cudaError_t gptk_build_wide(const float4* nodes2, int n_inner, WideResult* out, 
 
 // wavefront pipeline (gpt_wavefront.cu).  Per-path arrays hold `capacity` entries, lsum one per pixel.
 struct WaveBuffers {
-    float4 *ray_o, *ray_d, *accu, *lsum;   // ray_o.w / ray_d.w carry the colour mask's x / y
+    float4 *ray, *accu, *lsum;             // ray: 2 float4 per path = origin + direction, whose w lanes carry the colour mask's x / y
     float* mask_z;
     int2* hit;
     uint32_t* queue[2];

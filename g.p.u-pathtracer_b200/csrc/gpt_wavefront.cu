@@ -29,6 +29,30 @@
 #ifndef WF_STREAM
 #define WF_STREAM 0
 #endif
+// The ray of a path = ONE 32-byte record (origin xyz + mask x | direction xyz + mask y), read and written with one 256-bit
+// access (LDG / STG .256, sm_100): path ids are scattered after the first bounce, so every access instruction costs a tag look-up
+// per lane.
+#ifndef WF_RAY256
+#define WF_RAY256 1      // 0: the same record as two 128-bit accesses (A/B)
+#endif
+__device__ __forceinline__ void ld_ray32(const float4* __restrict__ ray, const uint32_t pid, float4& o, float4& d)
+{
+#if WF_RAY256
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w), "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "l"(ray + 2 * (size_t)pid) : "memory");
+#else
+    o = ray[2 * (size_t)pid]; d = ray[2 * (size_t)pid + 1];
+#endif
+}
+__device__ __forceinline__ void st_ray32(float4* __restrict__ ray, const uint32_t pid, const float4 o, const float4 d)
+{
+#if WF_RAY256
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(ray + 2 * (size_t)pid), "f"(o.x), "f"(o.y), "f"(o.z), "f"(o.w), "f"(d.x), "f"(d.y), "f"(d.z), "f"(d.w) : "memory");
+#else
+    ray[2 * (size_t)pid] = o; ray[2 * (size_t)pid + 1] = d;
+#endif
+}
 #if WF_STREAM
 #define WF_LD(p) __ldcs(p)
 #define WF_ST(p, v) __stcs((p), (v))
@@ -96,7 +120,7 @@ __device__ __forceinline__ void primary_ray(const PrimaryGen& g, const uint32_t 
 template <bool CULL, bool WIDE, bool PRIMARY>      // back-face culling resolved at compile time: the flag is tested once per triangle otherwise
 __global__ void __launch_bounds__(WF_THREADS, WIDE ? WF_WIDE_MIN_BLOCKS : WF_MIN_BLOCKS)
 k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr,
-               unsigned int* __restrict__ fetch, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
+               unsigned int* __restrict__ fetch, const float4* __restrict__ ray,
                int2* __restrict__ hit, const int refill_min, const int node_k, const PrimaryGen gen)
 {
     const unsigned lane = threadIdx.x & 31u;
@@ -127,7 +151,8 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
                         o = ps.o; d = ps.d;
                     } else {
                         pid = WF_LD(queue + j);
-                        const float4 ro = WF_LD(ray_o + pid), rd = WF_LD(ray_d + pid);
+                        float4 ro, rd;
+                        ld_ray32(ray, pid, ro, rd);
                         o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
                     }
                     trav_init(ts, stack, o, d, true);
@@ -169,7 +194,7 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
 // FAST: GPT_FLAG_FAST shading arithmetic (gpt_math.cuh) -- opt-in, statistically equal, not bit-equal.
 struct ShadeIo {
     const uint32_t* queue_in; unsigned int* counters; uint32_t* queue_out;
-    float4* ray_o; float4* ray_d; const int2* hit; float* mask_z; float4* accu;
+    float4* ray; const int2* hit; float* mask_z; float4* accu;      // ray: 2 float4 per path (ld_ray32 / st_ray32)
 };
 
 template <bool FIRST>
@@ -177,7 +202,8 @@ __device__ __forceinline__ void shade_load_path(const PrimaryGen& gen, const Sha
 {
     if (FIRST) primary_ray(gen, pid, ps);
     else {
-        const float4 ro = WF_LD(io.ray_o + pid), rd = WF_LD(io.ray_d + pid);
+        float4 ro, rd;
+        ld_ray32(io.ray, pid, ro, rd);
         ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
         ps.mask = mk3(ro.w, rd.w, WF_LD(io.mask_z + pid));
     }
@@ -196,8 +222,7 @@ __device__ __forceinline__ bool shade_finish_path(const DevScene& sc, const Prim
     const bool cont = shade_bounce<FIRST, FAST>(sc, gen.p, s_spheres, s_boxes, h, (uint32_t)gen.pix0 + (pid - s_local * n_wave), gen.sample0 + s_local, bounce, ps, io.accu + pid);
     const bool survive = cont && !last_bounce;
     if (survive) {
-        WF_ST(io.ray_o + pid, make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x));
-        WF_ST(io.ray_d + pid, make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y));
+        st_ray32(io.ray, pid, make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x), make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y));
         WF_ST(io.mask_z + pid, ps.mask.z);
     }
     return survive;
@@ -340,7 +365,7 @@ __host__ __device__ __forceinline__ int wf_sort_bits(const int mode) { return mo
 // mode 1: 7 + 1 (octant) = 24 bits   mode 2: 6 + 2 = 24   mode 3: 7 + 3 = 30   mode 4: 9 + 1 = 30   mode 5: 8 + 2 = 30   mode 6: 6 + 4 = 30   mode 7: 5 + 5 = 30   mode 8: 4 + 1 = 15 (two radix passes)   mode 9: 3 + 2 = 15
 __global__ void __launch_bounds__(256)
 k_wf_sort_keys(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr, const unsigned n_slots,
-               const float4* __restrict__ ray_o, const float4* __restrict__ ray_d, uint32_t* __restrict__ keys, const int mode)
+               const float4* __restrict__ ray, uint32_t* __restrict__ keys, const int mode)
 {
     const unsigned n = *n_ptr;
     const unsigned kmax = 0xffffffffu >> (32 - wf_sort_bits(mode));
@@ -357,7 +382,8 @@ k_wf_sort_keys(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
         unsigned key = kmax;
         if (j < n) {
             const uint32_t pid = queue[j];
-            const float4 o = ray_o[pid], d = ray_d[pid];
+            float4 o, d;
+            ld_ray32(ray, pid, o, d);
             const unsigned cx = (unsigned)fminf(fmaxf((o.x - lox) * sx, 0.0f), omax);
             const unsigned cy = (unsigned)fminf(fmaxf((o.y - loy) * sy, 0.0f), omax);
             const unsigned cz = (unsigned)fminf(fmaxf((o.z - loz) * sz, 0.0f), omax);
@@ -407,11 +433,11 @@ static void launch_extend(const DevScene& sc, const RenderParams& p, const WaveL
                           const WaveBuffers& wb, int node_k, const PrimaryGen& gen, cudaStream_t st)
 {
     if (sc.wnodes) {
-        if (p.cull) k_wf_extend_ww<true, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
-        else k_wf_extend_ww<false, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
+        if (p.cull) k_wf_extend_ww<true, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray, wb.hit, cfg.refill_min, node_k, gen);
+        else k_wf_extend_ww<false, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray, wb.hit, cfg.refill_min, node_k, gen);
     } else {
-        if (p.cull) k_wf_extend_ww<true, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
-        else k_wf_extend_ww<false, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray_o, wb.ray_d, wb.hit, cfg.refill_min, node_k, gen);
+        if (p.cull) k_wf_extend_ww<true, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray, wb.hit, cfg.refill_min, node_k, gen);
+        else k_wf_extend_ww<false, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray, wb.hit, cfg.refill_min, node_k, gen);
     }
 }
 
@@ -460,7 +486,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                 const uint32_t* q_ext = q_in;       // order in which the extend kernel fetches the rays
                 if (has_mesh && b > 0 && wb.sort_vals) {
                     if (kt) kt->tick(KT_OTHER, st);
-                    k_wf_sort_keys<<<grid, 256, 0, st>>>(sc, q_in, wb.counters + b, (unsigned)n_paths, wb.ray_o, wb.ray_d, wb.sort_keys[0], cfg.sort_mode);
+                    k_wf_sort_keys<<<grid, 256, 0, st>>>(sc, q_in, wb.counters + b, (unsigned)n_paths, wb.ray, wb.sort_keys[0], cfg.sort_mode);
                     size_t tb = wb.sort_tmp_bytes;
                     if ((e = cub::DeviceRadixSort::SortPairs(wb.sort_tmp, tb, (const uint32_t*)wb.sort_keys[0], wb.sort_keys[1], q_in, wb.sort_vals,
                                                              (long long)n_paths, 0, wf_sort_bits(cfg.sort_mode), st)) != cudaSuccess) return e;
@@ -476,7 +502,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
                 if (kt) kt->tick(KT_SHADE, st);
                 ShadeIo io;
                 io.queue_in = q_in; io.counters = wb.counters; io.queue_out = wb.queue[(b + 1u) & 1u];
-                io.ray_o = wb.ray_o; io.ray_d = wb.ray_d; io.hit = wb.hit; io.mask_z = wb.mask_z; io.accu = wb.accu;
+                io.ray = wb.ray; io.hit = wb.hit; io.mask_z = wb.mask_z; io.accu = wb.accu;
                 if (p.flags & RP_FAST) {
                     if (b == 0) k_wf_shade<true, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, stats);
                     else k_wf_shade<false, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, stats);
