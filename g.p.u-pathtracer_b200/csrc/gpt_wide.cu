@@ -95,6 +95,14 @@ k_w4_collapse_level(const float4* __restrict__ nodes2, const int* __restrict__ q
     if (!ok) { atomicExch(bad, 1); return; }
     unsigned qlo[3] = {0u, 0u, 0u}, qhi[3] = {0u, 0u, 0u};
     int child[4];
+    // the node's inner children get CONSECUTIVE slots of the next level (one reservation per node): a ray that goes on into two of
+    // them finds both within 256 bytes instead of anywhere in the level
+#ifndef W4_CONTIG
+#define W4_CONTIG 1
+#endif
+    int n_inner_ch = 0;
+    for (int k = 0; k < cnt; ++k) n_inner_ch += s[k].child >= 0;
+    int next_slot = (W4_CONTIG && n_inner_ch) ? atomicAdd(n_out, n_inner_ch) : 0;
     for (int k = 0; k < 4; ++k) {
         if (k >= cnt) {
             child[k] = GPT_W4_EMPTY;
@@ -112,7 +120,7 @@ k_w4_collapse_level(const float4* __restrict__ nodes2, const int* __restrict__ q
             qhi[ax] |= (unsigned)(qh + 1) << (8 * k);
         }
         if (s[k].child >= 0) {
-            const int j = atomicAdd(n_out, 1);
+            const int j = W4_CONTIG ? next_slot++ : atomicAdd(n_out, 1);
             q_out[j] = s[k].child;
             child[k] = (base_next + j) * 4;
         } else {

@@ -5,10 +5,10 @@ set -e
 cd "$(dirname "$0")/../../g.p.u-pathtracer_b200"
 while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
-  touch csrc/gpt_wavefront.cu csrc/gpt_kernels.cu csrc/gpt_repack.cu csrc/gpt_peaks.cu csrc/gpt_abi.cu
+  touch csrc/*.cu
   make EXTRA="$flags" > /tmp/build_$name.log 2>&1 || { tail -20 /tmp/build_$name.log; exit 1; }
   cp libgpt_b200.so ../variants/$name.so
   echo "$name: $flags"; grep -A2 "k_wf_shade\|k_wf_extend_wwILb1ELb0" csrc/gpt_wavefront.o.ptxas.log | grep -E "Used|spill" | head -4
 done
-touch csrc/gpt_wavefront.cu csrc/gpt_kernels.cu csrc/gpt_repack.cu csrc/gpt_peaks.cu csrc/gpt_abi.cu
+touch csrc/*.cu
 make > /dev/null 2>&1

@@ -520,3 +520,103 @@ print(json.dumps(res))
     assert d == mk and wf > mk, r                      # 262144 paths: the default is the megakernel
     d, wf, mk = r["large"]["launches"]
     assert d == wf and wf > mk, r                      # 442368 paths: the default is the wavefront pipeline
+
+
+# ------------------------------------------------------------------ round 2: pointer-identity rule, depth limit, NO_TRIAL
+def test_invalidate_scene_after_in_place_rewrite(gpt, torch_cuda):
+    """gpt_launch traverses a re-packed copy cached by pointer identity (gpt.h, POINTER-IDENTITY RULE): rewriting the caller's BVH
+    arrays IN PLACE is invisible until gpt_invalidate_scene(); then the next launch re-packs and equals the oracle on the new arrays."""
+    torch = torch_cuda
+    sc = scenes.load_scene("bunny_cornell")
+    sph = gpt.default_spheres()
+    w, h = 128, 72
+    # a second tree with the same array sizes: the same mesh moved 2.5 units in x (child boxes and vertices; the leaf terminators
+    # -- rows whose x is the bit pattern of -0.0, cudaUtils.h:413 -- stay as they are)
+    nodes2, tris2 = sc["nodes"].copy(), sc["tris"].copy()
+    n = nodes2.reshape(-1, 4, 4)
+    n[:, 0, 0:2] += 2.5
+    n[:, 1, 0:2] += 2.5
+    term = tris2.view(np.uint32)[:, 0] == 0x80000000
+    tris2[~term, 0] += 2.5
+    sc2 = dict(sc, nodes=nodes2, tris=tris2)
+    d_nodes, d_tris, d_idx = dev(torch, sc["nodes"]), dev(torch, sc["tris"]), dev(torch, sc["indices"])
+    d_sph = torch.from_numpy(np.frombuffer(bytes(sph), dtype=np.uint8).copy()).cuda()
+    info = small_info(gpt, w, h, depth=3)
+    info.bvhData.dev_triNode = d_nodes.data_ptr(); info.bvhData.triNodeSize = sc["nodes"].shape[0]
+    info.bvhData.dev_triPtr = d_tris.data_ptr(); info.bvhData.triSize = sc["tris"].shape[0]
+    info.bvhData.dev_triIndicesPtr = d_idx.data_ptr(); info.bvhData.triIndicesSize = sc["indices"].shape[0]
+    info.sphereTex = d_sph.data_ptr(); info.numSpheres = len(sph)
+    accum = torch.zeros(h * w * 3, dtype=torch.float32, device="cuda")
+    info.accumBuffer = accum.data_ptr()
+    info.hash, info.constantPdf = gpt.hash64(7), 1
+
+    def frame():
+        ctx.launch(info); ctx.sync()
+        return accum.cpu().numpy().reshape(h, w, 3).copy()
+    with gpt.Context(0) as ctx:
+        a = frame()
+        want_a = np.clip(scenes.oracle_render(sc, sph, info, info.hash, 0, 1)[..., :3], 0, 1)
+        assert np.array_equal(a, want_a)
+        d_nodes.copy_(dev(torch, nodes2)); d_tris.copy_(dev(torch, tris2))      # same addresses, same sizes, new content
+        torch.cuda.synchronize()
+        assert np.array_equal(frame(), a)                            # documented: the stale packed tree is still traversed
+        ctx.invalidate_scene()
+        b = frame()
+        want_b = np.clip(scenes.oracle_render(sc2, sph, info, info.hash, 0, 1)[..., :3], 0, 1)
+        assert not np.array_equal(b, a)
+        assert np.array_equal(b, want_b)
+
+
+def test_tree_deeper_than_the_stack_is_rejected(gpt, torch_cuda):
+    """A chain of 70 inner nodes (each: one leaf, one inner child): valid CudaBVH layout, but 70 levels would overrun the 64-entry
+    traversal stack (cudaUtils.h:22,259) -- GPT_ERR_LAYOUT instead of a silent out-of-bounds write; 60 levels are accepted."""
+    def chain(levels):
+        nodes = np.zeros((levels * 4, 4), np.float32)
+        tris, idx = [], []
+        ni = nodes.view(np.int32)
+        for i in range(levels):
+            z = -30.0 - i
+            for leaf in range(2 if i == levels - 1 else 1):
+                slot = len(tris)
+                x0 = float(leaf)
+                tris += [[x0, 0, z, 0], [x0 + 1, 0, z, 0], [x0, 1, z, 0]]
+                idx += [len(idx) // 4, 0, 0]
+                t = np.zeros(4, np.float32); t.view(np.uint32)[0] = 0x80000000
+                tris.append(list(t)); idx.append(0)
+                ni[4 * i + 3, leaf if i == levels - 1 else 0] = ~slot
+            if i < levels - 1:
+                ni[4 * i + 3, 1] = 64 * (i + 1)
+            nodes[4 * i + 0] = [-1, 3, -1, 3]; nodes[4 * i + 1] = [-1, 3, -1, 3]; nodes[4 * i + 2] = [-200, 0, -200, 0]
+        t = np.array(tris, np.float32)
+        t.view(np.uint32)[3::4, 0] = 0x80000000
+        return nodes, t, np.array(idx, np.int32)
+    with gpt.Context(0) as ctx:
+        n, t, i = chain(60)
+        ctx.upload_scene(n, t, i, gpt.default_spheres())
+        n, t, i = chain(70)
+        with pytest.raises(gpt.GptError, match="traversal stack"):
+            ctx.upload_scene(n, t, i, gpt.default_spheres())
+
+
+def test_no_trial_flag_keeps_calls_asynchronous(gpt, torch_cuda):
+    """GPT_FLAG_NO_TRIAL: a scene large enough for the timed per-scene trial never enters it (no render call synchronises on its
+    account), and the image equals the default context's."""
+    torch = torch_cuda
+    from support import procedural
+    v, f = procedural.synthetic_scene(120000, seed=3)
+    info = gpt.default_kernel_info(1280, 1024)                       # > 1 Mi paths per call: trial territory
+    info.depth = 3
+    out = []
+    for flags in (gpt.FLAG_NO_TRIAL, 0):
+        with gpt.Context(0, flags) as ctx:
+            b = ctx.build_bvh(v, f)
+            ctx.upload_built(b, gpt.default_spheres())
+            acc = torch.zeros(1024, 1280, 4, dtype=torch.float32, device="cuda")
+            pend0 = ctx.trial_info()[0]
+            ctx.render(info, acc, 1, 0, 1)
+            torch.cuda.synchronize()
+            out.append((pend0, ctx.trial_info()[0], acc.cpu().numpy()))
+            ctx.free_bvh(b)
+    assert out[0][0] is False and out[0][1] is False                 # never pending with the flag
+    assert out[1][0] is True                                         # the default context does put this scene on trial
+    assert np.mean(np.any(out[0][2] != out[1][2], axis=-1)) <= 1e-5  # binary vs (possibly) 4-wide candidate: t-ties only
