@@ -32,6 +32,9 @@ FLAG_WAVEFRONT = 1 << 7       # always the wavefront pipeline (default: megakern
 FLAG_BUILD_LBVH = 1 << 8      # build_bvh: Morton radix tree instead of PLOC clustering
 FLAG_FAST = 1 << 10           # opt-in fast shading arithmetic (statistical parity, not bit-exact)
 FLAG_NO_TRIAL = 1 << 9        # no timed per-scene trial: render calls never synchronise (graph capture, strict asynchrony)
+STATIC_MAX_PIXELS = 256 * 1024   # gpt_render_static (include/gpt.h GPT_STATIC_*): frame pixels, paths per wave, depth
+STATIC_MAX_PATHS = 256 * 1024
+STATIC_MAX_DEPTH = 64
 K_GENERATE, K_EXTEND, K_SHADE, K_COLLECT, K_ACCUMULATE, K_RESOLVE, K_OTHER = range(7)
 
 
@@ -101,7 +104,7 @@ assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 
 # every symbol include/gpt.h declares (tests check the library exports each one)
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
-           "gpt_upload_scene", "gpt_launch", "gpt_invalidate_scene", "gpt_render", "gpt_resolve", "gpt_render_frame_host",
+           "gpt_upload_scene", "gpt_launch", "gpt_invalidate_scene", "gpt_render", "gpt_render_static", "gpt_resolve", "gpt_render_frame_host",
            "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_measure_peaks", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
@@ -134,6 +137,7 @@ def load_library():
     L.gpt_launch.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_void_p]
     L.gpt_invalidate_scene.argtypes = [C.c_void_p]
     L.gpt_render.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p]
+    L.gpt_render_static.argtypes = L.gpt_render.argtypes
     L.gpt_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gpt_render_frame_host.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]
     L.gpt_trace_primary.argtypes = [C.c_void_p, C.POINTER(kernelInfo), C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -380,6 +384,11 @@ class Context:
     def render(self, info, accum_f4, seed, sample_begin, sample_count, stream=None):
         self._ck(self._L.gpt_render(self._h, C.byref(info), _ptr(accum_f4), C.c_uint64(seed), C.c_uint64(sample_begin),
                                     C.c_uint32(sample_count), _ptr(stream)), "gpt_render")
+
+    def render_static(self, info, accum_f4, seed, sample_begin, sample_count, stream=None):
+        """gpt_render on the library's fixed device scratch: allocates nothing; frames of <= STATIC_MAX_PIXELS, depth <= STATIC_MAX_DEPTH"""
+        self._ck(self._L.gpt_render_static(self._h, C.byref(info), _ptr(accum_f4), C.c_uint64(seed), C.c_uint64(sample_begin),
+                                           C.c_uint32(sample_count), _ptr(stream)), "gpt_render_static")
 
     def resolve(self, accum_f4, width, height, out_rgba8=None, out_rgb_f32=None, stream=None):
         self._ck(self._L.gpt_resolve(self._h, _ptr(accum_f4), int(width), int(height), _ptr(out_rgba8), _ptr(out_rgb_f32), _ptr(stream)),

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -820,3 +821,104 @@ int gpt_reset_stats(gpt_ctx* c)
 }
 
 } // extern "C"
+
+// ---- gpt_render_static: the wavefront pipeline on scratch that is never allocated ----------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc (code under
+// CUDA graph capture, tight serving loops, harnesses that forbid it).  The per-path state and per-pixel sums that ensure_wave()
+// cudaMallocs for gpt_render live here in ONE file-scope device array of fixed size, so every GPU that loads the library holds
+// GPT_STATIC_SCRATCH_BYTES (21 MiB) until the process exits.  The array's name is a host-side stand-in in host code, not a device
+// address: static_scratch_base() asks the runtime for the address once per device (cudaGetSymbolAddress with that device current)
+// and the kernels only ever see that pointer.
+//   layout (offsets are multiples of 256 B; P = GPT_STATIC_MAX_PATHS paths per wave, X = GPT_STATIC_MAX_PIXELS pixels):
+//     ray 32 P | accu 16 P | lsum 16 X | hit 8 P | mask_z 4 P | queue[0] 4 P | queue[1] 4 P | counters 4 KiB
+// All calls on a device share the array: the queue counters are cleared on `stream` at the start of every call (everything else is
+// written before it is read), and two calls that overlap on the GPU (different streams, or different contexts of one device) race.
+#define GPT_STATIC_P ((size_t)GPT_STATIC_MAX_PATHS)
+#define GPT_STATIC_X ((size_t)GPT_STATIC_MAX_PIXELS)
+#define GPT_STATIC_OFF_RAY      ((size_t)0)
+#define GPT_STATIC_OFF_ACCU     (GPT_STATIC_OFF_RAY + 32 * GPT_STATIC_P)
+#define GPT_STATIC_OFF_LSUM     (GPT_STATIC_OFF_ACCU + 16 * GPT_STATIC_P)
+#define GPT_STATIC_OFF_HIT      (GPT_STATIC_OFF_LSUM + 16 * GPT_STATIC_X)
+#define GPT_STATIC_OFF_MASK     (GPT_STATIC_OFF_HIT + 8 * GPT_STATIC_P)
+#define GPT_STATIC_OFF_Q0       (GPT_STATIC_OFF_MASK + 4 * GPT_STATIC_P)
+#define GPT_STATIC_OFF_Q1       (GPT_STATIC_OFF_Q0 + 4 * GPT_STATIC_P)
+#define GPT_STATIC_OFF_COUNTERS (GPT_STATIC_OFF_Q1 + 4 * GPT_STATIC_P)
+#define GPT_STATIC_COUNTER_BYTES ((size_t)4096)
+#define GPT_STATIC_SCRATCH_BYTES (GPT_STATIC_OFF_COUNTERS + GPT_STATIC_COUNTER_BYTES)
+static_assert(GPT_STATIC_MAX_PATHS % 64 == 0 && GPT_STATIC_MAX_PIXELS % 16 == 0, "sub-array offsets must stay 256-byte aligned");
+static_assert(2 * (GPT_STATIC_MAX_DEPTH + 1) * sizeof(unsigned int) <= GPT_STATIC_COUNTER_BYTES, "counter block too small for the depth limit");
+
+static __device__ __align__(256) unsigned char g_static_scratch[GPT_STATIC_SCRATCH_BYTES];
+
+#define GPT_STATIC_MAX_DEVICES 64
+static unsigned char* g_static_base[GPT_STATIC_MAX_DEVICES];      // device address of g_static_scratch on each device, nullptr = not asked yet
+static std::mutex g_static_mutex;
+
+// device address of the array on `device`, which must be the current device; nullptr + *err on failure
+static unsigned char* static_scratch_base(int device, cudaError_t* err)
+{
+    *err = cudaSuccess;
+    if (device < 0 || device >= GPT_STATIC_MAX_DEVICES) { *err = cudaErrorInvalidDevice; return nullptr; }
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_base[device]) {
+        void* ptr = nullptr;
+        *err = cudaGetSymbolAddress(&ptr, g_static_scratch);
+        if (*err != cudaSuccess || !ptr) { if (*err == cudaSuccess) *err = cudaErrorInvalidSymbol; return nullptr; }
+        g_static_base[device] = static_cast<unsigned char*>(ptr);
+    }
+    return g_static_base[device];
+}
+
+extern "C" int gpt_render_static(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_t seed, uint64_t sample_begin,
+                                 uint32_t sample_count, gpt_stream stream)
+{
+    if (!c || !info || !accum_f4) return GPT_ERR_INVALID;
+    if (sample_count == 0) return GPT_OK;
+    CU(c, cudaSetDevice(c->device));
+    char buf[256];
+    const long long n_pix = (long long)info->width * (long long)info->height;
+    if (info->width < 2 || info->height < 2 || n_pix > (long long)GPT_STATIC_MAX_PIXELS) {
+        snprintf(buf, sizeof(buf), "gpt_render_static: frame of %d x %d pixels is outside the static scratch (2 x 2 .. %d pixels = GPT_STATIC_MAX_PIXELS); use gpt_render",
+                 info->width, info->height, (int)GPT_STATIC_MAX_PIXELS);
+        return fail(c, GPT_ERR_INVALID, buf);
+    }
+    if (info->depth > GPT_STATIC_MAX_DEPTH) {
+        snprintf(buf, sizeof(buf), "gpt_render_static: depth %u is beyond GPT_STATIC_MAX_DEPTH = %d; use gpt_render", info->depth, (int)GPT_STATIC_MAX_DEPTH);
+        return fail(c, GPT_ERR_INVALID, buf);
+    }
+    if (!c->has_scene) return fail(c, GPT_ERR_NO_SCENE, "gpt_render_static: no uploaded scene (gpt_upload_scene is the set-up call; BVH pointers in kernelInfo are not packed here, that allocates)");
+    RenderParams p;
+    int rc = make_params(c, info, seed, &p); if (rc) return rc;
+    // the scene as uploaded; the 4-wide tree only if an earlier call already built it (building it allocates), never a trial
+    DevScene sc;
+    sc.nodes = c->nodes; sc.tris = c->tris; sc.n_nodes = c->n_nodes; sc.n_tris = c->n_tris;
+    sc.wnodes = (c->wnodes && current_wide(c)) ? c->wnodes : nullptr;
+    sc.spheres = c->spheres; sc.n_spheres = c->n_spheres;
+    sc.boxes = c->boxes; sc.n_boxes = c->n_boxes;
+    sc.tri_mats = c->tri_mats; sc.face_mat = c->face_mat; sc.n_tri_mats = c->n_tri_mats; sc.n_faces = c->n_faces;
+    if (info->sphereTex && info->numSpheres) {        // read live from the caller's array, as gpt_render does (tracer.cu:39)
+        if (info->numSpheres > (1u << 20)) return fail(c, GPT_ERR_INVALID, "numSpheres out of range");
+        sc.spheres = reinterpret_cast<const float*>(info->sphereTex); sc.n_spheres = (int)info->numSpheres;
+    }
+    cudaError_t e;
+    unsigned char* base = static_scratch_base(c->device, &e);
+    if (!base) return fail(c, GPT_ERR_CUDA, "gpt_render_static: cudaGetSymbolAddress(g_static_scratch)", e);
+    WaveBuffers wb = {};
+    wb.ray = reinterpret_cast<float4*>(base + GPT_STATIC_OFF_RAY);
+    wb.accu = reinterpret_cast<float4*>(base + GPT_STATIC_OFF_ACCU);
+    wb.lsum = reinterpret_cast<float4*>(base + GPT_STATIC_OFF_LSUM);
+    wb.hit = reinterpret_cast<int2*>(base + GPT_STATIC_OFF_HIT);
+    wb.mask_z = reinterpret_cast<float*>(base + GPT_STATIC_OFF_MASK);
+    wb.queue[0] = reinterpret_cast<uint32_t*>(base + GPT_STATIC_OFF_Q0);
+    wb.queue[1] = reinterpret_cast<uint32_t*>(base + GPT_STATIC_OFF_Q1);
+    wb.counters = reinterpret_cast<unsigned int*>(base + GPT_STATIC_OFF_COUNTERS);
+    wb.capacity = GPT_STATIC_P;                       // calls of more paths run as several waves (gptk_render_wavefront)
+    if (!c->wave_cfg.ready) gptk_wave_launch_cfg(&c->wave_cfg, c->sm_count);
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps the last call's contents (possibly of a call that failed half-way): the counters must start at zero
+    CU(c, cudaMemsetAsync(wb.counters, 0, gptk_wave_counter_count(p.depth) * sizeof(unsigned int), st));
+    e = gptk_render_wavefront(sc, p, wb, c->wave_cfg, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count,
+                              c->stats, st, &c->launches, nullptr);
+    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "gpt_render_static: launch", e);
+    return GPT_OK;
+}

@@ -224,6 +224,28 @@ GPT_API int gpt_invalidate_scene(gpt_ctx* ctx);
 GPT_API int gpt_render(gpt_ctx* ctx, const gpt_kernel_info* info, float* accum_f4,
                        uint64_t seed, uint64_t sample_begin, uint32_t sample_count, gpt_stream stream);
 
+/* gpt_render without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same contract, same
+ * samples and bit-identical sums as gpt_render on the wavefront pipeline, but the pipeline's scratch (per-path state of one wave,
+ * per-pixel sums, queue counters) is a fixed file-scope device array inside the library instead of buffers grown on demand: 21 MiB
+ * that EVERY GPU that loads the library holds until the process exits.  Limits, checked on entry (GPT_ERR_INVALID and a message
+ * from gpt_last_error_string beyond them; use gpt_render there):
+ *     info->width * info->height <= GPT_STATIC_MAX_PIXELS (262 144, e.g. 512 x 512);  info->depth <= GPT_STATIC_MAX_DEPTH (64);
+ *     any sample_count: calls of more than GPT_STATIC_MAX_PATHS (262 144) paths run as several waves.
+ * The scene must have been uploaded before (gpt_upload_scene / gpt_set_triangle_materials are the set-up calls and do allocate);
+ * BVH pointers in info->bvhData are ignored (packing them allocates), info->sphereTex is read live as in gpt_render.  The binary
+ * tree is traversed unless an earlier gpt_render call already built the 4-wide tree and chose it; no timed trial, no ray
+ * re-ordering, no per-kernel timing.  The call itself makes no cudaMalloc / cudaFree and never synchronises; the first call on
+ * each device resolves the array's device address (cudaGetSymbolAddress), so make one call before capturing.
+ * SHARED STATE: all calls on a device share the array, whichever context they come through.  It keeps the last call's contents;
+ * what must start at zero is cleared on `stream` at the start of every call.  Calls that overlap on the GPU (two streams, or two
+ * host threads) race on it: serialise them on one stream. */
+#define GPT_STATIC_MAX_PIXELS (256 * 1024)
+#define GPT_STATIC_MAX_PATHS  (256 * 1024)
+#define GPT_STATIC_MAX_DEPTH  64
+GPT_API int gpt_render_static(gpt_ctx* ctx, const gpt_kernel_info* info, float* accum_f4,
+                              uint64_t seed, uint64_t sample_begin, uint32_t sample_count, gpt_stream stream);
+
 /* mean = sum/count, clamp [0,1], pack like tracer.cu:394-398.  Either output may be NULL. */
 GPT_API int gpt_resolve(gpt_ctx* ctx, const float* accum_f4, int width, int height,
                         uint32_t* out_rgba8, float* out_rgb_f32, gpt_stream stream);
