@@ -649,7 +649,7 @@ def run_ours(args):
             # dominant kernel: the BVH traversal.  Its algorithmic bytes are the traversal terms of SURVEY 8-d's formula
             # (nodes, triangles, terminators, index remap); the 44 B x spheres term belongs to k_wf_shade.
             k_total_ms, n_ext = ktimes["extend"]
-            kname, k_avg_ms, rays_per_launch, k_bytes_per_ray = "k_wf_extend_" + os.environ.get("GPT_WF_EXTEND", "pq"), k_total_ms / n_ext, float(st.rays) / n_ext, bpr_trav
+            kname, k_avg_ms, rays_per_launch, k_bytes_per_ray = "k_wf_extend_ww", k_total_ms / n_ext, float(st.rays) / n_ext, bpr_trav
         achieved = k_bytes_per_ray * rays_per_launch / (k_avg_ms * 1e-3) / 1e9
         ext_ms, shade_ms = ktimes["extend"][0], ktimes["shade"][0]
         dram_launch = fcls.get("extend", {}).get("dram_bytes_per_ray")
@@ -658,7 +658,7 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, world),
-            "run": {"pipeline": args.pipeline, "extend_schedule": os.environ.get("GPT_WF_EXTEND", "pq (pooled leaf phases)"),
+            "run": {"pipeline": args.pipeline, "extend_schedule": "ww (persistent warps, while-while, per-lane node and leaf loops)",
                     "collective": "none" if world == 1 else ("none on the data path: root reads the peers' float4 frames over NVLink inside the fused "
                                   "reduce+accumulate+resolve kernel (CUDA IPC) on a side stream; one 4-byte NCCL all_reduce per step as a stream-ordered barrier"
                                   if peer is not None else "1 NCCL reduce(float4 accum) per step"),

@@ -49,7 +49,7 @@ def run(name, v, f, W, H, spp_total, mat, per_gpu=16):
         torch.cuda.synchronize(dev)
         t_build = time.time() - t0
         scratch = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
-        for r in range(7):                                  # warm-up + per-scene trial, not part of the image
+        for r in range(10):                                 # warm-up + per-scene trial (up to nine calls), not part of the image
             ctx.render(info, scratch, 99, 10_000_000 + r * per_gpu, per_gpu, stream.cuda_stream)
         del scratch
         total = torch.zeros(H, W, 4, dtype=torch.float32, device=dev) if rank == 0 else None
