@@ -622,6 +622,8 @@ def run_ours(args):
             dist.all_reduce(r2)
         e2e_rays = float(r2.item())
     sampler.stop_flag = True
+    if rank == 0:
+        sampler.join(timeout=8)          # a query started inside a short timed region is allowed to finish: at least one sample
 
     if rank == 0:
         peaks = {}

@@ -163,7 +163,7 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
         if (__ballot_sync(GPT_FULL_MASK, active) == 0u) break;      // nothing armed: queue exhausted
         if (active) {
             while (trav_wants_node(ts)) {
-                if (WIDE) node4_step(sc.wnodes, ts, stack); else node_step(sc.nodes, ts, stack);
+                if (WIDE) node4_step(sc.wnodes, ts, stack, GPT_PF_LEAF ? sc.tris : nullptr); else node_step(sc.nodes, ts, stack, GPT_PF_LEAF ? sc.tris : nullptr);
                 // reference policy (node_k = 1, cudaUtils.h:385-391): descend until every lane still in the loop holds a
                 // leaf.  node_k = k leaves as soon as fewer than k lanes lack a leaf -- they resume after the leaf phase --
                 // instead of making the whole warp wait for one or two stragglers (k = 2..3: -3 % extend time; k >= 8 loses)
