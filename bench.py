@@ -401,8 +401,10 @@ def config_records(gpt, torch, local, args, peaks, hbm, flush):
                 ctx.upload_built(built, sph)
                 rec["tree"] = "device-built (gpt_build_bvh): depth %d, %.1f ms" % (built.depth, built.build_ms)
             acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
-            for w in range(10):                               # buffers + the per-scene trial (<= 9 calls)
+            for w in range(16):                               # buffers + the per-scene trial (<= 12 calls)
                 ctx.render(info, acc, 0, 1_000_000 + w * spp, spp)
+                if w >= 2 and not ctx.trial_info()[0]:
+                    break
             torch.cuda.synchronize()
             ctx.reset_stats()
             reps = 3
@@ -417,7 +419,8 @@ def config_records(gpt, torch, local, args, peaks, hbm, flush):
             st, kt = ctx.stats(), ctx.kernel_times()
             rays = float(st.rays) / reps
             rec.update({"value": rays / ms / 1e3, "unit": "Mrays/s", "ms_per_frame": ms, "rays_per_frame": rays,
-                        "tree_in_use": "4-wide" if ctx.wide_info()[0] else "binary", "ray_reordering": ctx.reorder_info()[0],
+                        "tree_in_use": "rebuilt" if ctx.rebuild_info()["state"] == 1 else ("4-wide" if ctx.wide_info()[0] else "binary"),
+                        "rebuilt_tree": ctx.rebuild_info(), "trial_ns_per_ray": ctx.trial_info()[1], "ray_reordering": ctx.reorder_info()[0],
                         "kernel_class_ms": {k: v[0] / reps for k, v in kt.items() if v[1]}})
             ab = load_algo_bytes(name)
             if ab:
@@ -581,6 +584,32 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    def finish_trial():
+        """The per-scene trial (the tree as uploaded against the rebuilt one, gpt_rebuild_info) belongs in front of the timed region:
+        its calls synchronise.  Every rank runs the same number of calls; if the ranks' timings disagree about the tree (they would
+        then resolve t-ties differently and reduce_check would see it) all ranks fall back to the tree as uploaded."""
+        n = 0
+        while n < 16:
+            pend = torch.tensor([1.0 if ctx.trial_info()[0] else 0.0], device=dev)
+            if dist is not None:
+                dist.all_reduce(pend, op=dist.ReduceOp.MAX)
+            if float(pend.item()) == 0.0:
+                break
+            step(100000 + n)
+            n += 1
+        sync_all()
+        use = torch.tensor([float(ctx.rebuild_info()["state"] == 1)], device=dev)
+        lo, hi = use.clone(), use.clone()
+        if dist is not None:
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        agreed = float(lo.item()) == float(hi.item())
+        if not agreed:
+            ctx.set_flags(flags | gpt.FLAG_KEEP_TREE)
+        return {"trial_calls": n, "ranks_agreed": agreed, "in_use": "rebuilt" if (agreed and float(hi.item()) == 1.0) else "as uploaded",
+                "rebuilt": ctx.rebuild_info(), "trial_ns_per_ray_binary_wide_sorted": ctx.trial_info()[1]}
+
+    tree_rec = finish_trial()
     check = reduce_check() if world > 1 else None
     for i in range(args.warmup):
         step(i)
@@ -660,7 +689,7 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, world),
-            "run": {"pipeline": args.pipeline, "extend_schedule": "ww (persistent warps, while-while, per-lane node and leaf loops)",
+            "run": {"pipeline": args.pipeline, "extend_schedule": "ww (persistent warps, while-while, per-lane node and leaf loops)", "tree": tree_rec,
                     "collective": "none" if world == 1 else ("none on the data path: root reads the peers' float4 frames over NVLink inside the fused "
                                   "reduce+accumulate+resolve kernel (CUDA IPC) on a side stream; one 4-byte NCCL all_reduce per step as a stream-ordered barrier"
                                   if peer is not None else "1 NCCL reduce(float4 accum) per step"),
@@ -760,13 +789,38 @@ def run_ours(args):
             except Exception as ex:
                 line["device_built_tree"] = {"unavailable": repr(ex)}
         if world == 1 and args.pipeline != "mega":
+            # the same steps on the BVH exactly as uploaded (GPT_FLAG_KEEP_TREE): what the rebuilt tree is worth, and the figure to
+            # compare with earlier rounds' headline
+            try:
+                with gpt.Context(local, gpt.FLAG_KEEP_TREE) as c4:
+                    c4.upload_scene(sc["nodes"], sc["tris"], sc["indices"], sph)
+                    for i in range(max(3, args.warmup)):
+                        c4.render(info, frame, args.seed, i * SPP, SPP, stream.cuda_stream)
+                    torch.cuda.synchronize(dev)
+                    c4.reset_stats()
+                    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    t0.record(stream)
+                    for i in range(args.steps):
+                        flush.zero_()
+                        c4.render(info, frame, args.seed, (i + 8) * SPP, SPP, stream.cuda_stream)
+                        c4.resolve(frame, W, H, rgba, None, stream.cuda_stream)
+                    t1.record(stream)
+                    torch.cuda.synchronize(dev)
+                    ms4 = t0.elapsed_time(t1)
+                    line["tree_as_uploaded"] = {"value": float(c4.stats().rays) / (ms4 * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms4 / args.steps,
+                                                "what": "GPT_FLAG_KEEP_TREE: the reference's SBVH traversed as uploaded (no rebuilt tree); same steps"}
+            except Exception as ex:
+                line["tree_as_uploaded"] = {"unavailable": repr(ex)}
+        if world == 1 and args.pipeline != "mega":
             # opt-in GPT_FLAG_FAST (MUFU shading arithmetic; statistical parity, tests/test_gpu_refkernel.py "/FAST" cases): same steps
             try:
                 with gpt.Context(local, gpt.FLAG_FAST) as c3:
                     c3.upload_scene(sc["nodes"], sc["tris"], sc["indices"], sph)
                     f2 = torch.zeros_like(frame)
-                    for i in range(max(3, args.warmup)):
+                    for i in range(16):                                   # warm-up + the per-scene trial
                         c3.render(info, f2, args.seed, i * SPP, SPP, stream.cuda_stream)
+                        if i + 1 >= max(3, args.warmup) and not c3.trial_info()[0]:
+                            break
                     torch.cuda.synchronize(dev)
                     c3.reset_stats()
                     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

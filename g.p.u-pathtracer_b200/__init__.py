@@ -32,6 +32,7 @@ FLAG_WAVEFRONT = 1 << 7       # always the wavefront pipeline (default: megakern
 FLAG_BUILD_LBVH = 1 << 8      # build_bvh: Morton radix tree instead of PLOC clustering
 FLAG_FAST = 1 << 10           # opt-in fast shading arithmetic (statistical parity, not bit-exact)
 FLAG_NO_TRIAL = 1 << 9        # no timed per-scene trial: render calls never synchronise (graph capture, strict asynchrony)
+FLAG_KEEP_TREE = 1 << 11      # traverse the tree exactly as uploaded: no second tree from the library's own builder
 STATIC_MAX_PIXELS = 256 * 1024   # gpt_render_static (include/gpt.h GPT_STATIC_*): frame pixels, paths per wave, depth
 STATIC_MAX_PATHS = 256 * 1024
 STATIC_MAX_DEPTH = 64
@@ -105,7 +106,7 @@ assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 # every symbol include/gpt.h declares (tests check the library exports each one)
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
            "gpt_upload_scene", "gpt_launch", "gpt_invalidate_scene", "gpt_render", "gpt_render_static", "gpt_resolve", "gpt_render_frame_host",
-           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_measure_peaks", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info",
+           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_measure_peaks", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info", "gpt_rebuild_info",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
            "gpt_reduce_resolve_ptrs", "gpt_frame_free",
@@ -149,6 +150,7 @@ def load_library():
     L.gpt_wide_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.gpt_reorder_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.gpt_trial_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+    L.gpt_rebuild_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_float)]
     L.gpt_build_bvh.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.POINTER(BuiltBVH)]
     L.gpt_free_bvh.argtypes = [C.c_void_p, C.POINTER(BuiltBVH)]
     L.gpt_copy_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
@@ -504,6 +506,13 @@ class Context:
         ns = (C.c_double * 3)()
         self._ck(self._L.gpt_trial_info(self._h, C.byref(pend), ns), "gpt_trial_info")
         return bool(pend.value), [ns[0], ns[1], ns[2]]
+
+    def rebuild_info(self):
+        """the rebuilt tree (gpt_rebuild_info): {state: 1 in use / 0 not / -1 on trial, inner_nodes, depth, ns_per_ray, build_ms}"""
+        st, nn, dp = C.c_int(0), C.c_int(0), C.c_int(0)
+        ns, ms = C.c_double(0.0), C.c_float(0.0)
+        self._ck(self._L.gpt_rebuild_info(self._h, C.byref(st), C.byref(nn), C.byref(dp), C.byref(ns), C.byref(ms)), "gpt_rebuild_info")
+        return {"state": st.value, "inner_nodes": nn.value, "depth": dp.value, "ns_per_ray": ns.value, "build_ms": ms.value}
 
     def kernel_times(self):
         """{class name: (ms, launches)} since the last reset_stats (needs FLAG_TIME_KERNELS)."""

@@ -24,9 +24,13 @@ struct gpt_ctx {
     bool has_scene = false;
     // N3: 4-wide quantised tree over the packed binary one, built on first use (gpt_wide.cu)
     float4* wnodes = nullptr; int n_wide = 0, wide_levels = 0; bool wide_tried = false;
+    // a second packed tree over the same triangle references, made by the device builder when a reference-layout tree is packed
+    // (gptk_rebuild); own_tree = the uploaded arrays came from gpt_build_bvh of this context (nothing to gain from rebuilding)
+    float4* alt_nodes = nullptr; float4* alt_tris = nullptr; int alt_n_nodes = 0, alt_n_tris = 0, alt_depth = 0; float alt_build_ms = 0.0f;
+    bool own_tree = false; const void* built_nodes[8] = {}; int built_next = 0;
     // per-scene choice of traversal structure and ray order (traversal_plan): flags and environment win, else a timed trial
-    int tune_step = 0; bool tune_done = false; bool tuned_wide = false, tuned_sort = false;
-    double tune_ns[3] = {0.0, 0.0, 0.0};          // ns per ray: binary tree / wide tree in path order, chosen tree re-ordered
+    int tune_step = 0; bool tune_done = false; int tuned_tree = 0; bool tuned_sort = false;      // tree ids: 0 uploaded binary, 1 its 4-wide collapse, 2 rebuilt
+    double tune_ns[4] = {0.0, 0.0, 0.0, 0.0};     // ns per ray: binary tree / wide tree in path order, chosen tree re-ordered, rebuilt tree in path order
     // identity of the reference arrays the packed BVH was built from (gpt_launch re-packs on change)
     const void* src_nodes = nullptr; const void* src_tris = nullptr; const void* src_idx = nullptr;
     size_t src_n_nodes = 0, src_n_tris = 0, src_n_idx = 0;
@@ -92,13 +96,19 @@ int gpt_create(gpt_ctx** out, int device)
 static void free_wide(gpt_ctx* c)
 {
     cudaFree(c->wnodes); c->wnodes = nullptr; c->n_wide = 0; c->wide_levels = 0; c->wide_tried = false;
-    c->tune_step = 0; c->tune_done = false; c->tuned_wide = c->tuned_sort = false;      // a new tree: the questions are open again
-    c->tune_ns[0] = c->tune_ns[1] = c->tune_ns[2] = 0.0;
+    c->tune_step = 0; c->tune_done = false; c->tuned_tree = 0; c->tuned_sort = false;      // a new tree: the questions are open again
+    c->tune_ns[0] = c->tune_ns[1] = c->tune_ns[2] = c->tune_ns[3] = 0.0;
+}
+
+static void free_alt(gpt_ctx* c)
+{
+    cudaFree(c->alt_nodes); cudaFree(c->alt_tris); c->alt_nodes = c->alt_tris = nullptr;
+    c->alt_n_nodes = c->alt_n_tris = c->alt_depth = 0; c->alt_build_ms = 0.0f;
 }
 
 static void free_scene(gpt_ctx* c)
 {
-    free_wide(c);
+    free_wide(c); free_alt(c);
     cudaFree(c->nodes); cudaFree(c->tris); cudaFree(c->spheres); cudaFree(c->boxes);
     c->nodes = c->tris = nullptr; c->spheres = c->boxes = nullptr;
     c->n_nodes = c->n_tris = c->n_spheres = c->n_boxes = 0;
@@ -161,6 +171,10 @@ static const bool k_env_no_trial = []{ const char* e = getenv("GPT_NO_TRIAL"); r
 static const long long k_env_wide_min = []{ const char* e = getenv("GPT_WIDE_MIN_TRIS"); return e ? atoll(e) : -2ll; }();   // -2 = unset
 static const int k_env_sort = []{ const char* e = getenv("GPT_WF_SORT"); return e ? atoi(e) : -1; }();
 static const long long k_env_sort_min = []{ const char* e = getenv("GPT_SORT_MIN_TRIS"); return e ? atoll(e) : -2ll; }();
+// The rebuilt tree (gptk_rebuild): GPT_REBUILD=0 never builds it, =1 always traverses it (where one could be built), unset: built for
+// reference-layout trees of 1 Ki .. 4 Mi packed triangles that do not come from gpt_build_bvh, and put on trial with the others.
+// GPT_FLAG_KEEP_TREE, GPT_FLAG_BINARY_BVH, GPT_FLAG_WIDE_BVH and GPT_FLAG_MEGAKERNEL all mean "the tree as uploaded".
+static const int k_env_rebuild = []{ const char* e = getenv("GPT_REBUILD"); return (e && *e) ? atoi(e) : -1; }();
 
 // Which pipeline: the wavefront pipeline needs ~19 launches per call and each costs ~19 us of launch gap + drain, so below a few
 // hundred thousand paths per call the single-launch megakernel is faster (cornell 512x512, 1 spp, depth 4: 0.17 ms against
@@ -191,33 +205,67 @@ static int sort_choice(const gpt_ctx* c)
     if (c->n_tris < (256 << 10)) return 0;
     return -1;
 }
-// what to use outside a trial call: forced, decided, or the default
-static bool current_wide(const gpt_ctx* c)
+// the rebuilt tree: 0 = not available / not allowed, 1 = forced, -1 = open (trial)
+static int alt_choice(const gpt_ctx* c)
 {
-    const int t = tree_choice(c);
-    return t >= 0 ? t == 1 : (c->tune_done ? c->tuned_wide : c->n_tris >= (1 << 20));
+    if (!c->alt_nodes || (c->flags & (GPT_FLAG_KEEP_TREE | GPT_FLAG_BINARY_BVH | GPT_FLAG_WIDE_BVH | GPT_FLAG_MEGAKERNEL)) || k_env_rebuild == 0) return 0;
+    return k_env_rebuild > 0 ? 1 : -1;
 }
+// the trees a scene may be traversed on (ids: 0 uploaded binary, 1 its 4-wide collapse, 2 rebuilt), in trial order
+static int tree_cands(const gpt_ctx* c, int* ids)
+{
+    const int t = tree_choice(c), a = alt_choice(c);
+    int n = 0;
+    if (a == 1) { ids[n++] = 2; return n; }
+    if (t != 1) ids[n++] = 0;
+    if (t != 0) ids[n++] = 1;
+    if (a < 0) ids[n++] = 2;
+    return n;
+}
+static double tree_ns(const gpt_ctx* c, int id) { return c->tune_ns[id == 2 ? 3 : id]; }
+// the fastest measured candidate; a later candidate must beat the best so far by 2 %
+static int best_tree(const gpt_ctx* c, const int* ids, int n)
+{
+    int best = ids[0];
+    for (int k = 1; k < n; ++k) {
+        const double m = tree_ns(c, ids[k]), b = tree_ns(c, best);
+        if (m > 0.0 && b > 0.0 && m < 0.98 * b) best = ids[k];
+    }
+    return best;
+}
+// what to use outside a trial call: forced, decided, or the default (the wide tree from 1 Mi triangles, else the tree as uploaded)
+static int current_tree(const gpt_ctx* c)
+{
+    int ids[3];
+    const int n = tree_cands(c, ids);
+    if (n == 1) return ids[0];
+    if (c->tune_done) return c->tuned_tree;
+    if (tree_choice(c) < 0 && c->n_tris >= (1 << 20)) return 1;
+    return ids[0];
+}
+static bool current_wide(const gpt_ctx* c) { return current_tree(c) == 1; }
 static bool current_sort(const gpt_ctx* c)
 {
     const int s = sort_choice(c);
     return s >= 0 ? s == 1 : (c->tune_done && c->tuned_sort);
 }
 
-struct TraversalPlan { bool wide; bool sort; bool trial; bool timed; int slot; };     // slot = tune_ns index of a timed call
+struct TraversalPlan { int tree; bool sort; bool trial; bool timed; int slot; };     // slot = tune_ns index of a timed call
 static TraversalPlan traversal_plan(const gpt_ctx* c, size_t n_paths)
 {
-    TraversalPlan pl = {current_wide(c), current_sort(c), false, false, -1};
-    const int t = tree_choice(c), s = sort_choice(c);
-    const int n_tree = t < 0 ? 2 : 1, n_cand = n_tree + (s < 0 ? 1 : 0);
+    TraversalPlan pl = {current_tree(c), current_sort(c), false, false, -1};
+    int ids[3];
+    const int n_tree = tree_cands(c, ids), s = sort_choice(c);
+    const int n_cand = n_tree + (s < 0 ? 1 : 0);
     if (c->tune_done || n_cand < 2 || n_paths < ((size_t)1 << 20) || (c->flags & GPT_FLAG_NO_TRIAL) || k_env_no_trial) return pl;
     const int cand = c->tune_step / 3;
     pl.trial = true; pl.timed = (c->tune_step % 3) != 0;
     if (cand < n_tree) {                                          // a tree candidate, rays in path order
-        pl.wide = t < 0 ? cand == 1 : t == 1;
+        pl.tree = ids[cand];
         pl.sort = false;
-        pl.slot = pl.wide ? 1 : 0;
-    } else {                                                      // the faster tree, re-ordered
-        pl.wide = t < 0 ? (c->tune_ns[1] > 0.0 && c->tune_ns[1] < 0.98 * c->tune_ns[0]) : t == 1;
+        pl.slot = pl.tree == 2 ? 3 : pl.tree;
+    } else {                                                      // the fastest tree, re-ordered
+        pl.tree = best_tree(c, ids, n_tree);
         pl.sort = true;
         pl.slot = 2;
     }
@@ -225,13 +273,22 @@ static TraversalPlan traversal_plan(const gpt_ctx* c, size_t n_paths)
 }
 static void trial_advance(gpt_ctx* c)
 {
-    const int t = tree_choice(c), s = sort_choice(c);
-    const int n_tree = t < 0 ? 2 : 1, n_cand = n_tree + (s < 0 ? 1 : 0);
+    int ids[3];
+    const int n_tree = tree_cands(c, ids), s = sort_choice(c);
+    const int n_cand = n_tree + (s < 0 ? 1 : 0);
     if (++c->tune_step < 3 * n_cand) return;
     c->tune_done = true;
-    c->tuned_wide = t < 0 ? (c->tune_ns[1] > 0.0 && c->tune_ns[0] > 0.0 && c->tune_ns[1] < 0.98 * c->tune_ns[0]) : t == 1;
-    const double path = c->tune_ns[c->tuned_wide ? 1 : 0];
+    c->tuned_tree = best_tree(c, ids, n_tree);
+    const double path = tree_ns(c, c->tuned_tree);
     c->tuned_sort = s < 0 && c->tune_ns[2] > 0.0 && path > 0.0 && c->tune_ns[2] < 0.97 * path;
+}
+// point a DevScene at one of the context's trees (1 without a built wide tree falls back to the binary tree it was collapsed from)
+static void set_tree(const gpt_ctx* c, DevScene* sc, int tree)
+{
+    const bool alt = tree == 2 && c->alt_nodes;
+    sc->nodes = alt ? c->alt_nodes : c->nodes; sc->tris = alt ? c->alt_tris : c->tris;
+    sc->n_nodes = alt ? c->alt_n_nodes : c->n_nodes; sc->n_tris = alt ? c->alt_n_tris : c->n_tris;
+    sc->wnodes = (tree == 1) ? c->wnodes : nullptr;
 }
 
 static int ensure_sort(gpt_ctx* c, bool want)
@@ -254,7 +311,7 @@ static int render_wavefront(gpt_ctx* c, const DevScene& sc_in, const RenderParam
     const TraversalPlan pl = traversal_plan(c, (size_t)p.width * p.height * sample_count);
     rc = ensure_sort(c, pl.sort); if (rc) return rc;
     DevScene sc = sc_in;
-    sc.wnodes = pl.wide ? c->wnodes : nullptr;
+    set_tree(c, &sc, pl.tree);
     WaveBuffers wb = c->wave;
     if (!pl.sort) wb.sort_vals = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -319,7 +376,9 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
                                 const int32_t* idx, size_t n_idx)
 {
     cudaFree(c->nodes); cudaFree(c->tris); c->nodes = c->tris = nullptr; c->n_nodes = c->n_tris = 0;
-    free_wide(c);
+    free_wide(c); free_alt(c);
+    c->own_tree = false;
+    for (const void* b : c->built_nodes) if (b && b == nodes) c->own_tree = true;
     if (n_node_vec4 == 0 || !nodes) return GPT_OK;     // sphere-only scene
     if (!tris || !idx) return fail(c, GPT_ERR_INVALID, "BVH nodes given without triangle / index arrays");
     RepackResult r;
@@ -333,6 +392,16 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
         return fail(c, GPT_ERR_LAYOUT, buf);
     }
     c->nodes = r.nodes; c->tris = r.tris; c->n_nodes = r.n_nodes; c->n_tris = r.n_tris; c->tree_depth = r.depth;
+    // the same triangle references under a tree of this library's own builder (see k_env_rebuild); failure just leaves the one above
+    const bool wanted = !c->own_tree && k_env_rebuild != 0 && !(c->flags & (GPT_FLAG_KEEP_TREE | GPT_FLAG_BINARY_BVH | GPT_FLAG_WIDE_BVH | GPT_FLAG_MEGAKERNEL)) &&
+                        (k_env_rebuild > 0 ? c->n_tris >= 2 : (c->n_tris >= (1 << 10) && c->n_tris <= (4 << 20)));
+    if (wanted) {
+        static const int k_env_ploc = []{ const char* v = getenv("GPT_PLOC_RADIUS"); return (v && *v) ? atoi(v) : 24; }();
+        RepackResult a; int status = 0; float ms = 0.0f;
+        e = gptk_rebuild(c->tris, c->n_tris, (const float4*)tris, 8, (c->flags & GPT_FLAG_BUILD_LBVH) ? 0 : k_env_ploc, &a, &status, &ms, &c->launches, 0);
+        if (e != cudaSuccess) cudaGetLastError();
+        else if (status == 0) { c->alt_nodes = a.nodes; c->alt_tris = a.tris; c->alt_n_nodes = a.n_nodes; c->alt_n_tris = a.n_tris; c->alt_depth = a.depth; c->alt_build_ms = ms; }
+    }
     return GPT_OK;
 }
 
@@ -431,6 +500,7 @@ int gpt_build_bvh(gpt_ctx* c, const float* verts, size_t n_verts, const int32_t*
         char buf[128]; snprintf(buf, sizeof(buf), "gpt_build_bvh: %s", why[r.status < 6 ? r.status : 0]);
         return fail(c, r.status == 3 || r.status == 4 ? GPT_ERR_LAYOUT : GPT_ERR_INVALID, buf);
     }
+    c->built_nodes[c->built_next] = r.nodes; c->built_next = (c->built_next + 1) % 8;      // uploading these arrays needs no rebuild
     out->bvh.dev_triNode = r.nodes; out->bvh.triNodeSize = r.n_node_vec4;
     out->bvh.dev_triPtr = r.tris; out->bvh.triSize = r.n_tri_vec4;
     out->bvh.dev_triIndicesPtr = r.indices; out->bvh.triIndicesSize = r.n_indices;
@@ -515,8 +585,7 @@ static void ensure_wide(gpt_ctx* c)
 static void uploaded_scene(gpt_ctx* c, DevScene* sc)
 {
     ensure_wide(c);
-    sc->wnodes = current_wide(c) ? c->wnodes : nullptr;          // render calls refine this per call (render_wavefront)
-    sc->nodes = c->nodes; sc->tris = c->tris; sc->n_nodes = c->n_nodes; sc->n_tris = c->n_tris;
+    set_tree(c, sc, current_tree(c));                            // render calls refine this per call (render_wavefront)
     sc->spheres = c->spheres; sc->n_spheres = c->n_spheres;
     sc->boxes = c->boxes; sc->n_boxes = c->n_boxes;
     sc->tri_mats = c->tri_mats; sc->face_mat = c->face_mat; sc->n_tri_mats = c->n_tri_mats; sc->n_faces = c->n_faces;
@@ -527,8 +596,20 @@ int gpt_reorder_info(gpt_ctx* c, int* state, double* ns_per_ray_path_order, doub
     if (!c) return GPT_ERR_INVALID;
     const TraversalPlan pl = traversal_plan(c, (size_t)1 << 30);
     if (state) *state = (pl.trial && sort_choice(c) < 0) ? -1 : (current_sort(c) ? 1 : 0);
-    if (ns_per_ray_path_order) *ns_per_ray_path_order = c->tune_ns[(c->tune_done ? c->tuned_wide : current_wide(c)) ? 1 : 0];
+    if (ns_per_ray_path_order) *ns_per_ray_path_order = tree_ns(c, c->tune_done ? c->tuned_tree : current_tree(c));
     if (ns_per_ray_reordered) *ns_per_ray_reordered = c->tune_ns[2];
+    return GPT_OK;
+}
+
+int gpt_rebuild_info(gpt_ctx* c, int* state, int* n_inner_nodes, int* depth, double* ns_per_ray, float* build_ms)
+{
+    if (!c) return GPT_ERR_INVALID;
+    const int a = alt_choice(c);
+    if (state) *state = a == 0 ? 0 : ((a < 0 && traversal_plan(c, (size_t)1 << 30).trial) ? -1 : (current_tree(c) == 2 ? 1 : 0));
+    if (n_inner_nodes) *n_inner_nodes = c->alt_n_nodes;
+    if (depth) *depth = c->alt_depth;
+    if (ns_per_ray) *ns_per_ray = c->tune_ns[3];
+    if (build_ms) *build_ms = c->alt_build_ms;
     return GPT_OK;
 }
 
@@ -889,10 +970,9 @@ extern "C" int gpt_render_static(gpt_ctx* c, const gpt_kernel_info* info, float*
     if (!c->has_scene) return fail(c, GPT_ERR_NO_SCENE, "gpt_render_static: no uploaded scene (gpt_upload_scene is the set-up call; BVH pointers in kernelInfo are not packed here, that allocates)");
     RenderParams p;
     int rc = make_params(c, info, seed, &p); if (rc) return rc;
-    // the scene as uploaded; the 4-wide tree only if an earlier call already built it (building it allocates), never a trial
+    // the tree in use (uploaded / rebuilt at upload / 4-wide); the 4-wide tree only if an earlier call already built it (building it allocates), never a trial
     DevScene sc;
-    sc.nodes = c->nodes; sc.tris = c->tris; sc.n_nodes = c->n_nodes; sc.n_tris = c->n_tris;
-    sc.wnodes = (c->wnodes && current_wide(c)) ? c->wnodes : nullptr;
+    { const int tree = current_tree(c); set_tree(c, &sc, (tree == 1 && !c->wnodes) ? 0 : tree); }
     sc.spheres = c->spheres; sc.n_spheres = c->n_spheres;
     sc.boxes = c->boxes; sc.n_boxes = c->n_boxes;
     sc.tri_mats = c->tri_mats; sc.face_mat = c->face_mat; sc.n_tri_mats = c->n_tri_mats; sc.n_faces = c->n_faces;

@@ -59,6 +59,12 @@ struct RepackResult { float4* nodes; float4* tris; int n_nodes; int n_tris; int 
 cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float4* ref_tris, size_t n_tri_vec4,
                         const int* ref_indices, size_t n_indices, RepackResult* out, cudaStream_t st);
 
+// A second packed tree over the same triangle references, made by the device builder below from the caller's exact vertices
+// (gpt_repack.cu).  packed_tris / n_tris = the first packing; ref_tris = the caller's triangle array it was packed from.
+// *status: 0 ok, 1 builder refused / too deep, 2 internal mismatch, 3 fewer than 2 triangles.  Synchronises `st`.
+cudaError_t gptk_rebuild(const float4* packed_tris, int n_tris, const float4* ref_tris, int max_leaf, int ploc_radius,
+                         RepackResult* out, int* status, float* build_ms, unsigned long long* launches, cudaStream_t st);
+
 // device-side LBVH builder (gpt_build.cu): indexed mesh (device pointers) -> arrays in CudaBVH's compact layout,
 // cudaMalloc'd by the callee.  status: 0 ok, 1 vertex index out of range, 2 non-finite vertex, 3 too large, 4 too deep
 struct BuildResult { float4* nodes; size_t n_node_vec4; float4* tris; size_t n_tri_vec4; int* indices; size_t n_indices;

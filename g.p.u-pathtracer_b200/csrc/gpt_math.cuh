@@ -36,20 +36,6 @@ __device__ __forceinline__ void ldg_node64(const float4* __restrict__ p, float4&
 #endif
 }
 
-// Software prefetch of what a lane will fetch once the warp's node loop has ended (A/B switches, results cannot change):
-// GPT_PF_LEAF = 1 / 2: the first triangle of a leaf when it is postponed, into L1 / L2; GPT_PF_NODE = 1 / 2: the nearest pushed child.
-#ifndef GPT_PF_LEAF
-#define GPT_PF_LEAF 0
-#endif
-#ifndef GPT_PF_NODE
-#define GPT_PF_NODE 0
-#endif
-template <int LEVEL> __device__ __forceinline__ void prefetch_global(const void* p)
-{
-    if (LEVEL == 1) asm volatile("prefetch.global.L1 [%0];" :: "l"(p));
-    if (LEVEL == 2) asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
-}
-
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
 __device__ __forceinline__ f3 add3(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
 __device__ __forceinline__ f3 sub3(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }

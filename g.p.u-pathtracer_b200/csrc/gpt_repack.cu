@@ -160,3 +160,93 @@ fail:
     return e;
 #undef CK
 }
+
+// ---- a second tree over the SAME triangle references, built by this library's own builder (gpt_build.cu) ----------------------
+// The reference's host SBVH is tuned for its own kernel (leaves of up to 8 triangles: 6.5 triangle tests per ray on the bench
+// scene); the while-while extend kernel here is faster on the PLOC tree with SAH-collapsed leaves (+17 % rays/s on the bench scene,
+// +18 % on the 100 k-triangle dragon).  gptk_rebuild makes that tree from what the caller uploaded: every triangle reference the
+// re-pack kept (duplicates of spatial splits included -- the same triangle twice gives the same t and the same face index) goes
+// into the builder as a triangle soup with the caller's exact vertices, the builder's arrays go through the same re-pack, and
+// the face index / caller slot of each packed triangle are restored from the first packing.  Packed rows (v0, v1 - v0, v2 - v0)
+// are bit-identical to the first packing's, so every ray-triangle distance is; only the ORDER in which triangles are met differs,
+// i.e. which of two triangles with bit-equal t wins (the 4-wide tree's caveat).
+__global__ void k_soup(const float4* __restrict__ packed, const int n, const float4* __restrict__ ref_tris, float* __restrict__ verts, int* __restrict__ faces)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int slot = __float_as_int(packed[GPT_TRI_STRIDE * (size_t)i + GPT_TRI_B].w);
+    for (int k = 0; k < 3; ++k) {
+        const float4 v = ref_tris[(size_t)slot + k];
+        verts[9 * (size_t)i + 3 * k] = v.x; verts[9 * (size_t)i + 3 * k + 1] = v.y; verts[9 * (size_t)i + 3 * k + 2] = v.z;
+        faces[3 * (size_t)i + k] = 3 * i + k;
+    }
+}
+
+__global__ void k_restore_ids(float4* __restrict__ alt, const int n_alt, const float4* __restrict__ packed, const int n, int* __restrict__ bad)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_alt) return;
+    const int i = __float_as_int(alt[GPT_TRI_STRIDE * (size_t)j].w);             // soup triangle = index in the first packing
+    if (i < 0 || i >= n) { atomicExch(bad, 1); return; }
+    const float4 a = packed[GPT_TRI_STRIDE * (size_t)i], b = packed[GPT_TRI_STRIDE * (size_t)i + GPT_TRI_B];
+    const float4 ra = alt[GPT_TRI_STRIDE * (size_t)j], rb = alt[GPT_TRI_STRIDE * (size_t)j + GPT_TRI_B];
+    const float4 c = packed[GPT_TRI_STRIDE * (size_t)i + GPT_TRI_B + 1], rc = alt[GPT_TRI_STRIDE * (size_t)j + GPT_TRI_B + 1];
+    // the rows must be the first packing's, bit for bit: that is what makes the two trees give the same distances
+    if (__float_as_uint(a.x) != __float_as_uint(ra.x) || __float_as_uint(a.y) != __float_as_uint(ra.y) || __float_as_uint(a.z) != __float_as_uint(ra.z) ||
+        __float_as_uint(b.x) != __float_as_uint(rb.x) || __float_as_uint(b.y) != __float_as_uint(rb.y) || __float_as_uint(b.z) != __float_as_uint(rb.z) ||
+        __float_as_uint(c.x) != __float_as_uint(rc.x) || __float_as_uint(c.y) != __float_as_uint(rc.y) || __float_as_uint(c.z) != __float_as_uint(rc.z)) {
+        atomicExch(bad, 2); return;
+    }
+    alt[GPT_TRI_STRIDE * (size_t)j].w = a.w;                  // original face index
+    alt[GPT_TRI_STRIDE * (size_t)j + GPT_TRI_B].w = b.w;      // slot in the caller's triangle array
+}
+
+// status: 0 ok (out filled), 1 the builder refused or the tree is too deep, 2 triangles lost or rows differ (internal), 3 too few triangles
+cudaError_t gptk_rebuild(const float4* packed_tris, int n_tris, const float4* ref_tris, int max_leaf, int ploc_radius,
+                         RepackResult* out, int* status, float* build_ms, unsigned long long* launches, cudaStream_t st)
+{
+    *out = RepackResult{}; *status = 3; *build_ms = 0.0f;
+    if (n_tris < 2) return cudaSuccess;
+    float* verts = nullptr; int* faces = nullptr; int* bad = nullptr;
+    BuildResult b = BuildResult{};
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaError_t e;
+    int h_bad = 0;
+#define CK(x) do { e = (x); if (e != cudaSuccess) goto fail; } while (0)
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, st));
+    CK(cudaMalloc(&verts, sizeof(float) * 9 * (size_t)n_tris));
+    CK(cudaMalloc(&faces, sizeof(int) * 3 * (size_t)n_tris));
+    CK(cudaMalloc(&bad, sizeof(int)));
+    CK(cudaMemsetAsync(bad, 0, sizeof(int), st));
+    k_soup<<<(n_tris + 255) / 256, 256, 0, st>>>(packed_tris, n_tris, ref_tris, verts, faces);
+    CK(cudaGetLastError());
+    CK(gptk_build_lbvh(verts, 3 * (size_t)n_tris, faces, (size_t)n_tris, max_leaf, ploc_radius, &b, st));
+    *launches += 1ull + (unsigned long long)b.launches;
+    if (b.status != 0 || !b.nodes) { *status = 1; goto done; }
+    CK(gptk_repack(b.nodes, b.n_node_vec4, b.tris, b.n_tri_vec4, b.indices, b.n_indices, out, st));
+    *launches += 2;
+    if (out->bad_layout || !out->nodes) { *status = 1; goto done; }
+    if (out->n_tris != n_tris) { *status = 2; goto done; }
+    k_restore_ids<<<(n_tris + 255) / 256, 256, 0, st>>>(out->tris, n_tris, packed_tris, n_tris, bad);
+    CK(cudaGetLastError());
+    *launches += 1;
+    CK(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(e1, st));
+    CK(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(build_ms, e0, e1);
+    *status = h_bad ? 2 : 0;
+done:
+    if (*status != 0) { cudaFree(out->nodes); cudaFree(out->tris); *out = RepackResult{}; }
+    cudaFree(verts); cudaFree(faces); cudaFree(bad); cudaFree(b.nodes); cudaFree(b.tris); cudaFree(b.indices);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return cudaSuccess;
+fail:
+    cudaFree(out->nodes); cudaFree(out->tris); *out = RepackResult{};
+    cudaFree(verts); cudaFree(faces); cudaFree(bad); cudaFree(b.nodes); cudaFree(b.tris); cudaFree(b.indices);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    *status = 1;
+    return e;
+#undef CK
+}

@@ -109,19 +109,17 @@ __device__ __forceinline__ int node_next(const float4* __restrict__ nodes, TravS
             int far_child = ch.y;
             if (c1min < c0min) { far_child = next; next = ch.y; }
             ++s.sp; stack[s.sp] = far_child;
-            if (GPT_PF_NODE && far_child >= 0) prefetch_global<GPT_PF_NODE>(nodes + far_child);
         }
     }
     return next;
 }
 
 // One inner-node visit with the reference's leaf handling, cudaUtils.h:305-369.
-__device__ __forceinline__ void node_step(const float4* __restrict__ nodes, TravState& s, int* stack, const float4* __restrict__ tris_pf = nullptr)
+__device__ __forceinline__ void node_step(const float4* __restrict__ nodes, TravState& s, int* stack)
 {
     int next = node_next(nodes, s, stack);
     if (next < 0 && s.leaf >= 0) {           // first leaf: postpone it and keep descending (:362-369)
         s.leaf = next; s.tri_cur = ~next;
-        if (GPT_PF_LEAF && tris_pf) prefetch_global<GPT_PF_LEAF>(tris_pf + GPT_TRI_STRIDE * (size_t)s.tri_cur);
         next = stack[s.sp]; --s.sp;
     }
     s.node = next;
@@ -178,16 +176,15 @@ __device__ __forceinline__ int node4_next(const float4* __restrict__ wn, TravSta
         next = c0;
         if (k3 < inf) { ++s.sp; stack[s.sp] = c3; }
         if (k2 < inf) { ++s.sp; stack[s.sp] = c2; }
-        if (k1 < inf) { ++s.sp; stack[s.sp] = c1; if (GPT_PF_NODE && c1 >= 0) prefetch_global<GPT_PF_NODE>(wn + c1); }
+        if (k1 < inf) { ++s.sp; stack[s.sp] = c1; }
     }
     return next;
 }
-__device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravState& s, int* stack, const float4* __restrict__ tris_pf = nullptr)
+__device__ __forceinline__ void node4_step(const float4* __restrict__ wn, TravState& s, int* stack)
 {
     int next = node4_next(wn, s, stack);
     if (next < 0 && s.leaf >= 0) {           // first leaf: postpone it and keep descending
         s.leaf = next; s.tri_cur = ~next;
-        if (GPT_PF_LEAF && tris_pf) prefetch_global<GPT_PF_LEAF>(tris_pf + GPT_TRI_STRIDE * (size_t)s.tri_cur);
         next = stack[s.sp]; --s.sp;
     }
     s.node = next;

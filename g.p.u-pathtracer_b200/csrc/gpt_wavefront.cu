@@ -163,7 +163,7 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
         if (__ballot_sync(GPT_FULL_MASK, active) == 0u) break;      // nothing armed: queue exhausted
         if (active) {
             while (trav_wants_node(ts)) {
-                if (WIDE) node4_step(sc.wnodes, ts, stack, GPT_PF_LEAF ? sc.tris : nullptr); else node_step(sc.nodes, ts, stack, GPT_PF_LEAF ? sc.tris : nullptr);
+                if (WIDE) node4_step(sc.wnodes, ts, stack); else node_step(sc.nodes, ts, stack);
                 // reference policy (node_k = 1, cudaUtils.h:385-391): descend until every lane still in the loop holds a
                 // leaf.  node_k = k leaves as soon as fewer than k lanes lack a leaf -- they resume after the leaf phase --
                 // instead of making the whole warp wait for one or two stragglers (k = 2..3: -3 % extend time; k >= 8 loses)
@@ -455,7 +455,11 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
     // for the rest of the warp to find one.  Measured extend time, k = 3 / 6 / 10 / 16 (profiles/r01_schedules.md #39): bench scene
     // (5 k triangles) 16.5 / - / 17.2 (k = 8) / 19.7; dragon 100 k 16.3 / 15.6 / 15.2 / 15.4; 16 cars 157 k 41.1 / 38.3 / 37.7 / 39.4;
     // dragon 1.6 M 23.3 / 21.3 / 20.7 / 20.9; synthetic 2 M 20.8 / 19.2 / 18.4 / 18.1; 20 M 37.6 / 35.2 / 33.9 / 33.2
-    const int node_k = cfg.node_k_env ? cfg.node_k_env : (sc.n_tris < (64 << 10) ? WF_NODE_K : (sc.n_tris < (2 << 20) ? 8 : 16));      // 8: between the reference-built dragon's best (6) and the device-built trees' (10)
+    // Small scenes on a tree with small leaves (the device builder's, ~1.8 triangle references per inner node against ~3 for the
+    // reference's SBVH) sit in between: bench scene on the rebuilt tree, k = 2 / 3 / 4 / 6 / 8: 13.03 / 12.54 / 12.36 / 12.34 / 12.52 ms
+    // (profiles/r02_schedules.md #58), while the SBVH of the same mesh is best at 3
+    const int small_k = (2 * (long long)sc.n_tris <= 5 * (long long)sc.n_nodes) ? 5 : WF_NODE_K;
+    const int node_k = cfg.node_k_env ? cfg.node_k_env : (sc.n_tris < (64 << 10) ? small_k : (sc.n_tris < (2 << 20) ? 8 : 16));      // 8: between the reference-built dragon's best (6) and the device-built trees' (10)
     const int n_pix = p.width * p.height;
     const int n_counters = (int)gptk_wave_counter_count(p.depth);
     // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays

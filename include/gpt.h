@@ -129,9 +129,12 @@ enum {
                                       * with the oracle: rsqrt normalisation, hardware sin/cos/pow/reciprocal (MUFU) in the shade kernel.
                                       * Nearest hits -- t, face index, the primary-hit map -- are unchanged (the traversal is not touched).
                                       * Off by default: gpt_launch / gpt_render stay bit-exact unless the caller sets it. */
-    GPT_FLAG_NO_TRIAL   = 1u << 9    /* never run the timed per-scene trial (gpt_trial_info): no render call then synchronises, so
+    GPT_FLAG_NO_TRIAL   = 1u << 9,   /* never run the timed per-scene trial (gpt_trial_info): no render call then synchronises, so
                                       * calls are strictly asynchronous and can be captured into a CUDA graph; the size defaults
                                       * decide tree and ray order (also: GPT_NO_TRIAL=1 in the environment) */
+    GPT_FLAG_KEEP_TREE  = 1u << 11   /* traverse the BVH exactly as uploaded (or its 4-wide collapse): do not build a second tree over
+                                      * the same triangles with this library's builder (gpt_rebuild_info; also GPT_REBUILD=0 in the
+                                      * environment).  Must be set before the upload / the first gpt_launch to save the build. */
 };
 
 typedef struct {
@@ -298,6 +301,14 @@ GPT_API int gpt_wide_info(gpt_ctx* ctx, int* n_wide, int* levels);
  * -1 still on trial (scenes of >= 256 Ki packed triangles, when neither GPT_WF_SORT nor GPT_SORT_MIN_TRIS is set: part of the
  * trial gpt_trial_info describes); the two figures are the trial's whole-call times for the tree in use. */
 GPT_API int gpt_reorder_info(gpt_ctx* ctx, int* state, double* ns_per_ray_path_order, double* ns_per_ray_reordered);
+/* The rebuilt tree.  When arrays in the reference's layout are packed (gpt_upload_scene, or new BVH pointers in gpt_launch) and hold
+ * 1 Ki .. 4 Mi triangle references, the library also builds a tree of its own over the SAME references (device PLOC builder, the
+ * caller's exact vertices; a few ms) and lets the per-scene trial decide between the two: the reference's SBVH is shaped for its own
+ * kernel, and the extend kernel here runs 15-20 % faster on the rebuilt one.  Distances, face indices and slots are those of the
+ * uploaded arrays bit for bit; what can differ is which of two triangles hit at bit-equal distance is met first (as for the 4-wide
+ * tree).  Not built for arrays that come from gpt_build_bvh, nor under GPT_FLAG_KEEP_TREE / _BINARY_BVH / _WIDE_BVH / _MEGAKERNEL.
+ * *state = 1 in use, 0 not, -1 on trial; *ns_per_ray = its timed trial calls (0 = not measured). */
+GPT_API int gpt_rebuild_info(gpt_ctx* ctx, int* state, int* n_inner_nodes, int* depth, double* ns_per_ray, float* build_ms);
 /* The per-scene trial behind both choices (tree and ray order): *pending = 1 while large render calls are still being timed;
  * ns_per_ray = whole-call ns per ray of the timed calls so far: [0] binary tree, [1] 4-wide tree (both in path order),
  * [2] the faster tree with rays re-ordered; 0 = not measured (candidate forced, closed, or not reached yet). */

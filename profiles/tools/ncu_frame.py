@@ -44,8 +44,10 @@ def main():
             built = ctx.build_bvh(verts, faces)
             ctx.upload_built(built, sph)
         acc = torch.zeros(H, W, 4, dtype=torch.float32, device="cuda")
-        for w in range(10):                               # buffers + the per-scene trial (<= 9 calls)
+        for w in range(16):                               # buffers + the per-scene trial (<= 12 calls)
             ctx.render(info, acc, 0, 1_000_000 + w * spp, spp)
+            if w >= 2 and not ctx.trial_info()[0]:
+                break
         torch.cuda.synchronize()
         ctx.reset_stats()
         torch.cuda.profiler.start()
@@ -54,7 +56,7 @@ def main():
         torch.cuda.profiler.stop()
         st = ctx.stats()
         out = {"scene": name, "width": W, "height": H, "spp": spp, "depth": 8, "triangles": int(len(faces)), "rays": int(st.rays), "paths": int(st.paths),
-               "launches": int(st.kernel_launches), "tree_in_use": "4-wide" if ctx.wide_info()[0] else "binary", "reorder": ctx.reorder_info()[0]}
+               "launches": int(st.kernel_launches), "tree_in_use": "rebuilt" if ctx.rebuild_info()["state"] == 1 else ("4-wide" if ctx.wide_info()[0] else "binary"), "reorder": ctx.reorder_info()[0]}
         print(json.dumps(out))
         d = os.path.join(ROOT, "gpurun_out")
         if os.path.isdir(d):

@@ -16,8 +16,8 @@ python -c "import json; json.load(open('gpurun_out/frame_counters.json'))" && cp
 python -c "import json; json.load(open('gpurun_out/algo_bytes.json'))" && cp gpurun_out/algo_bytes.json profiles/r02_algorithmic_bytes.json
 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" >> gpurun_out/bench.err
 python bench.py --impl reference > gpurun_out/bench_reference_arm.json 2> gpurun_out/bench_reference_arm.err
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-configs > gpurun_out/ncu_launches.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k "regex:k_wf_extend_ww|k_wf_shade" -s 20 -c 2 -o gpurun_out/r02_full python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-configs > gpurun_out/ncu_full.log 2>&1
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-configs > gpurun_out/ncu_launches.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k "regex:k_wf_extend_ww|k_wf_shade" -s 120 -c 2 -o gpurun_out/r02_full python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-configs > gpurun_out/ncu_full.log 2>&1
 ncu -i gpurun_out/r02_full.ncu-rep --page raw --csv > gpurun_out/r02_full_raw.csv 2> gpurun_out/ncu_full_raw.err
 python profiles/tools/small_frames.py > gpurun_out/small_frames.log 2>&1
 rm -f gpurun_out/r02_full.ncu-rep.tmp; ls -la gpurun_out

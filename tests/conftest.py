@@ -15,6 +15,10 @@ os.environ.setdefault("GPT_SORT_MIN_TRIS", "1100000")
 # Calls of fewer than GPT_SMALL_FRAME_PATHS paths (default 393216) go to the megakernel.  The parity tests render small frames and
 # mean to exercise the pipeline their flags name, so the switch is off here; tests/test_gpu_parity.py::test_small_calls_* covers it.
 os.environ.setdefault("GPT_SMALL_FRAME_PATHS", "0")
+# GPT_REBUILD=0: no second tree from the library's own builder over uploaded reference-layout arrays (gpt_rebuild_info).  The parity
+# tests compare slots, visit order and frames across calls with the tree AS UPLOADED; the rebuilt tree (same distances and face
+# indices, ties aside) and its trial run in tests/test_gpu_rebuild.py and test_gpu_configs.py, whose subprocesses drop the variable.
+os.environ.setdefault("GPT_REBUILD", "0")
 
 
 def pytest_configure(config):
