@@ -257,7 +257,10 @@ static TraversalPlan traversal_plan(const gpt_ctx* c, size_t n_paths)
     int ids[3];
     const int n_tree = tree_cands(c, ids), s = sort_choice(c);
     const int n_cand = n_tree + (s < 0 ? 1 : 0);
-    if (c->tune_done || n_cand < 2 || n_paths < ((size_t)1 << 20) || (c->flags & GPT_FLAG_NO_TRIAL) || k_env_no_trial) return pl;
+    // calls large enough to time: 1 Mi paths; with a rebuilt tree among the candidates every call the wavefront pipeline takes by
+    // default (one 1-spp launchKernel of a 720p window is 0.9 M paths and must not be left on the slower tree for ever)
+    const size_t min_paths = alt_choice(c) < 0 ? (size_t)393216 : ((size_t)1 << 20);
+    if (c->tune_done || n_cand < 2 || n_paths < min_paths || (c->flags & GPT_FLAG_NO_TRIAL) || k_env_no_trial) return pl;
     const int cand = c->tune_step / 3;
     pl.trial = true; pl.timed = (c->tune_step % 3) != 0;
     if (cand < n_tree) {                                          // a tree candidate, rays in path order
@@ -398,7 +401,8 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
     if (wanted) {
         static const int k_env_ploc = []{ const char* v = getenv("GPT_PLOC_RADIUS"); return (v && *v) ? atoi(v) : 24; }();
         RepackResult a; int status = 0; float ms = 0.0f;
-        e = gptk_rebuild(c->tris, c->n_tris, (const float4*)tris, 8, (c->flags & GPT_FLAG_BUILD_LBVH) ? 0 : k_env_ploc, &a, &status, &ms, &c->launches, 0);
+        static const int k_env_leaf = []{ const char* v = getenv("GPT_REBUILD_MAX_LEAF"); return (v && *v) ? atoi(v) : 8; }();
+        e = gptk_rebuild(c->tris, c->n_tris, (const float4*)tris, k_env_leaf, (c->flags & GPT_FLAG_BUILD_LBVH) ? 0 : k_env_ploc, &a, &status, &ms, &c->launches, 0);
         if (e != cudaSuccess) cudaGetLastError();
         else if (status == 0) { c->alt_nodes = a.nodes; c->alt_tris = a.tris; c->alt_n_nodes = a.n_nodes; c->alt_n_tris = a.n_tris; c->alt_depth = a.depth; c->alt_build_ms = ms; }
     }

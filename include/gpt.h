@@ -19,9 +19,10 @@
  * the library is re-entrant across contexts.  gpt_launch / gpt_render / gpt_resolve / gpt_reduce_resolve only enqueue work
  * on `stream` EXCEPT that a call may block the host (cudaDeviceSynchronize / cudaStreamSynchronize) when it
  *   - has to grow the scratch buffers (first call, a larger frame, more samples per call, a deeper path),
- *   - finds new BVH pointers in kernelInfo and re-packs them (gpt_launch), or builds the 4-wide tree (first render of a scene),
- *   - is one of the timed calls of the per-scene trial (gpt_trial_info; the first <= 9 render calls of >= 1 Mi paths after a
- *     scene upload on scenes of >= 64 Ki triangles; GPT_FLAG_NO_TRIAL switches the trial off).
+ *   - finds new BVH pointers in kernelInfo and re-packs them (gpt_launch; this also builds the rebuilt tree, gpt_rebuild_info), or
+ *     builds the 4-wide tree (first render of a scene),
+ *   - is one of the timed calls of the per-scene trial (gpt_trial_info; the first <= 12 render calls of >= 1 Mi paths after a
+ *     scene upload on scenes with more than one candidate tree or ray order; GPT_FLAG_NO_TRIAL switches the trial off).
  * gpt_upload_scene, gpt_build_bvh, gpt_set_triangle_materials, gpt_get_stats, gpt_get_kernel_times, gpt_reset_stats,
  * gpt_render_frame_host and the gpt_frame_* setup calls always synchronise.
  */
