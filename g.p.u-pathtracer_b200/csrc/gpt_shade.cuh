@@ -75,18 +75,20 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         return false;
     }
     f3 hitpos = mad3(ps.d, h.t, ps.o);                                   // :112
-    f3 n, nl, objcol, emit; int mat;
+    // The geometry branches only gather the un-normalised normal; the normalisation (an IEEE square root and a division) and the
+    // face-forwarding run once, after the branches have re-converged, instead of once per geometry type present in the warp.
+    f3 nr, objcol, emit; int mat;
+    bool unit = false, face_forward = true;
     if (h.geom == GEO_SPHERE) {                                          // :113-122
         const float* s = s_spheres + 11 * h.prim;
-        n = norm3_t<FAST>(sub3(hitpos, mk3(s[0], s[1], s[2])));
-        nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
+        nr = sub3(hitpos, mk3(s[0], s[1], s[2]));
         emit = mk3(s[4], s[5], s[6]); objcol = mk3(s[7], s[8], s[9]); mat = __float_as_int(s[10]);
     } else if (h.geom == GEO_TRI) {                                      // :123-139
         float4 b, c;
         tri_rows_bc(sc.tris, h.prim, b, c);
         // cross(v0-v1, v0-v2) == cross(e1, e2) bit for bit (negation is exact)   cudaUtils.h:432
-        n = norm3_t<FAST>(cross3(mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z)));
-        nl = n;                                                          // Q4: not face-forwarded
+        nr = cross3(mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z));
+        face_forward = false;                                            // Q4: not face-forwarded
         emit = ld3(p.emi); objcol = ld3(p.col); mat = p.tri_mat;
         if (sc.n_faces) {                                                // N4: per-face material table
             const int face = __float_as_int(tri_row_a(sc.tris, h.prim).w);
@@ -101,10 +103,12 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         }
     } else {                                                             // BOX (commented branch :143-152)
         const float* bx = s_boxes + 13 * h.prim;
-        n = box_normal(bx, hitpos);
-        nl = dot3(n, ps.d) < 0.0f ? n : scale3(n, -1.0f);
+        nr = box_normal(bx, hitpos); unit = true;                        // an axis: used as it is
         emit = mk3(bx[6], bx[7], bx[8]); objcol = mk3(bx[9], bx[10], bx[11]); mat = __float_as_int(bx[12]);
     }
+    f3 n = norm3_t<FAST>(nr);
+    if (unit) n = nr;
+    const f3 nl = (face_forward && !(dot3(n, ps.d) < 0.0f)) ? scale3(n, -1.0f) : n;
     if (FIRST && accu_slot) {
         *accu_slot = make_float4(fmaf(ps.mask.x, emit.x, 0.0f), fmaf(ps.mask.y, emit.y, 0.0f), fmaf(ps.mask.z, emit.z, 0.0f), 0.0f);
     } else if (accu_slot) {
@@ -117,7 +121,8 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
     } else
     ps.accu = mk3(fmaf(ps.mask.x, emit.x, ps.accu.x), fmaf(ps.mask.y, emit.y, ps.accu.y), fmaf(ps.mask.z, emit.z, ps.accu.z));   // :120/:133, contracted
 
-    f3 nextdir;
+    f3 nextdir, mscale = objcol;
+    float eps = 0.001f;
     if (mat == MAT_DIFF) {                                               // :156-186 (Q5)
         f3 nt = (fabsf(nl.x) > fabsf(nl.y)) ? mk3(nl.z, 0.0f, -nl.x) : mk3(0.0f, -nl.z, nl.y);
         nt = norm3_t<FAST>(nt);
@@ -128,25 +133,21 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
         nextdir = mk3(fmaf(nt.x, rv.z, fmaf(nl.x, rv.y, nb.x * rv.x)),
                       fmaf(nt.y, rv.z, fmaf(nl.y, rv.y, nb.y * rv.x)),
                       fmaf(nt.z, rv.z, fmaf(nl.z, rv.y, nb.z * rv.x)));
-        nextdir = norm3_t<FAST>(nextdir);
-        hitpos = mad3(nl, 0.001f, hitpos);
-        ps.mask = mul3(ps.mask, objcol);
     } else if (mat == MAT_SPEC) {                                        // :190-203 (Q6)
         // :194 'dir - nl * dot * 2.0f' the way nvcc emits it for the reference: pr = rn(nl*k), 2*pr formed as fma(k, nl, pr), plain subtract
         const float k = dot3(nl, ps.d);
         const f3 pr = scale3(nl, k);
-        nextdir = norm3_t<FAST>(mk3(ps.d.x - fmaf(k, nl.x, pr.x), ps.d.y - fmaf(k, nl.y, pr.y), ps.d.z - fmaf(k, nl.z, pr.z)));
-        hitpos = mad3(nl, 0.001f, hitpos);
-        ps.mask = mul3(ps.mask, objcol);
+        nextdir = mk3(ps.d.x - fmaf(k, nl.x, pr.x), ps.d.y - fmaf(k, nl.y, pr.y), ps.d.z - fmaf(k, nl.z, pr.z));
     } else if (mat == MAT_REFR) {                                        // :205-256 (Q7)
         const bool into = dot3(n, nl) > 0.0f;
         const float nc = p.air, ntr = p.glass;
         const float nnt = into ? fdiv_t<FAST>(nc, ntr) : fdiv_t<FAST>(ntr, nc);
         const float ddn = dot3(ps.d, nl);
         const float cos2t = fmaf(-(nnt * nnt), fmaf(-ddn, ddn, 1.0f), 1.0f);        // :212, contracted as in the reference's SASS
+        mscale = mk3(1.0f, 1.0f, 1.0f);                                  // total internal reflection leaves the mask alone (x * 1 is exact)
         if (cos2t < 0.0f) {
             const float k = dot3(n, ps.d) * 2.0f;
-            nextdir = norm3_t<FAST>(mad3(n, -k, ps.d));
+            nextdir = mad3(n, -k, ps.d);
         } else {
             const float s = (into ? 1.0f : -1.0f) * fmaf(ddn, nnt, sqrt_t<FAST>(cos2t));
             const f3 tdir = norm3_t<FAST>(mad3(n, -s, scale3(ps.d, nnt)));
@@ -157,15 +158,14 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
             const float P = 0.25f + 0.5f * Re;
             const float RP = fdiv_t<FAST>(Re, P), TP = fdiv_t<FAST>(Tr, 1.0f - P);
             if (u.x < 0.2f) {                                            // :239 constant, not P
-                ps.mask = scale3(ps.mask, RP);
+                mscale = mk3(RP, RP, RP);
                 const float k = dot3(n, ps.d) * 2.0f;
-                nextdir = norm3_t<FAST>(mad3(n, -k, ps.d));
+                nextdir = mad3(n, -k, ps.d);
             } else {
-                ps.mask = scale3(ps.mask, TP);
-                nextdir = norm3_t<FAST>(tdir);
+                mscale = mk3(TP, TP, TP);
+                nextdir = tdir;                                          // normalised a second time below, as the reference does
             }
         }
-        hitpos = mad3(nl, 0.001f, hitpos);
     } else {                                                             // METAL :257-293 (Q1)
         float sphi, cphi; sincos2pi_t<FAST>(u.x, sphi, cphi);
         const float cosT = pow_t<FAST>(1.0f - u.y, fdiv_t<FAST>(1.0f, p.phong + 1.0f));
@@ -183,10 +183,12 @@ __device__ __forceinline__ bool shade_bounce(const DevScene& sc, const RenderPar
             const float wc = (float)p.width * cosT;                      // :280 `w` = int image width
             nextdir = mk3(fmaf(vv.x, b, uu.x * a) + wc, fmaf(vv.y, b, uu.y * a) + wc, fmaf(vv.z, b, uu.z * a) + wc);
         }
-        nextdir = norm3_t<FAST>(nextdir);
-        hitpos = mad3(nl, 0.0001f, hitpos);
-        ps.mask = mul3(ps.mask, objcol);
+        eps = 0.0001f;
     }
+    // common tail of the four materials, after re-convergence: normalise the new direction, lift the origin off the surface, tint
+    nextdir = norm3_t<FAST>(nextdir);
+    hitpos = mad3(nl, eps, hitpos);
+    ps.mask = mul3(ps.mask, mscale);
     ps.o = hitpos; ps.d = nextdir;
     return true;
 }

@@ -331,6 +331,28 @@ __device__ __forceinline__ SceneHit finish_scene_hit(const DevScene& sc, const f
     return h;
 }
 
+// the same sweep with the spheres' centre + radius read as one float4 each (an array in shared memory: LDS.128); same arithmetic
+template <bool FAST = false>
+__device__ __forceinline__ SceneHit finish_scene_hit_smem(const DevScene& sc, const float4* posrad, const float* s_boxes,
+                                                          const float tri_t, const int tri, const f3 o, const f3 d)
+{
+    SceneHit h; h.t = tri_t; h.geom = GEO_NONE; h.prim = -1;
+    if (tri >= 0) { h.geom = GEO_TRI; h.prim = tri; }
+    constexpr int sphere_unroll = SPHERE_UNROLL;
+#pragma unroll sphere_unroll
+    for (int i = 0; i < sc.n_spheres; ++i) {
+        const float4 pr = posrad[i];
+        const float s4[4] = {pr.x, pr.y, pr.z, pr.w};
+        const float t = sphere_test<FAST>(s4, o, d);
+        if (t != 0.0f && t < h.t && t > 0.01f) { h.t = t; h.geom = GEO_SPHERE; h.prim = i; }
+    }
+    for (int i = 0; i < sc.n_boxes; ++i) {
+        const float t = box_test(s_boxes + 13 * i, o, d);
+        if (t != 0.0f && t < h.t) { h.t = t; h.geom = GEO_BOX; h.prim = i; }
+    }
+    return h;
+}
+
 __device__ __forceinline__ SceneHit intersect_scene(const DevScene& sc, const float* s_spheres, const float* s_boxes,
                                                     const f3 o, const f3 d, const bool cull)
 {

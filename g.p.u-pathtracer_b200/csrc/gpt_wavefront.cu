@@ -74,6 +74,7 @@ __device__ __forceinline__ void st_ray32(float4* __restrict__ ray, const uint32_
 #endif
 
 struct SmemPrims {
+    float4 posrad[GPT_MAX_SMEM_SPHERES];       // centre + radius of every sphere again, 16-byte aligned: the sweep reads ONE LDS.128 per sphere
     float spheres[GPT_MAX_SMEM_SPHERES * 11];
     float boxes[GPT_MAX_SMEM_BOXES * 13];
 };
@@ -83,6 +84,8 @@ __device__ __forceinline__ void stage_prims(const DevScene& sc, SmemPrims& sm, c
     s_spheres = sc.spheres; s_boxes = sc.boxes;
     if (sc.n_spheres <= GPT_MAX_SMEM_SPHERES) {
         for (int i = threadIdx.x; i < sc.n_spheres * 11; i += blockDim.x) sm.spheres[i] = sc.spheres[i];
+        for (int i = threadIdx.x; i < sc.n_spheres; i += blockDim.x)
+            sm.posrad[i] = make_float4(sc.spheres[11 * i], sc.spheres[11 * i + 1], sc.spheres[11 * i + 2], sc.spheres[11 * i + 3]);
         s_spheres = sm.spheres;
     }
     if (sc.n_boxes <= GPT_MAX_SMEM_BOXES) {
@@ -137,13 +140,15 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
     while (true) {
         const unsigned m_idle = __ballot_sync(GPT_FULL_MASK, !active);
         if (m_idle != 0u && !exhausted && (__popc(m_idle) >= refill_min || m_idle == GPT_FULL_MASK)) {
+            const unsigned k_idle = (unsigned)__popc(m_idle);
             unsigned base = 0;
             const int leader = __ffs(m_idle) - 1;
-            if ((int)lane == leader) base = atomicAdd(fetch, (unsigned)__popc(m_idle));
+            if ((int)lane == leader) base = atomicAdd(fetch, k_idle);
             base = __shfl_sync(GPT_FULL_MASK, base, leader);
-            if (base + (unsigned)__popc(m_idle) >= n) exhausted = true;
+            if (base + k_idle >= n) exhausted = true;
+            const unsigned j_lane = base + (unsigned)__popc(m_idle & lt_mask);
             if (!active) {
-                const unsigned j = base + (unsigned)__popc(m_idle & lt_mask);
+                const unsigned j = j_lane;
                 if (j < n) {
                     if (PRIMARY) {
                         pid = j;
@@ -197,6 +202,21 @@ struct ShadeIo {
     float4* ray; const int2* hit; float* mask_z; float4* accu;      // ray: 2 float4 per path (ld_ray32 / st_ray32)
 };
 
+#ifndef WF_SPHERE_LDS
+#define WF_SPHERE_LDS 1
+#endif
+#ifndef WF_SHADE_PIPE
+#define WF_SHADE_PIPE 1
+#endif
+#ifndef WF_SHADE_PF
+#define WF_SHADE_PF 1
+#endif
+template <int LEVEL> __device__ __forceinline__ void shade_prefetch(const void* p)
+{
+    if (LEVEL == 1) asm volatile("prefetch.global.L1 [%0];" :: "l"(p));
+    if (LEVEL == 2) asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+}
+
 template <bool FIRST>
 __device__ __forceinline__ void shade_load_path(const PrimaryGen& gen, const ShadeIo& io, const uint32_t pid, PathState& ps)
 {
@@ -241,6 +261,29 @@ __device__ __forceinline__ void shade_compact(const bool survive, const uint32_t
     }
 }
 
+// the same for a whole CTA of 256 threads: ONE atomic per CTA and trip instead of one per warp.  All the queue atomics of a launch hit
+// one address, and the L2's atomic unit serialises them (~0.85 cycles each: 1 M warp-level atomics of a 33 M-path launch are
+// 0.45 ms of a 1.2 ms kernel, and every warp queues behind the others for its result).  Every thread of the CTA must call it.
+__device__ __forceinline__ void shade_compact_cta(const bool survive, const uint32_t pid, unsigned int* n_out, uint32_t* queue_out, const unsigned lane,
+                                                  unsigned* s_cnt, unsigned* s_base)
+{
+    const unsigned m = __ballot_sync(GPT_FULL_MASK, survive);
+    const unsigned w = threadIdx.x >> 5;
+    if (lane == 0) s_cnt[w] = (unsigned)__popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned tot = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { const unsigned t = s_cnt[k]; s_cnt[k] = tot; tot += t; }
+        *s_base = tot ? atomicAdd(n_out, tot) : 0u;
+    }
+    __syncthreads();
+    if (survive) WF_ST(queue_out + (*s_base + s_cnt[w] + (unsigned)__popc(m & ((1u << lane) - 1u))), pid);
+}
+
+#ifndef WF_SHADE_CTA_AGG
+#define WF_SHADE_CTA_AGG 1
+#endif
 template <bool FIRST, bool FAST>
 __global__ void __launch_bounds__(256, SHADE_MIN_BLOCKS)
 k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const ShadeIo io,
@@ -261,21 +304,40 @@ k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const
         if ((p.flags & RP_COUNT_BOUNCES) && bounce < 16) atomicAdd(&stats[2 + bounce], (unsigned long long)n);
     }
     // whole warps iterate together so the ballots below are warp-uniform
-    const unsigned n_round = (n + 31u) & ~31u;
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+    __shared__ unsigned s_cnt[8], s_base;
+    const unsigned n_round = WF_SHADE_CTA_AGG ? ((n + 255u) & ~255u) : ((n + 31u) & ~31u);      // CTA-uniform trip counts for the barriers
+    const unsigned stride = gridDim.x * blockDim.x;
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    // A trip starts with three dependent fetches (queue slot -> path id -> ray / hit / mask of that path, scattered 32-B
+    // records): WF_SHADE_PIPE fetches the NEXT trip's path id one trip ahead, WF_SHADE_PF = 1 / 2 also asks L1 / L2 for that
+    // path's records while this trip computes (ncu: long-scoreboard stalls are what the kernel waits on once its arithmetic is cheap)
+    uint32_t pid_next = 0;
+    if (!FIRST && WF_SHADE_PIPE && i < n) pid_next = WF_LD(io.queue_in + i);
+    for (; i < n_round; i += stride) {
         bool survive = false, valid = i < n;
         uint32_t pid = 0;
         PathState ps;
         SceneHit h; h.t = GPT_F32_MAX; h.geom = GEO_NONE; h.prim = -1;
+        const bool more = !FIRST && WF_SHADE_PIPE && i + stride < n;
         if (valid) {
-            pid = FIRST ? i : WF_LD(io.queue_in + i);
+            pid = FIRST ? i : (WF_SHADE_PIPE ? pid_next : WF_LD(io.queue_in + i));
+            if (more) pid_next = WF_LD(io.queue_in + (i + stride));
             shade_load_path<FIRST>(gen, io, pid, ps);
             float tri_t = GPT_F32_MAX; int tri = -1;
             if (has_mesh) { const int2 hh = WF_LD(io.hit + pid); tri_t = __int_as_float(hh.x); tri = hh.y; }
-            h = finish_scene_hit<FAST>(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
+            // spheres staged in shared memory: the sweep reads them through the __shared__ array itself (LDS.128), not through the
+            // generic pointer, whose 4 x 32-bit LD per sphere wait on the long scoreboard (ncu: the kernel's largest stall)
+            if (WF_SPHERE_LDS && sc.n_spheres <= GPT_MAX_SMEM_SPHERES) h = finish_scene_hit_smem<FAST>(sc, sm.posrad, s_boxes, tri_t, tri, ps.o, ps.d);
+            else h = finish_scene_hit<FAST>(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
+            if (more && WF_SHADE_PF) {
+                shade_prefetch<WF_SHADE_PF>(io.ray + 2 * (size_t)pid_next);
+                shade_prefetch<WF_SHADE_PF>(io.mask_z + pid_next);
+                if (has_mesh) shade_prefetch<WF_SHADE_PF>(io.hit + pid_next);
+            }
         }
         if (valid) survive = shade_finish_path<FIRST, FAST>(sc, gen, io, s_spheres, s_boxes, h, pid, bounce, last_bounce, ps);
-        shade_compact(survive, pid, n_out, io.queue_out, lane);
+        if (WF_SHADE_CTA_AGG) shade_compact_cta(survive, pid, n_out, io.queue_out, lane, s_cnt, &s_base);
+        else shade_compact(survive, pid, n_out, io.queue_out, lane);
     }
 }
 
