@@ -419,7 +419,7 @@ def config_records(gpt, torch, local, args, peaks, hbm, flush):
             st, kt = ctx.stats(), ctx.kernel_times()
             rays = float(st.rays) / reps
             rec.update({"value": rays / ms / 1e3, "unit": "Mrays/s", "ms_per_frame": ms, "rays_per_frame": rays,
-                        "tree_in_use": "rebuilt" if ctx.rebuild_info()["state"] == 1 else ("4-wide" if ctx.wide_info()[0] else "binary"),
+                        "tree_in_use": ctx.tree_info()["in_use"], "trees": ctx.tree_info(),
                         "rebuilt_tree": ctx.rebuild_info(), "trial_ns_per_ray": ctx.trial_info()[1], "ray_reordering": ctx.reorder_info()[0],
                         "kernel_class_ms": {k: v[0] / reps for k, v in kt.items() if v[1]}})
             ab = load_algo_bytes(name)
@@ -598,7 +598,7 @@ def run_ours(args):
             step(100000 + n)
             n += 1
         sync_all()
-        use = torch.tensor([float(ctx.rebuild_info()["state"] == 1)], device=dev)
+        use = torch.tensor([float(gpt.Context.TREE_NAMES.index(ctx.tree_info()["in_use"]))], device=dev)
         lo, hi = use.clone(), use.clone()
         if dist is not None:
             dist.all_reduce(lo, op=dist.ReduceOp.MIN)
@@ -606,7 +606,7 @@ def run_ours(args):
         agreed = float(lo.item()) == float(hi.item())
         if not agreed:
             ctx.set_flags(flags | gpt.FLAG_KEEP_TREE)
-        return {"trial_calls": n, "ranks_agreed": agreed, "in_use": "rebuilt" if (agreed and float(hi.item()) == 1.0) else "as uploaded",
+        return {"trial_calls": n, "ranks_agreed": agreed, "in_use": ctx.tree_info()["in_use"] if agreed else "as uploaded", "trees": ctx.tree_info(),
                 "rebuilt": ctx.rebuild_info(), "trial_ns_per_ray_binary_wide_sorted": ctx.trial_info()[1]}
 
     tree_rec = finish_trial()

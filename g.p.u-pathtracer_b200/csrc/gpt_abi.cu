@@ -27,10 +27,12 @@ struct gpt_ctx {
     // a second packed tree over the same triangle references, made by the device builder when a reference-layout tree is packed
     // (gptk_rebuild); own_tree = the uploaded arrays came from gpt_build_bvh of this context (nothing to gain from rebuilding)
     float4* alt_nodes = nullptr; float4* alt_tris = nullptr; int alt_n_nodes = 0, alt_n_tris = 0, alt_depth = 0; float alt_build_ms = 0.0f;
+    // ... and the uploaded tree with its larger leaves split into small SAH subtrees (gptk_split_leaves)
+    float4* spl_nodes = nullptr; float4* spl_tris = nullptr; int spl_n_nodes = 0, spl_depth = 0;
     bool own_tree = false; const void* built_nodes[8] = {}; int built_next = 0;
     // per-scene choice of traversal structure and ray order (traversal_plan): flags and environment win, else a timed trial
-    int tune_step = 0; bool tune_done = false; int tuned_tree = 0; bool tuned_sort = false;      // tree ids: 0 uploaded binary, 1 its 4-wide collapse, 2 rebuilt
-    double tune_ns[4] = {0.0, 0.0, 0.0, 0.0};     // ns per ray: binary tree / wide tree in path order, chosen tree re-ordered, rebuilt tree in path order
+    int tune_step = 0; bool tune_done = false; int tuned_tree = 0; bool tuned_sort = false;      // tree ids: 0 uploaded binary, 1 its 4-wide collapse, 2 rebuilt, 3 leaves split
+    double tune_ns[5] = {0.0, 0.0, 0.0, 0.0, 0.0};     // ns per ray: binary tree / wide tree in path order, chosen tree re-ordered, rebuilt tree, split-leaf tree (path order)
     // identity of the reference arrays the packed BVH was built from (gpt_launch re-packs on change)
     const void* src_nodes = nullptr; const void* src_tris = nullptr; const void* src_idx = nullptr;
     size_t src_n_nodes = 0, src_n_tris = 0, src_n_idx = 0;
@@ -97,13 +99,14 @@ static void free_wide(gpt_ctx* c)
 {
     cudaFree(c->wnodes); c->wnodes = nullptr; c->n_wide = 0; c->wide_levels = 0; c->wide_tried = false;
     c->tune_step = 0; c->tune_done = false; c->tuned_tree = 0; c->tuned_sort = false;      // a new tree: the questions are open again
-    c->tune_ns[0] = c->tune_ns[1] = c->tune_ns[2] = c->tune_ns[3] = 0.0;
+    c->tune_ns[0] = c->tune_ns[1] = c->tune_ns[2] = c->tune_ns[3] = c->tune_ns[4] = 0.0;
 }
 
 static void free_alt(gpt_ctx* c)
 {
     cudaFree(c->alt_nodes); cudaFree(c->alt_tris); c->alt_nodes = c->alt_tris = nullptr;
     c->alt_n_nodes = c->alt_n_tris = c->alt_depth = 0; c->alt_build_ms = 0.0f;
+    cudaFree(c->spl_nodes); cudaFree(c->spl_tris); c->spl_nodes = c->spl_tris = nullptr; c->spl_n_nodes = c->spl_depth = 0;
 }
 
 static void free_scene(gpt_ctx* c)
@@ -175,6 +178,9 @@ static const long long k_env_sort_min = []{ const char* e = getenv("GPT_SORT_MIN
 // reference-layout trees of 1 Ki .. 4 Mi packed triangles that do not come from gpt_build_bvh, and put on trial with the others.
 // GPT_FLAG_KEEP_TREE, GPT_FLAG_BINARY_BVH, GPT_FLAG_WIDE_BVH and GPT_FLAG_MEGAKERNEL all mean "the tree as uploaded".
 static const int k_env_rebuild = []{ const char* e = getenv("GPT_REBUILD"); return (e && *e) ? atoi(e) : -1; }();
+// The split-leaf tree (gptk_split_leaves) follows the same rules; GPT_SPLIT=0 / 1 switches it alone (1: always traversed, and
+// GPT_REBUILD=1 wins over it); GPT_SPLIT_MAX_LEAF sets the leaf cap (2)
+static const int k_env_split = []{ const char* e = getenv("GPT_SPLIT"); return (e && *e) ? atoi(e) : -1; }();
 
 // Which pipeline: the wavefront pipeline needs ~19 launches per call and each costs ~19 us of launch gap + drain, so below a few
 // hundred thousand paths per call the single-launch megakernel is faster (cornell 512x512, 1 spp, depth 4: 0.17 ms against
@@ -211,18 +217,25 @@ static int alt_choice(const gpt_ctx* c)
     if (!c->alt_nodes || (c->flags & (GPT_FLAG_KEEP_TREE | GPT_FLAG_BINARY_BVH | GPT_FLAG_WIDE_BVH | GPT_FLAG_MEGAKERNEL)) || k_env_rebuild == 0) return 0;
     return k_env_rebuild > 0 ? 1 : -1;
 }
-// the trees a scene may be traversed on (ids: 0 uploaded binary, 1 its 4-wide collapse, 2 rebuilt), in trial order
+static int split_choice(const gpt_ctx* c)
+{
+    if (!c->spl_nodes || (c->flags & (GPT_FLAG_KEEP_TREE | GPT_FLAG_BINARY_BVH | GPT_FLAG_WIDE_BVH | GPT_FLAG_MEGAKERNEL)) || k_env_rebuild == 0 || k_env_split == 0) return 0;
+    return k_env_split > 0 ? 1 : -1;
+}
+// the trees a scene may be traversed on (ids: 0 uploaded binary, 1 its 4-wide collapse, 2 rebuilt, 3 leaves split), in trial order
 static int tree_cands(const gpt_ctx* c, int* ids)
 {
-    const int t = tree_choice(c), a = alt_choice(c);
+    const int t = tree_choice(c), a = alt_choice(c), sp = split_choice(c);
     int n = 0;
     if (a == 1) { ids[n++] = 2; return n; }
+    if (sp == 1) { ids[n++] = 3; return n; }
     if (t != 1) ids[n++] = 0;
     if (t != 0) ids[n++] = 1;
     if (a < 0) ids[n++] = 2;
+    if (sp < 0) ids[n++] = 3;
     return n;
 }
-static double tree_ns(const gpt_ctx* c, int id) { return c->tune_ns[id == 2 ? 3 : id]; }
+static double tree_ns(const gpt_ctx* c, int id) { return c->tune_ns[id >= 2 ? id + 1 : id]; }
 // the fastest measured candidate; a later candidate must beat the best so far by 2 %
 static int best_tree(const gpt_ctx* c, const int* ids, int n)
 {
@@ -236,7 +249,7 @@ static int best_tree(const gpt_ctx* c, const int* ids, int n)
 // what to use outside a trial call: forced, decided, or the default (the wide tree from 1 Mi triangles, else the tree as uploaded)
 static int current_tree(const gpt_ctx* c)
 {
-    int ids[3];
+    int ids[4];
     const int n = tree_cands(c, ids);
     if (n == 1) return ids[0];
     if (c->tune_done) return c->tuned_tree;
@@ -254,7 +267,7 @@ struct TraversalPlan { int tree; bool sort; bool trial; bool timed; int slot; };
 static TraversalPlan traversal_plan(const gpt_ctx* c, size_t n_paths)
 {
     TraversalPlan pl = {current_tree(c), current_sort(c), false, false, -1};
-    int ids[3];
+    int ids[4];
     const int n_tree = tree_cands(c, ids), s = sort_choice(c);
     const int n_cand = n_tree + (s < 0 ? 1 : 0);
     // calls large enough to time: 1 Mi paths; with a rebuilt tree among the candidates every call the wavefront pipeline takes by
@@ -266,7 +279,7 @@ static TraversalPlan traversal_plan(const gpt_ctx* c, size_t n_paths)
     if (cand < n_tree) {                                          // a tree candidate, rays in path order
         pl.tree = ids[cand];
         pl.sort = false;
-        pl.slot = pl.tree == 2 ? 3 : pl.tree;
+        pl.slot = pl.tree >= 2 ? pl.tree + 1 : pl.tree;
     } else {                                                      // the fastest tree, re-ordered
         pl.tree = best_tree(c, ids, n_tree);
         pl.sort = true;
@@ -276,7 +289,7 @@ static TraversalPlan traversal_plan(const gpt_ctx* c, size_t n_paths)
 }
 static void trial_advance(gpt_ctx* c)
 {
-    int ids[3];
+    int ids[4];
     const int n_tree = tree_cands(c, ids), s = sort_choice(c);
     const int n_cand = n_tree + (s < 0 ? 1 : 0);
     if (++c->tune_step < 3 * n_cand) return;
@@ -288,9 +301,9 @@ static void trial_advance(gpt_ctx* c)
 // point a DevScene at one of the context's trees (1 without a built wide tree falls back to the binary tree it was collapsed from)
 static void set_tree(const gpt_ctx* c, DevScene* sc, int tree)
 {
-    const bool alt = tree == 2 && c->alt_nodes;
-    sc->nodes = alt ? c->alt_nodes : c->nodes; sc->tris = alt ? c->alt_tris : c->tris;
-    sc->n_nodes = alt ? c->alt_n_nodes : c->n_nodes; sc->n_tris = alt ? c->alt_n_tris : c->n_tris;
+    const bool alt = tree == 2 && c->alt_nodes, spl = tree == 3 && c->spl_nodes;
+    sc->nodes = alt ? c->alt_nodes : (spl ? c->spl_nodes : c->nodes); sc->tris = alt ? c->alt_tris : (spl ? c->spl_tris : c->tris);
+    sc->n_nodes = alt ? c->alt_n_nodes : (spl ? c->spl_n_nodes : c->n_nodes); sc->n_tris = alt ? c->alt_n_tris : c->n_tris;
     sc->wnodes = (tree == 1) ? c->wnodes : nullptr;
 }
 
@@ -397,7 +410,7 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
     c->nodes = r.nodes; c->tris = r.tris; c->n_nodes = r.n_nodes; c->n_tris = r.n_tris; c->tree_depth = r.depth;
     // the same triangle references under a tree of this library's own builder (see k_env_rebuild); failure just leaves the one above
     const bool wanted = !c->own_tree && k_env_rebuild != 0 && !(c->flags & (GPT_FLAG_KEEP_TREE | GPT_FLAG_BINARY_BVH | GPT_FLAG_WIDE_BVH | GPT_FLAG_MEGAKERNEL)) &&
-                        (k_env_rebuild > 0 ? c->n_tris >= 2 : (c->n_tris >= (1 << 10) && c->n_tris <= (4 << 20)));
+                        ((k_env_rebuild > 0 || k_env_split > 0) ? c->n_tris >= 2 : (c->n_tris >= (1 << 10) && c->n_tris <= (4 << 20)));
     if (wanted) {
         static const int k_env_ploc = []{ const char* v = getenv("GPT_PLOC_RADIUS"); return (v && *v) ? atoi(v) : 24; }();
         RepackResult a; int status = 0; float ms = 0.0f;
@@ -405,6 +418,13 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
         e = gptk_rebuild(c->tris, c->n_tris, (const float4*)tris, k_env_leaf, (c->flags & GPT_FLAG_BUILD_LBVH) ? 0 : k_env_ploc, &a, &status, &ms, &c->launches, 0);
         if (e != cudaSuccess) cudaGetLastError();
         else if (status == 0) { c->alt_nodes = a.nodes; c->alt_tris = a.tris; c->alt_n_nodes = a.n_nodes; c->alt_n_tris = a.n_tris; c->alt_depth = a.depth; c->alt_build_ms = ms; }
+        if (k_env_split != 0) {
+            static const int k_env_split_leaf = []{ const char* v = getenv("GPT_SPLIT_MAX_LEAF"); return (v && *v) ? atoi(v) : 2; }();
+            RepackResult sres; int sst = 0;
+            e = gptk_split_leaves(c->nodes, c->n_nodes, c->tris, c->n_tris, (const float4*)tris, k_env_split_leaf, &sres, &sst, &c->launches, 0);
+            if (e != cudaSuccess) cudaGetLastError();
+            else if (sst == 0) { c->spl_nodes = sres.nodes; c->spl_tris = sres.tris; c->spl_n_nodes = sres.n_nodes; c->spl_depth = sres.depth; }
+        }
     }
     return GPT_OK;
 }
@@ -614,6 +634,16 @@ int gpt_rebuild_info(gpt_ctx* c, int* state, int* n_inner_nodes, int* depth, dou
     if (depth) *depth = c->alt_depth;
     if (ns_per_ray) *ns_per_ray = c->tune_ns[3];
     if (build_ms) *build_ms = c->alt_build_ms;
+    return GPT_OK;
+}
+
+int gpt_tree_info(gpt_ctx* c, int* tree_in_use, int* pending, double ns_per_ray[4], int n_inner_nodes[4])
+{
+    if (!c) return GPT_ERR_INVALID;
+    if (tree_in_use) *tree_in_use = current_tree(c);
+    if (pending) *pending = traversal_plan(c, (size_t)1 << 30).trial ? 1 : 0;
+    if (ns_per_ray) for (int i = 0; i < 4; ++i) ns_per_ray[i] = tree_ns(c, i);
+    if (n_inner_nodes) { n_inner_nodes[0] = c->n_nodes; n_inner_nodes[1] = c->n_wide; n_inner_nodes[2] = c->alt_n_nodes; n_inner_nodes[3] = c->spl_n_nodes; }
     return GPT_OK;
 }
 

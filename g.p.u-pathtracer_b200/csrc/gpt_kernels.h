@@ -65,6 +65,11 @@ cudaError_t gptk_repack(const float4* ref_nodes, size_t n_node_vec4, const float
 cudaError_t gptk_rebuild(const float4* packed_tris, int n_tris, const float4* ref_tris, int max_leaf, int ploc_radius,
                          RepackResult* out, int* status, float* build_ms, unsigned long long* launches, cudaStream_t st);
 
+// The packed tree with every leaf of max_leaf + 1 .. 16 references replaced by a small SAH subtree (gpt_repack.cu): new node and
+// triangle arrays, same triangle count, rows only permuted inside their leaf.  *status: 0 ok, 1 nothing to split, 2 too deep.
+cudaError_t gptk_split_leaves(const float4* nodes, int n_inner, const float4* tris, int n_tris, const float4* ref_tris, int max_leaf,
+                              RepackResult* out, int* status, unsigned long long* launches, cudaStream_t st);
+
 // device-side LBVH builder (gpt_build.cu): indexed mesh (device pointers) -> arrays in CudaBVH's compact layout,
 // cudaMalloc'd by the callee.  status: 0 ok, 1 vertex index out of range, 2 non-finite vertex, 3 too large, 4 too deep
 struct BuildResult { float4* nodes; size_t n_node_vec4; float4* tris; size_t n_tri_vec4; int* indices; size_t n_indices;

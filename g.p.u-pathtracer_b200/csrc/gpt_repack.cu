@@ -250,3 +250,208 @@ fail:
     return e;
 #undef CK
 }
+
+// ---- the uploaded tree with its leaves split (gptk_split_leaves) ------------------------------------------------------------------
+// The reference's SplitBVHBuilder stops at leaves of up to 8 references where its SAH (node cost = triangle cost) says so; the
+// kernels here pay 87 instructions per triangle test against 75 per node visit and no longer want them (profiles/r02_schedules.md
+// #68: the reference builder run with a leaf cap of 2 gives a tree the extend kernel walks 27 % faster on the dragon -- and 13 %
+// faster than the PLOC tree of gptk_rebuild, whose upper levels are not SBVH quality).  A top-down builder's upper levels do not
+// depend on where it stops, so that tree is THIS tree with every larger leaf replaced by a small SAH subtree -- which one thread
+// per leaf can build: <= 16 references, object splits only, sweep over the three axes.  The packed triangle rows are only permuted
+// inside their leaf's range (and their "triangles that follow" lanes rewritten), new inner nodes are appended behind the old ones.
+#define SPLIT_MAXT 16
+
+__device__ __forceinline__ float box_half_area(const float3 lo, const float3 hi)
+{
+    const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void k_split_count(const float4* __restrict__ nodes, const int n_inner, const float4* __restrict__ tris, const int max_leaf, int* __restrict__ counts)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * n_inner) return;
+    const int4 ch = *reinterpret_cast<const int4*>(nodes + 4 * (size_t)(i >> 1) + 3);
+    const int c = (i & 1) ? ch.y : ch.x;
+    int extra = 0;
+    if (c < 0) {
+        const int cnt = __float_as_int(tris[GPT_TRI_STRIDE * (size_t)(~c) + GPT_TRI_B + 1].w) + 1;
+        if (cnt > max_leaf && cnt <= SPLIT_MAXT) extra = cnt - 1;          // a binary tree over cnt leaves has at most cnt - 1 inner nodes
+    }
+    counts[i] = extra;
+}
+
+__global__ void __launch_bounds__(64)
+k_split_build(const float4* __restrict__ nodes_old, const int n_inner, const float4* __restrict__ tris_old, const float4* __restrict__ ref_tris,
+              const int* __restrict__ offsets, const int max_leaf, float4* __restrict__ nodes_new, float4* __restrict__ tris_new)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * n_inner) return;
+    if (offsets[i + 1] == offsets[i]) return;                               // not a leaf to split
+    const int4 ch = *reinterpret_cast<const int4*>(nodes_old + 4 * (size_t)(i >> 1) + 3);
+    const int base = ~((i & 1) ? ch.y : ch.x);
+    const int cnt = __float_as_int(tris_old[GPT_TRI_STRIDE * (size_t)base + GPT_TRI_B + 1].w) + 1;
+    float3 lo[SPLIT_MAXT], hi[SPLIT_MAXT];
+    float right_area[SPLIT_MAXT];
+    int perm[SPLIT_MAXT], follow[SPLIT_MAXT];
+    for (int k = 0; k < cnt; ++k) {
+        const float4 a = tris_old[GPT_TRI_STRIDE * (size_t)(base + k)], b = tris_old[GPT_TRI_STRIDE * (size_t)(base + k) + GPT_TRI_B],
+                     c = tris_old[GPT_TRI_STRIDE * (size_t)(base + k) + GPT_TRI_B + 1];
+        const int slot = __float_as_int(b.w);
+        const float4 v1 = ref_tris[(size_t)slot + 1], v2 = ref_tris[(size_t)slot + 2];      // the caller's exact vertices ...
+        const float w1x = a.x + b.x, w1y = a.y + b.y, w1z = a.z + b.z, w2x = a.x + c.x, w2y = a.y + c.y, w2z = a.z + c.z;   // ... and the ones the test sees
+        lo[k] = make_float3(fminf(fminf(a.x, fminf(v1.x, v2.x)), fminf(w1x, w2x)), fminf(fminf(a.y, fminf(v1.y, v2.y)), fminf(w1y, w2y)), fminf(fminf(a.z, fminf(v1.z, v2.z)), fminf(w1z, w2z)));
+        hi[k] = make_float3(fmaxf(fmaxf(a.x, fmaxf(v1.x, v2.x)), fmaxf(w1x, w2x)), fmaxf(fmaxf(a.y, fmaxf(v1.y, v2.y)), fmaxf(w1y, w2y)), fmaxf(fmaxf(a.z, fmaxf(v1.z, v2.z)), fmaxf(w1z, w2z)));
+        perm[k] = k; follow[k] = 0;
+    }
+    // explicit stack of ranges; where = index of the int that receives the pointer to the subtree (node * 4 + child) in nodes_new rows [3]
+    int st_a[SPLIT_MAXT], st_b[SPLIT_MAXT], st_where[SPLIT_MAXT], sp = 0;
+    int next_node = n_inner + offsets[i];
+    st_a[0] = 0; st_b[0] = cnt; st_where[0] = 4 * (i >> 1) + (i & 1); sp = 1;
+    while (sp > 0) {
+        --sp;
+        const int a = st_a[sp], b = st_b[sp], where = st_where[sp], n = b - a;
+        float3 plo = lo[perm[a]], phi = hi[perm[a]];
+        for (int k = a + 1; k < b; ++k) {
+            plo = make_float3(fminf(plo.x, lo[perm[k]].x), fminf(plo.y, lo[perm[k]].y), fminf(plo.z, lo[perm[k]].z));
+            phi = make_float3(fmaxf(phi.x, hi[perm[k]].x), fmaxf(phi.y, hi[perm[k]].y), fmaxf(phi.z, hi[perm[k]].z));
+        }
+        const float parent_area = box_half_area(plo, phi);
+        // best object split: the references sorted by box centre along each axis, every cut position (SAH, costs 1 : 1)
+        float best = 3.0e38f; int best_axis = -1, best_k = 0;
+        if (n > 1) {
+            for (int axis = 0; axis < 3; ++axis) {
+                for (int x = a + 1; x < b; ++x) {                                   // insertion sort of perm[a..b) by centre
+                    const int p = perm[x];
+                    const float key = axis == 0 ? lo[p].x + hi[p].x : (axis == 1 ? lo[p].y + hi[p].y : lo[p].z + hi[p].z);
+                    int y = x - 1;
+                    while (y >= a) {
+                        const int q = perm[y];
+                        const float kq = axis == 0 ? lo[q].x + hi[q].x : (axis == 1 ? lo[q].y + hi[q].y : lo[q].z + hi[q].z);
+                        if (kq <= key) break;
+                        perm[y + 1] = q; --y;
+                    }
+                    perm[y + 1] = p;
+                }
+                float3 rl = lo[perm[b - 1]], rh = hi[perm[b - 1]];
+                for (int k = b - 1; k > a; --k) {
+                    rl = make_float3(fminf(rl.x, lo[perm[k]].x), fminf(rl.y, lo[perm[k]].y), fminf(rl.z, lo[perm[k]].z));
+                    rh = make_float3(fmaxf(rh.x, hi[perm[k]].x), fmaxf(rh.y, hi[perm[k]].y), fmaxf(rh.z, hi[perm[k]].z));
+                    right_area[k] = box_half_area(rl, rh);
+                }
+                float3 ll = lo[perm[a]], lh = hi[perm[a]];
+                for (int k = a + 1; k < b; ++k) {                                   // left = [a, k), right = [k, b)
+                    const float cost = box_half_area(ll, lh) * (float)(k - a) + right_area[k] * (float)(b - k);
+                    if (cost < best) { best = cost; best_axis = axis; best_k = k; }
+                    ll = make_float3(fminf(ll.x, lo[perm[k]].x), fminf(ll.y, lo[perm[k]].y), fminf(ll.z, lo[perm[k]].z));
+                    lh = make_float3(fmaxf(lh.x, hi[perm[k]].x), fmaxf(lh.y, hi[perm[k]].y), fmaxf(lh.z, hi[perm[k]].z));
+                }
+            }
+        }
+        // SplitBVHBuilder.cpp:142: a leaf where the leaf's SAH is the minimum AND it is small enough
+        const bool leaf = n == 1 || (n <= max_leaf && !(parent_area + best < parent_area * (float)n));
+        if (leaf) {
+            reinterpret_cast<int*>(nodes_new + 4 * (size_t)(where >> 2) + 3)[where & 3] = ~(base + a);
+            for (int k = a; k < b; ++k) follow[k] = b - 1 - k;
+            continue;
+        }
+        for (int x = a + 1; x < b; ++x) {                                           // back to the winning axis' order
+            const int p = perm[x];
+            const float key = best_axis == 0 ? lo[p].x + hi[p].x : (best_axis == 1 ? lo[p].y + hi[p].y : lo[p].z + hi[p].z);
+            int y = x - 1;
+            while (y >= a) {
+                const int q = perm[y];
+                const float kq = best_axis == 0 ? lo[q].x + hi[q].x : (best_axis == 1 ? lo[q].y + hi[q].y : lo[q].z + hi[q].z);
+                if (kq <= key) break;
+                perm[y + 1] = q; --y;
+            }
+            perm[y + 1] = p;
+        }
+        float3 l0 = lo[perm[a]], h0 = hi[perm[a]], l1 = lo[perm[best_k]], h1 = hi[perm[best_k]];
+        for (int k = a + 1; k < best_k; ++k) {
+            l0 = make_float3(fminf(l0.x, lo[perm[k]].x), fminf(l0.y, lo[perm[k]].y), fminf(l0.z, lo[perm[k]].z));
+            h0 = make_float3(fmaxf(h0.x, hi[perm[k]].x), fmaxf(h0.y, hi[perm[k]].y), fmaxf(h0.z, hi[perm[k]].z));
+        }
+        for (int k = best_k + 1; k < b; ++k) {
+            l1 = make_float3(fminf(l1.x, lo[perm[k]].x), fminf(l1.y, lo[perm[k]].y), fminf(l1.z, lo[perm[k]].z));
+            h1 = make_float3(fmaxf(h1.x, hi[perm[k]].x), fmaxf(h1.y, hi[perm[k]].y), fmaxf(h1.z, hi[perm[k]].z));
+        }
+        const int id = next_node++;
+        nodes_new[4 * (size_t)id + 0] = make_float4(l0.x, h0.x, l0.y, h0.y);       // the packed node layout, gpt_scene.cuh
+        nodes_new[4 * (size_t)id + 1] = make_float4(l1.x, h1.x, l1.y, h1.y);
+        nodes_new[4 * (size_t)id + 2] = make_float4(l0.z, h0.z, l1.z, h1.z);
+        nodes_new[4 * (size_t)id + 3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        reinterpret_cast<int*>(nodes_new + 4 * (size_t)(where >> 2) + 3)[where & 3] = 4 * id;
+        st_a[sp] = best_k; st_b[sp] = b; st_where[sp] = 4 * id + 1; ++sp;
+        st_a[sp] = a; st_b[sp] = best_k; st_where[sp] = 4 * id + 0; ++sp;
+    }
+    for (int k = 0; k < cnt; ++k) {                                                 // the leaf's rows in their new order
+        const size_t src = GPT_TRI_STRIDE * (size_t)(base + perm[k]), dst = GPT_TRI_STRIDE * (size_t)(base + k);
+        float4 c = tris_old[src + GPT_TRI_B + 1];
+        c.w = __int_as_float(follow[k]);
+        tris_new[dst] = tris_old[src]; tris_new[dst + GPT_TRI_B] = tris_old[src + GPT_TRI_B]; tris_new[dst + GPT_TRI_B + 1] = c;
+    }
+}
+
+// status: 0 ok (out filled: a NEW node array and a NEW triangle array of the same triangle count), 1 nothing to split, 2 too deep
+cudaError_t gptk_split_leaves(const float4* nodes, int n_inner, const float4* tris, int n_tris, const float4* ref_tris, int max_leaf,
+                              RepackResult* out, int* status, unsigned long long* launches, cudaStream_t st)
+{
+    *out = RepackResult{}; *status = 1;
+    if (n_inner < 1 || n_tris < 1) return cudaSuccess;
+    if (max_leaf < 1) max_leaf = 1;
+    const int n_child = 2 * n_inner;
+    int *counts = nullptr, *offsets = nullptr, *flag = nullptr, *level = nullptr;
+    void* tmp = nullptr; size_t tmp_bytes = 0;
+    int extra = 0, depth = 1;
+    cudaError_t e;
+#define CK(x) do { e = (x); if (e != cudaSuccess) goto fail; } while (0)
+    CK(cudaMalloc(&counts, sizeof(int) * (size_t)(n_child + 1)));
+    CK(cudaMalloc(&offsets, sizeof(int) * (size_t)(n_child + 1)));
+    CK(cudaMalloc(&flag, sizeof(int)));
+    CK(cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)(n_child + 1), st));
+    k_split_count<<<(n_child + 255) / 256, 256, 0, st>>>(nodes, n_inner, tris, max_leaf, counts);
+    CK(cudaGetLastError());
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, offsets, n_child + 1, st));
+    CK(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 16));
+    CK(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, counts, offsets, n_child + 1, st));
+    CK(cudaMemcpyAsync(&extra, offsets + n_child, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    *launches += 3;
+    if (extra <= 0) goto done;
+    {
+        const int n_new = n_inner + extra;                                      // an upper bound: unused rows stay zero and unreachable
+        CK(cudaMalloc(&out->nodes, sizeof(float4) * 4 * (size_t)n_new));
+        CK(cudaMalloc(&out->tris, sizeof(float4) * GPT_TRI_STRIDE * ((size_t)n_tris + 1)));
+        CK(cudaMemsetAsync(out->nodes, 0, sizeof(float4) * 4 * (size_t)n_new, st));
+        CK(cudaMemcpyAsync(out->nodes, nodes, sizeof(float4) * 4 * (size_t)n_inner, cudaMemcpyDeviceToDevice, st));
+        CK(cudaMemcpyAsync(out->tris, tris, sizeof(float4) * GPT_TRI_STRIDE * ((size_t)n_tris + 1), cudaMemcpyDeviceToDevice, st));
+        k_split_build<<<(n_child + 63) / 64, 64, 0, st>>>(nodes, n_inner, tris, ref_tris, offsets, max_leaf, out->nodes, out->tris);
+        CK(cudaGetLastError());
+        *launches += 1;
+        // depth of the new tree (children sit behind their parents here too)
+        CK(cudaMalloc(&level, sizeof(int) * (size_t)n_new));
+        CK(cudaMemsetAsync(level, 0, sizeof(int) * (size_t)n_new, st));
+        { const int one = 1; CK(cudaMemcpyAsync(level, &one, sizeof(int), cudaMemcpyHostToDevice, st)); }
+        for (; depth <= GPT_STACK_SIZE; ++depth) {
+            int h_changed = 0;
+            CK(cudaMemsetAsync(flag, 0, sizeof(int), st));
+            k_node_levels<<<(n_new + 255) / 256, 256, 0, st>>>(out->nodes, n_new, level, depth, flag);
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(&h_changed, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            if (!h_changed) break;
+        }
+        out->n_nodes = n_new; out->n_tris = n_tris; out->depth = depth;
+        *status = depth >= GPT_STACK_SIZE ? 2 : 0;
+        if (*status) { cudaFree(out->nodes); cudaFree(out->tris); *out = RepackResult{}; }
+    }
+done:
+    cudaFree(counts); cudaFree(offsets); cudaFree(flag); cudaFree(tmp); cudaFree(level);
+    return cudaSuccess;
+fail:
+    cudaFree(counts); cudaFree(offsets); cudaFree(flag); cudaFree(tmp); cudaFree(level);
+    cudaFree(out->nodes); cudaFree(out->tris); *out = RepackResult{};
+    return e;
+#undef CK
+}

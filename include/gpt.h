@@ -21,7 +21,7 @@
  *   - has to grow the scratch buffers (first call, a larger frame, more samples per call, a deeper path),
  *   - finds new BVH pointers in kernelInfo and re-packs them (gpt_launch; this also builds the rebuilt tree, gpt_rebuild_info), or
  *     builds the 4-wide tree (first render of a scene),
- *   - is one of the timed calls of the per-scene trial (gpt_trial_info; the first <= 12 render calls of >= 1 Mi paths after a
+ *   - is one of the timed calls of the per-scene trial (gpt_trial_info; the first <= 12 render calls of >= 1 Mi paths -- >= 393 216 paths when a rebuilt tree is a candidate -- after a
  *     scene upload on scenes with more than one candidate tree or ray order; GPT_FLAG_NO_TRIAL switches the trial off).
  * gpt_upload_scene, gpt_build_bvh, gpt_set_triangle_materials, gpt_get_stats, gpt_get_kernel_times, gpt_reset_stats,
  * gpt_render_frame_host and the gpt_frame_* setup calls always synchronise.
@@ -310,7 +310,14 @@ GPT_API int gpt_reorder_info(gpt_ctx* ctx, int* state, double* ns_per_ray_path_o
  * tree).  Not built for arrays that come from gpt_build_bvh, nor under GPT_FLAG_KEEP_TREE / _BINARY_BVH / _WIDE_BVH / _MEGAKERNEL.
  * *state = 1 in use, 0 not, -1 on trial; *ns_per_ray = its timed trial calls (0 = not measured). */
 GPT_API int gpt_rebuild_info(gpt_ctx* ctx, int* state, int* n_inner_nodes, int* depth, double* ns_per_ray, float* build_ms);
-/* The per-scene trial behind both choices (tree and ray order): *pending = 1 while large render calls are still being timed;
+/* All candidate trees at once.  *tree_in_use: 0 the binary tree as uploaded, 1 its 4-wide collapse, 2 the rebuilt tree (above), 3 the
+ * uploaded tree with its leaves split: every leaf of 3 .. 16 references replaced by a small SAH subtree (one thread per leaf at
+ * pack time; the reference builder stops at leaves of up to 8 references, the kernels here want 1-2) -- what the reference builder
+ * itself would have produced with a leaf cap of 2, and on large meshes a better tree than the rebuilt one.  Built and tried under the
+ * same rules as the rebuilt tree (GPT_FLAG_KEEP_TREE; GPT_SPLIT=0 / 1 in the environment), with the same caveat (t-ties).
+ * ns_per_ray[i] / n_inner_nodes[i]: the trial's figure (0 = not measured) and the node count (0 = not built) of tree i. */
+GPT_API int gpt_tree_info(gpt_ctx* ctx, int* tree_in_use, int* pending, double ns_per_ray[4], int n_inner_nodes[4]);
+/* The per-scene trial behind both choices (tree and ray order): *pending = 1 while large render calls (>= 1 Mi paths; >= 393 216 when a rebuilt tree is a candidate) are still being timed;
  * ns_per_ray = whole-call ns per ray of the timed calls so far: [0] binary tree, [1] 4-wide tree (both in path order),
  * [2] the faster tree with rays re-ordered; 0 = not measured (candidate forced, closed, or not reached yet). */
 GPT_API int gpt_trial_info(gpt_ctx* ctx, int* pending, double ns_per_ray[3]);

@@ -56,7 +56,7 @@ def main():
         torch.cuda.profiler.stop()
         st = ctx.stats()
         out = {"scene": name, "width": W, "height": H, "spp": spp, "depth": 8, "triangles": int(len(faces)), "rays": int(st.rays), "paths": int(st.paths),
-               "launches": int(st.kernel_launches), "tree_in_use": "rebuilt" if ctx.rebuild_info()["state"] == 1 else ("4-wide" if ctx.wide_info()[0] else "binary"), "reorder": ctx.reorder_info()[0]}
+               "launches": int(st.kernel_launches), "tree_in_use": ctx.tree_info()["in_use"], "reorder": ctx.reorder_info()[0]}
         print(json.dumps(out))
         d = os.path.join(ROOT, "gpurun_out")
         if os.path.isdir(d):

@@ -172,7 +172,7 @@ def main():
             max_diff_px = max(max_diff_px, ndiff)
             frames_equal = frames_equal and ndiff <= max(2, W * H // 100000)
         pending = ctx.trial_info()[0]
-        if (not pending and calls >= 2) or calls >= 12:
+        if (not pending and calls >= 2) or calls >= 20:
             break
     st = ctx.stats()
     a = first.cpu().numpy()
@@ -202,7 +202,7 @@ def main():
     out["pixels"] = {"size": [W, H], "spp": args.spp, "depth": args.depth, "checked": args.pixels, "differing": bad, "worst_abs_diff": worst,
                      "render_calls": calls, "frames_equal_across_calls": frames_equal, "max_pixels_differing_between_calls": max_diff_px, "trial_pending_after": trial_pending,
                      "trial_ns_per_ray": ns_per_ray, "rebuilt": ctx.rebuild_info(),
-                     "tree_in_use": "rebuilt" if ctx.rebuild_info()["state"] == 1 else ("4-wide" if ctx.wide_info()[0] else "binary"),
+                     "tree_in_use": ctx.tree_info()["in_use"], "trees": ctx.tree_info(),
                      "reorder_state": ctx.reorder_info()[0], "paths": int(st.paths), "rays": int(st.rays),
                      "count_plane_ok": bool((a[..., 3] == args.spp).all()), "finite": bool(np.isfinite(a).all())}
     if st.paths != calls * W * H * args.spp:
@@ -212,7 +212,7 @@ def main():
     if trial_pending:
         fails.append("pixels: the per-scene trial never ended")
     # the wide tree may resolve a bit-equal-t tie between two triangles the other way (same t, same material here): allow one pixel
-    if bad > (1 if (ctx.wide_info()[0] or ctx.rebuild_info()["state"] == 1) else 0):
+    if bad > (1 if ctx.tree_info()["in_use"] != "binary" else 0):
         fails.append("pixels: %d of %d differ from the oracle" % (bad, args.pixels))
     if built is not None:
         ctx.free_bvh(built)

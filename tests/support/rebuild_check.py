@@ -46,15 +46,20 @@ def main():
     keep = gpt.Context(0, gpt.FLAG_KEEP_TREE)
     keep.upload_scene(sc["nodes"], sc["tris"], sc["indices"], sph)
     out["rebuilt"] = ctx.rebuild_info()
+    out["trees"] = ctx.tree_info()
     out["rebuilt_under_keep_tree"] = keep.rebuild_info()
-    if keep.rebuild_info()["inner_nodes"] != 0 or keep.rebuild_info()["state"] != 0:
+    kt = keep.tree_info()
+    if keep.rebuild_info()["inner_nodes"] != 0 or keep.rebuild_info()["state"] != 0 or kt["inner_nodes"]["split"] != 0 or kt["in_use"] not in ("binary", "4-wide"):
         fails.append("GPT_FLAG_KEEP_TREE still built a second tree")
     if out["rebuilt"]["inner_nodes"] <= 0:
         fails.append("no rebuilt tree")
+    forced = "split" if os.environ.get("GPT_SPLIT") == "1" else "rebuilt"
+    if forced == "split" and out["trees"]["inner_nodes"]["split"] <= out["trees"]["inner_nodes"]["binary"]:
+        fails.append("no split-leaf tree")
 
     if not args.trial:
-        if out["rebuilt"]["state"] != 1:
-            fails.append("GPT_REBUILD=1 but the rebuilt tree is not in use")
+        if out["trees"]["in_use"] != forced:
+            fails.append("the %s tree is forced by the environment but %s is in use" % (forced, out["trees"]["in_use"]))
         # ---- rays
         n = 20000
         o, d = incoherent_rays(sc["verts"], n, 11)
@@ -110,6 +115,15 @@ def main():
             if nd > 2 or not np.isfinite(got).all():
                 fails.append("frame (%s): %d pixels differ from the oracle" % (label, nd))
         ctx.set_triangle_materials(None, None)
+        # ---- the entry point that allocates nothing walks the same tree: bit-identical to gpt_render
+        acc_s = torch.zeros(150, 200, 4, dtype=torch.float32, device="cuda")
+        acc_r = torch.zeros_like(acc_s)
+        ctx.render_static(info, acc_s, 33, 6, 5)
+        ctx.render(info, acc_r, 33, 6, 5)
+        torch.cuda.synchronize()
+        out["static_equals_render"] = bool(torch.equal(acc_s, acc_r)) and float(acc_r[..., 3].min()) == 5.0
+        if not out["static_equals_render"]:
+            fails.append("gpt_render_static differs from gpt_render on the rebuilt tree")
     else:
         W, H = 1920, 1080
         info = gpt.default_kernel_info(W, H)
@@ -137,12 +151,14 @@ def main():
             torch.cuda.synchronize()
             worst = max(worst, int((acc != ref).any(dim=-1).sum().item()))
         pend, ns = ctx.trial_info()
-        out["trial"] = {"calls": calls, "pending_after": pend, "ns_per_ray_binary_wide_sorted": ns, "rebuilt": ctx.rebuild_info(),
+        out["trial"] = {"calls": calls, "pending_after": pend, "ns_per_ray_binary_wide_sorted": ns, "rebuilt": ctx.rebuild_info(), "trees": ctx.tree_info(),
                         "states_during": states, "max_pixels_differing_from_uploaded_tree": worst, "pixels": W * H}
         if pend or ns[0] <= 0.0 or out["trial"]["rebuilt"]["ns_per_ray"] <= 0.0:
             fails.append("the trial did not time both trees")
-        if out["trial"]["rebuilt"]["state"] not in (0, 1):
+        if out["trial"]["rebuilt"]["state"] not in (0, 1) or out["trial"]["trees"]["pending"]:
             fails.append("rebuilt tree still on trial")
+        if out["trial"]["trees"]["inner_nodes"]["split"] and out["trial"]["trees"]["ns_per_ray"]["split"] <= 0.0:
+            fails.append("the split-leaf tree was built but not timed")
         if worst > max(2, W * H // 100000):
             fails.append("frames differ between the trees beyond t-ties: %d pixels" % worst)
     ctx.close(); keep.close()

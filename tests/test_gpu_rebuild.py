@@ -13,10 +13,13 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def run_check(scene, *extra, rebuild=None, timeout=900):
+def run_check(scene, *extra, rebuild=None, split=None, timeout=900):
     env = {k: v for k, v in os.environ.items() if not k.startswith("GPT_")}
     if rebuild is not None:
         env["GPT_REBUILD"] = str(rebuild)
+    if split is not None:
+        env["GPT_SPLIT"] = str(split)
+    if rebuild is not None or split is not None:
         env["GPT_SMALL_FRAME_PATHS"] = "0"          # small frames through the wavefront pipeline, like the other parity tests
     out = subprocess.run([sys.executable, os.path.join(HERE, "support", "rebuild_check.py"), scene, *extra],
                          env=env, capture_output=True, text=True, timeout=timeout)
@@ -39,13 +42,20 @@ def test_rebuilt_tree_gives_the_oracle_hits_and_frames(torch_cuda, scene):
     assert r["rebuilt"]["state"] == 1 and r["rays"]["t_mismatch"] == 0 and r["primary"]["t_mismatch"] == 0
 
 
-def test_default_policy_times_both_trees_and_keeps_the_image(torch_cuda):
-    """no GPT_* variable: the 5 000-triangle bench scene gets a rebuilt tree at upload and a trial of 2 x 3 large render calls"""
+@pytest.mark.parametrize("scene", ["bunny_cornell", "dragon_cornell", "gto_sixteen", "sphere_mesh"])
+def test_split_leaf_tree_gives_the_oracle_hits_and_frames(torch_cuda, scene):
+    """GPT_SPLIT=1: every call traverses the uploaded tree with its leaves split (gpt_tree_info); same checks"""
+    r = run_check(scene, split=1)
+    assert r["trees"]["in_use"] == "split" and r["rays"]["t_mismatch"] == 0 and r["primary"]["t_mismatch"] == 0
+
+
+def test_default_policy_times_the_trees_and_keeps_the_image(torch_cuda):
+    """no GPT_* variable: the 5 000-triangle bench scene gets a rebuilt and a split-leaf tree at upload and a trial of 3 x 3 large calls"""
     r = run_check("bunny_cornell", "--trial")
-    assert r["trial"]["calls"] == 6 and r["trial"]["rebuilt"]["build_ms"] > 0.0
+    assert r["trial"]["calls"] == 9 and r["trial"]["rebuilt"]["build_ms"] > 0.0
 
 
-def test_default_policy_with_the_wide_tree_as_third_candidate(torch_cuda):
-    """100 k triangles on the reference's SBVH: uploaded binary tree, its 4-wide collapse and the rebuilt tree, three calls each"""
+def test_default_policy_with_the_wide_tree_as_fourth_candidate(torch_cuda):
+    """100 k triangles on the reference's SBVH: uploaded binary tree, its 4-wide collapse, the rebuilt and the split-leaf tree, three calls each"""
     r = run_check("dragon_cornell", "--trial")
-    assert r["trial"]["calls"] == 9
+    assert r["trial"]["calls"] == 12
