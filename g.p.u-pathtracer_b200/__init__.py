@@ -106,7 +106,7 @@ assert C.sizeof(BVHData) == 48 and C.sizeof(kernelInfo) == 296
 # every symbol include/gpt.h declares (tests check the library exports each one)
 EXPORTS = ["gpt_create", "gpt_destroy", "gpt_set_flags", "gpt_last_error_string", "gpt_version", "gpt_sync",
            "gpt_upload_scene", "gpt_launch", "gpt_invalidate_scene", "gpt_render", "gpt_render_static", "gpt_resolve", "gpt_render_frame_host",
-           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_measure_peaks", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info", "gpt_rebuild_info", "gpt_tree_info",
+           "gpt_trace_primary", "gpt_trace_rays", "gpt_get_stats", "gpt_reset_stats", "gpt_get_kernel_times", "gpt_measure_peaks", "gpt_wide_info", "gpt_reorder_info", "gpt_trial_info", "gpt_rebuild_info", "gpt_tree_info", "gpt_megakernel_tree_info",
            "gpt_build_bvh", "gpt_free_bvh", "gpt_copy_to_host",
            "gpt_frame_alloc", "gpt_frame_open_peers", "gpt_frame_ptr", "gpt_frame_clear", "gpt_reduce_resolve",
            "gpt_reduce_resolve_ptrs", "gpt_frame_free",
@@ -151,6 +151,7 @@ def load_library():
     L.gpt_reorder_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.gpt_trial_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double)]
     L.gpt_tree_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int)]
+    L.gpt_megakernel_tree_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double)]
     L.gpt_rebuild_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_float)]
     L.gpt_build_bvh.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.POINTER(BuiltBVH)]
     L.gpt_free_bvh.argtypes = [C.c_void_p, C.POINTER(BuiltBVH)]
@@ -517,6 +518,13 @@ class Context:
         self._ck(self._L.gpt_tree_info(self._h, C.byref(use), C.byref(pend), ns, nn), "gpt_tree_info")
         return {"in_use": self.TREE_NAMES[use.value], "pending": bool(pend.value), "ns_per_ray": dict(zip(self.TREE_NAMES, list(ns))),
                 "inner_nodes": dict(zip(self.TREE_NAMES, list(nn)))}
+
+    def megakernel_tree_info(self):
+        """{in_use: name, pending, ns_per_ray: {name: ns}}: the megakernel's own tree trial (gpt_megakernel_tree_info)"""
+        use, pend = C.c_int(0), C.c_int(0)
+        ns = (C.c_double * 4)()
+        self._ck(self._L.gpt_megakernel_tree_info(self._h, C.byref(use), C.byref(pend), ns), "gpt_megakernel_tree_info")
+        return {"in_use": self.TREE_NAMES[use.value], "pending": bool(pend.value), "ns_per_ray": dict(zip(self.TREE_NAMES, list(ns)))}
 
     def rebuild_info(self):
         """the rebuilt tree (gpt_rebuild_info): {state: 1 in use / 0 not / -1 on trial, inner_nodes, depth, ns_per_ray, build_ms}"""

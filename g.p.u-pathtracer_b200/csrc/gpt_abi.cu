@@ -32,6 +32,8 @@ struct gpt_ctx {
     bool own_tree = false; const void* built_nodes[8] = {}; int built_next = 0;
     // per-scene choice of traversal structure and ray order (traversal_plan): flags and environment win, else a timed trial
     int tune_step = 0; bool tune_done = false; int tuned_tree = 0; bool tuned_sort = false;      // tree ids: 0 uploaded binary, 1 its 4-wide collapse, 2 rebuilt, 3 leaves split
+    // the single-launch megakernel (small calls) keeps its own trial over the binary trees: what it prefers differs from the pipeline
+    int mega_step = 0; bool mega_done = false; int mega_tree = 0; double mega_ns[4] = {0.0, 0.0, 0.0, 0.0};
     double tune_ns[5] = {0.0, 0.0, 0.0, 0.0, 0.0};     // ns per ray: binary tree / wide tree in path order, chosen tree re-ordered, rebuilt tree, split-leaf tree (path order)
     // identity of the reference arrays the packed BVH was built from (gpt_launch re-packs on change)
     const void* src_nodes = nullptr; const void* src_tris = nullptr; const void* src_idx = nullptr;
@@ -100,6 +102,7 @@ static void free_wide(gpt_ctx* c)
     cudaFree(c->wnodes); c->wnodes = nullptr; c->n_wide = 0; c->wide_levels = 0; c->wide_tried = false;
     c->tune_step = 0; c->tune_done = false; c->tuned_tree = 0; c->tuned_sort = false;      // a new tree: the questions are open again
     c->tune_ns[0] = c->tune_ns[1] = c->tune_ns[2] = c->tune_ns[3] = c->tune_ns[4] = 0.0;
+    c->mega_step = 0; c->mega_done = false; c->mega_tree = 0; c->mega_ns[0] = c->mega_ns[1] = c->mega_ns[2] = c->mega_ns[3] = 0.0;
 }
 
 static void free_alt(gpt_ctx* c)
@@ -319,6 +322,70 @@ static int ensure_sort(gpt_ctx* c, bool want)
     return GPT_OK;
 }
 
+// ---- the same question for the megakernel (calls of fewer than GPT_SMALL_FRAME_PATHS paths: one launchKernel of a small window) ----
+// Candidates: the binary trees among tree_cands (no 4-wide traversal in the megakernel, no ray order to choose).  Calls of >= 16 Ki
+// paths take part, three per candidate as above; whole-call ns per ray decide, a later candidate must win by 2 %.  Measured
+// (profiles/r02_schedules.md #70): the megakernel prefers the split-leaf tree on every scene tried, also where the pipeline prefers
+// the rebuilt one, hence a trial of its own.
+static int mega_cands(const gpt_ctx* c, int* ids)
+{
+    int all[4];
+    const int n_all = tree_cands(c, all);
+    int n = 0;
+    for (int k = 0; k < n_all; ++k) if (all[k] != 1) ids[n++] = all[k];
+    if (n == 0) ids[n++] = 0;
+    return n;
+}
+static int mega_best(const gpt_ctx* c, const int* ids, int n)
+{
+    int best = ids[0];
+    for (int k = 1; k < n; ++k) {
+        const double m = c->mega_ns[ids[k]], b = c->mega_ns[best];
+        if (m > 0.0 && b > 0.0 && m < 0.98 * b) best = ids[k];
+    }
+    return best;
+}
+// one megakernel render call (both contracts) on the tree that policy picks
+static int render_mega(gpt_ctx* c, const DevScene& sc_in, const RenderParams& p, float4* accum_f4, float* accum_v3, uint32_t* draw,
+                       unsigned long long constant_pdf, unsigned long long sample_begin, uint32_t sample_count, cudaStream_t st)
+{
+    int ids[4];
+    const int n = mega_cands(c, ids);
+    const size_t n_paths = (size_t)p.width * p.height * sample_count;
+    int tree = n == 1 ? ids[0] : (c->mega_done ? c->mega_tree : ((c->tune_done && c->tuned_tree != 1) ? c->tuned_tree : ids[0]));
+    const bool trial = n > 1 && !c->mega_done && n_paths >= 16384 && !(c->flags & GPT_FLAG_NO_TRIAL) && !k_env_no_trial;
+    const bool timed = trial && (c->mega_step % 3) != 0;
+    if (trial) tree = ids[c->mega_step / 3];
+    DevScene sc = sc_in;
+    set_tree(c, &sc, tree);
+    sc.wnodes = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    unsigned long long rays0 = 0, rays1 = 0;
+    if (timed) {
+        CU(c, cudaStreamSynchronize(st));
+        CU(c, cudaMemcpy(&rays0, c->stats, sizeof(rays0), cudaMemcpyDeviceToHost));
+        CU(c, cudaEventCreate(&e0)); CU(c, cudaEventCreate(&e1));
+        CU(c, cudaEventRecord(e0, st));
+    }
+    cudaError_t e = accum_v3 ? gptk_render_legacy(sc, p, accum_v3, draw, constant_pdf, c->work_counter, c->stats, c->sm_count, st)
+                             : gptk_render_mega(sc, p, accum_f4, sample_begin, sample_count, c->work_counter, c->stats, c->sm_count, st);
+    c->launches += 1;
+    if (e != cudaSuccess) { if (e0) { cudaEventDestroy(e0); cudaEventDestroy(e1); } return fail(c, GPT_ERR_CUDA, "render launch", e); }
+    if (timed) {
+        float ms = 0.0f;
+        cudaEventRecord(e1, st);
+        e = cudaEventSynchronize(e1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+        if (e == cudaSuccess) e = cudaMemcpy(&rays1, c->stats, sizeof(rays1), cudaMemcpyDeviceToHost);
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "megakernel tree trial", e);
+        const double ns = rays1 > rays0 ? (double)ms * 1e6 / (double)(rays1 - rays0) : 0.0;
+        if (ns > 0.0 && (c->mega_ns[tree] <= 0.0 || ns < c->mega_ns[tree])) c->mega_ns[tree] = ns;
+    }
+    if (trial && ++c->mega_step >= 3 * n) { c->mega_done = true; c->mega_tree = mega_best(c, ids, n); }
+    return GPT_OK;
+}
+
 // one wavefront render call under that policy (both contracts)
 static int render_wavefront(gpt_ctx* c, const DevScene& sc_in, const RenderParams& p, float4* accum_f4, float* accum_v3, uint32_t* draw,
                             unsigned long long constant_pdf, unsigned long long sample_begin, uint32_t sample_count, cudaStream_t st)
@@ -410,7 +477,7 @@ static int pack_bvh_from_device(gpt_ctx* c, const void* nodes, size_t n_node_vec
     c->nodes = r.nodes; c->tris = r.tris; c->n_nodes = r.n_nodes; c->n_tris = r.n_tris; c->tree_depth = r.depth;
     // the same triangle references under a tree of this library's own builder (see k_env_rebuild); failure just leaves the one above
     const bool wanted = !c->own_tree && k_env_rebuild != 0 && !(c->flags & (GPT_FLAG_KEEP_TREE | GPT_FLAG_BINARY_BVH | GPT_FLAG_WIDE_BVH | GPT_FLAG_MEGAKERNEL)) &&
-                        ((k_env_rebuild > 0 || k_env_split > 0) ? c->n_tris >= 2 : (c->n_tris >= (1 << 10) && c->n_tris <= (4 << 20)));
+                        ((k_env_rebuild > 0 || k_env_split > 0) ? c->n_tris >= 2 : (c->n_tris >= 16 && c->n_tris <= (4 << 20)));
     if (wanted) {
         static const int k_env_ploc = []{ const char* v = getenv("GPT_PLOC_RADIUS"); return (v && *v) ? atoi(v) : 24; }();
         RepackResult a; int status = 0; float ms = 0.0f;
@@ -647,6 +714,17 @@ int gpt_tree_info(gpt_ctx* c, int* tree_in_use, int* pending, double ns_per_ray[
     return GPT_OK;
 }
 
+int gpt_megakernel_tree_info(gpt_ctx* c, int* tree_in_use, int* pending, double ns_per_ray[4])
+{
+    if (!c) return GPT_ERR_INVALID;
+    int ids[4];
+    const int n = mega_cands(c, ids);
+    if (tree_in_use) *tree_in_use = n == 1 ? ids[0] : (c->mega_done ? c->mega_tree : ((c->tune_done && c->tuned_tree != 1) ? c->tuned_tree : ids[0]));
+    if (pending) *pending = (n > 1 && !c->mega_done && !(c->flags & GPT_FLAG_NO_TRIAL) && !k_env_no_trial) ? 1 : 0;
+    if (ns_per_ray) for (int i = 0; i < 4; ++i) ns_per_ray[i] = c->mega_ns[i];
+    return GPT_OK;
+}
+
 int gpt_trial_info(gpt_ctx* c, int* pending, double ns_per_ray[3])
 {
     if (!c) return GPT_ERR_INVALID;
@@ -707,16 +785,10 @@ int gpt_launch(gpt_ctx* c, const gpt_kernel_info* info, gpt_stream stream)
     RenderParams p; DevScene sc;
     int rc = make_params(c, info, info->hash, &p); if (rc) return rc;
     rc = launch_scene(c, info, &sc); if (rc) return rc;
-    cudaError_t e;
     if (!use_megakernel(c, (size_t)p.width * p.height)) {
         return render_wavefront(c, sc, p, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u, (cudaStream_t)stream);
-    } else {
-        e = gptk_render_legacy(sc, p, info->accumBuffer, info->dev_drawRes, info->constantPdf,
-                               c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
-        c->launches += 1;
     }
-    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "render launch", e);
-    return GPT_OK;
+    return render_mega(c, sc, p, nullptr, info->accumBuffer, info->dev_drawRes, info->constantPdf, 0ull, 1u, (cudaStream_t)stream);
 }
 
 int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_t seed, uint64_t sample_begin,
@@ -728,16 +800,10 @@ int gpt_render(gpt_ctx* c, const gpt_kernel_info* info, float* accum_f4, uint64_
     RenderParams p; DevScene sc;
     int rc = make_params(c, info, seed, &p); if (rc) return rc;
     rc = launch_scene(c, info, &sc); if (rc) return rc;
-    cudaError_t e;
     if (!use_megakernel(c, (size_t)p.width * p.height * sample_count)) {
         return render_wavefront(c, sc, p, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count, (cudaStream_t)stream);
-    } else {
-        e = gptk_render_mega(sc, p, reinterpret_cast<float4*>(accum_f4), sample_begin, sample_count,
-                             c->work_counter, c->stats, c->sm_count, (cudaStream_t)stream);
-        c->launches += 1;
     }
-    if (e != cudaSuccess) return fail(c, GPT_ERR_CUDA, "render launch", e);
-    return GPT_OK;
+    return render_mega(c, sc, p, reinterpret_cast<float4*>(accum_f4), nullptr, nullptr, 1ull, sample_begin, sample_count, (cudaStream_t)stream);
 }
 
 int gpt_resolve(gpt_ctx* c, const float* accum_f4, int width, int height, uint32_t* out_rgba8, float* out_rgb_f32, gpt_stream stream)

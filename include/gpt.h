@@ -303,7 +303,7 @@ GPT_API int gpt_wide_info(gpt_ctx* ctx, int* n_wide, int* levels);
  * trial gpt_trial_info describes); the two figures are the trial's whole-call times for the tree in use. */
 GPT_API int gpt_reorder_info(gpt_ctx* ctx, int* state, double* ns_per_ray_path_order, double* ns_per_ray_reordered);
 /* The rebuilt tree.  When arrays in the reference's layout are packed (gpt_upload_scene, or new BVH pointers in gpt_launch) and hold
- * 1 Ki .. 4 Mi triangle references, the library also builds a tree of its own over the SAME references (device PLOC builder, the
+ * 16 .. 4 Mi triangle references, the library also builds a tree of its own over the SAME references (device PLOC builder, the
  * caller's exact vertices; a few ms) and lets the per-scene trial decide between the two: the reference's SBVH is shaped for its own
  * kernel, and the extend kernel here runs 15-20 % faster on the rebuilt one.  Distances, face indices and slots are those of the
  * uploaded arrays bit for bit; what can differ is which of two triangles hit at bit-equal distance is met first (as for the 4-wide
@@ -317,6 +317,10 @@ GPT_API int gpt_rebuild_info(gpt_ctx* ctx, int* state, int* n_inner_nodes, int* 
  * same rules as the rebuilt tree (GPT_FLAG_KEEP_TREE; GPT_SPLIT=0 / 1 in the environment), with the same caveat (t-ties).
  * ns_per_ray[i] / n_inner_nodes[i]: the trial's figure (0 = not measured) and the node count (0 = not built) of tree i. */
 GPT_API int gpt_tree_info(gpt_ctx* ctx, int* tree_in_use, int* pending, double ns_per_ray[4], int n_inner_nodes[4]);
+/* The same for the single-launch megakernel (calls of fewer than GPT_SMALL_FRAME_PATHS paths, e.g. one launchKernel of a small
+ * window): it keeps a trial of its own over the binary trees (0, 2, 3; calls of >= 16 Ki paths, three per candidate, the timed ones
+ * synchronise) because what it prefers differs from the pipeline's choice.  ns_per_ray[1] stays 0. */
+GPT_API int gpt_megakernel_tree_info(gpt_ctx* ctx, int* tree_in_use, int* pending, double ns_per_ray[4]);
 /* The per-scene trial behind both choices (tree and ray order): *pending = 1 while large render calls (>= 1 Mi paths; >= 393 216 when a rebuilt tree is a candidate) are still being timed;
  * ns_per_ray = whole-call ns per ray of the timed calls so far: [0] binary tree, [1] 4-wide tree (both in path order),
  * [2] the faster tree with rays re-ordered; 0 = not measured (candidate forced, closed, or not reached yet). */

@@ -41,7 +41,7 @@ for name, W, H, depth in [("cornell", 512, 512, 4), ("dragon_cornell", 1280, 720
     for label, flags in (("wavefront", gpt.FLAG_WAVEFRONT), ("megakernel", gpt.FLAG_MEGAKERNEL), ("default", 0)):
         with gpt.Context(0, flags) as ctx:
             res["gpt_launch_%s_ms" % label] = loop(ctx.launch)
-            res["rebuilt_tree_in_use_%s" % label] = ctx.rebuild_info()["state"]
+            res["tree_%s" % label] = ctx.tree_info()["in_use"] if W * H >= 393216 or label == "wavefront" else ctx.megakernel_tree_info()["in_use"]
     print(json.dumps(res), flush=True)
     out = os.path.join(ROOT, "gpurun_out")
     if os.path.isdir(out):

@@ -150,6 +150,24 @@ def main():
             ctx.render(info, acc, 5, 0, 4)
             torch.cuda.synchronize()
             worst = max(worst, int((acc != ref).any(dim=-1).sum().item()))
+        # ---- the megakernel's own trial: small calls (96 x 64 x 4 spp = 24 576 paths) until it has ended; frames equal to the uploaded tree's
+        si = gpt.default_kernel_info(96, 64)
+        si.depth = 5
+        sref = torch.zeros(64, 96, 4, dtype=torch.float32, device="cuda")
+        sacc = torch.zeros_like(sref)
+        keep.render(si, sref, 7, 0, 4)
+        mcalls, mworst = 0, 0
+        while mcalls < 16:
+            sacc.zero_()
+            ctx.render(si, sacc, 7, 0, 4)
+            torch.cuda.synchronize()
+            mcalls += 1
+            mworst = max(mworst, int((sacc != sref).any(dim=-1).sum().item()))
+            if not ctx.megakernel_tree_info()["pending"]:
+                break
+        out["megakernel_trial"] = dict(ctx.megakernel_tree_info(), calls=mcalls, max_pixels_differing_from_uploaded_tree=mworst)
+        if out["megakernel_trial"]["pending"] or mcalls != 9 or mworst > 2:
+            fails.append("megakernel tree trial: %r" % (out["megakernel_trial"],))
         pend, ns = ctx.trial_info()
         out["trial"] = {"calls": calls, "pending_after": pend, "ns_per_ray_binary_wide_sorted": ns, "rebuilt": ctx.rebuild_info(), "trees": ctx.tree_info(),
                         "states_during": states, "max_pixels_differing_from_uploaded_tree": worst, "pixels": W * H}
