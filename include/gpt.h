@@ -21,8 +21,10 @@
  *   - has to grow the scratch buffers (first call, a larger frame, more samples per call, a deeper path),
  *   - finds new BVH pointers in kernelInfo and re-packs them (gpt_launch; this also builds the rebuilt tree, gpt_rebuild_info), or
  *     builds the 4-wide tree (first render of a scene),
- *   - is one of the timed calls of the per-scene trial (gpt_trial_info; the first <= 12 render calls of >= 1 Mi paths -- >= 393 216 paths when a rebuilt tree is a candidate -- after a
- *     scene upload on scenes with more than one candidate tree or ray order; GPT_FLAG_NO_TRIAL switches the trial off).
+ *   - is one of the timed calls of the per-scene trial (gpt_trial_info; the first <= 15 render calls of >= 1 Mi paths --
+ *     >= 393 216 paths when a second tree is a candidate -- after a
+ *     scene upload on scenes with more than one candidate tree or ray order; likewise the first <= 9 small calls of >= 16 Ki paths
+ *     for the megakernel's own tree trial, gpt_megakernel_tree_info; GPT_FLAG_NO_TRIAL switches both off).
  * gpt_upload_scene, gpt_build_bvh, gpt_set_triangle_materials, gpt_get_stats, gpt_get_kernel_times, gpt_reset_stats,
  * gpt_render_frame_host and the gpt_frame_* setup calls always synchronise.
  */
