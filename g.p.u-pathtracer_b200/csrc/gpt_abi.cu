@@ -131,7 +131,7 @@ static void free_wave(gpt_ctx* c)
     w = WaveBuffers{}; c->wave_pixels = 0; c->wave_counters = 0;
 }
 
-// wavefront scratch: per-path state for one wave (68 B/path) + one launch sum per pixel.  A wave holds as many
+// wavefront scratch: per-path state for one wave (104 B/path) + one launch sum per pixel.  A wave holds as many
 // samples of the frame as fit GPT_WAVE_MAX_PATHS (5 GB of the 180 GB HBM at the cap); grown on demand.
 #define GPT_WAVE_MAX_PATHS ((size_t)64 << 20)
 static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sample_count)
@@ -144,8 +144,8 @@ static int ensure_wave(gpt_ctx* c, size_t n_pix, unsigned int depth, uint32_t sa
     if (want < c->wave.capacity) want = c->wave.capacity;
     free_wave(c);
     WaveBuffers& w = c->wave;
-    CU(c, cudaMalloc(&w.ray, 2 * want * sizeof(float4)));
-    CU(c, cudaMalloc(&w.mask_z, want * sizeof(float)));  CU(c, cudaMalloc(&w.accu, want * sizeof(float4)));
+    CU(c, cudaMalloc(&w.ray, 2 * 2 * want * sizeof(float4)));        // double-buffered by bounce parity, like the queues
+    CU(c, cudaMalloc(&w.mask_z, 2 * want * sizeof(float)));  CU(c, cudaMalloc(&w.accu, want * sizeof(float4)));
     CU(c, cudaMalloc(&w.hit, want * sizeof(int2)));
     CU(c, cudaMalloc(&w.queue[0], want * sizeof(uint32_t))); CU(c, cudaMalloc(&w.queue[1], want * sizeof(uint32_t)));
     CU(c, cudaMalloc(&w.lsum, n_pix * sizeof(float4)));
@@ -1007,21 +1007,21 @@ int gpt_reset_stats(gpt_ctx* c)
 // No counterpart in the reference; added for callers that cannot call cudaMalloc (code under
 // CUDA graph capture, tight serving loops, harnesses that forbid it).  The per-path state and per-pixel sums that ensure_wave()
 // cudaMallocs for gpt_render live here in ONE file-scope device array of fixed size, so every GPU that loads the library holds
-// GPT_STATIC_SCRATCH_BYTES (21 MiB) until the process exits.  The array's name is a host-side stand-in in host code, not a device
+// GPT_STATIC_SCRATCH_BYTES (30 MiB) until the process exits.  The array's name is a host-side stand-in in host code, not a device
 // address: static_scratch_base() asks the runtime for the address once per device (cudaGetSymbolAddress with that device current)
 // and the kernels only ever see that pointer.
 //   layout (offsets are multiples of 256 B; P = GPT_STATIC_MAX_PATHS paths per wave, X = GPT_STATIC_MAX_PIXELS pixels):
-//     ray 32 P | accu 16 P | lsum 16 X | hit 8 P | mask_z 4 P | queue[0] 4 P | queue[1] 4 P | counters 4 KiB
+//     ray 2 x 32 P | accu 16 P | lsum 16 X | hit 8 P | mask_z 2 x 4 P | queue[0] 4 P | queue[1] 4 P | counters 4 KiB
 // All calls on a device share the array: the queue counters are cleared on `stream` at the start of every call (everything else is
 // written before it is read), and two calls that overlap on the GPU (different streams, or different contexts of one device) race.
 #define GPT_STATIC_P ((size_t)GPT_STATIC_MAX_PATHS)
 #define GPT_STATIC_X ((size_t)GPT_STATIC_MAX_PIXELS)
 #define GPT_STATIC_OFF_RAY      ((size_t)0)
-#define GPT_STATIC_OFF_ACCU     (GPT_STATIC_OFF_RAY + 32 * GPT_STATIC_P)
+#define GPT_STATIC_OFF_ACCU     (GPT_STATIC_OFF_RAY + 64 * GPT_STATIC_P)
 #define GPT_STATIC_OFF_LSUM     (GPT_STATIC_OFF_ACCU + 16 * GPT_STATIC_P)
 #define GPT_STATIC_OFF_HIT      (GPT_STATIC_OFF_LSUM + 16 * GPT_STATIC_X)
 #define GPT_STATIC_OFF_MASK     (GPT_STATIC_OFF_HIT + 8 * GPT_STATIC_P)
-#define GPT_STATIC_OFF_Q0       (GPT_STATIC_OFF_MASK + 4 * GPT_STATIC_P)
+#define GPT_STATIC_OFF_Q0       (GPT_STATIC_OFF_MASK + 8 * GPT_STATIC_P)
 #define GPT_STATIC_OFF_Q1       (GPT_STATIC_OFF_Q0 + 4 * GPT_STATIC_P)
 #define GPT_STATIC_OFF_COUNTERS (GPT_STATIC_OFF_Q1 + 4 * GPT_STATIC_P)
 #define GPT_STATIC_COUNTER_BYTES ((size_t)4096)

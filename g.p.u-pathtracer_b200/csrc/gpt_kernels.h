@@ -90,7 +90,11 @@ cudaError_t gptk_build_wide(const float4* nodes2, int n_inner, WideResult* out, 
 
 // wavefront pipeline (gpt_wavefront.cu).  Per-path arrays hold `capacity` entries, lsum one per pixel.
 struct WaveBuffers {
-    float4 *ray, *accu, *lsum;             // ray: 2 float4 per path = origin + direction, whose w lanes carry the colour mask's x / y
+    // Records of the paths alive at a bounce lie in QUEUE order, double-buffered by bounce parity (gpt_wavefront.cu):
+    // ray: 2 x (2 float4 per slot) = origin + direction, whose w lanes carry the colour mask's x / y; mask_z: 2 x (1 float per slot);
+    // queue[2]: the slot's path id; hit: 1 int2 per slot (written by the extend kernel, read by the shade kernel of the same bounce);
+    // accu: by path id
+    float4 *ray, *accu, *lsum;
     float* mask_z;
     int2* hit;
     uint32_t* queue[2];

@@ -155,7 +155,10 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
                         PathState ps; primary_ray(gen, pid, ps);
                         o = ps.o; d = ps.d;
                     } else {
-                        pid = WF_LD(queue + j);
+                        // the ray records lie in QUEUE order (the shade kernel writes a survivor's record at its queue slot): no
+                        // path id in between, and neighbouring lanes read neighbouring 32-byte records.  `queue` is only the
+                        // permutation of the optional ray re-ordering (nullptr: slot = position)
+                        pid = queue ? WF_LD(queue + j) : j;
                         float4 ro, rd;
                         ld_ray32(ray, pid, ro, rd);
                         o = mk3(ro.x, ro.y, ro.z); d = mk3(rd.x, rd.y, rd.z);
@@ -199,14 +202,12 @@ k_wf_extend_ww(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
 // FAST: GPT_FLAG_FAST shading arithmetic (gpt_math.cuh) -- opt-in, statistically equal, not bit-equal.
 struct ShadeIo {
     const uint32_t* queue_in; unsigned int* counters; uint32_t* queue_out;
-    float4* ray; const int2* hit; float* mask_z; float4* accu;      // ray: 2 float4 per path (ld_ray32 / st_ray32)
+    const float4* ray_in; float4* ray_out; const float* mask_in; float* mask_out;      // records in queue order: 2 float4 + 1 float per slot
+    const int2* hit; float4* accu;                                                       // hit: by the slot of the queue read; accu: by path id
 };
 
 #ifndef WF_SPHERE_LDS
 #define WF_SPHERE_LDS 1
-#endif
-#ifndef WF_SHADE_PIPE
-#define WF_SHADE_PIPE 1
 #endif
 #ifndef WF_SHADE_PF
 #define WF_SHADE_PF 1
@@ -218,14 +219,14 @@ template <int LEVEL> __device__ __forceinline__ void shade_prefetch(const void* 
 }
 
 template <bool FIRST>
-__device__ __forceinline__ void shade_load_path(const PrimaryGen& gen, const ShadeIo& io, const uint32_t pid, PathState& ps)
+__device__ __forceinline__ void shade_load_path(const PrimaryGen& gen, const ShadeIo& io, const uint32_t pid, const unsigned slot, PathState& ps)
 {
     if (FIRST) primary_ray(gen, pid, ps);
     else {
         float4 ro, rd;
-        ld_ray32(io.ray, pid, ro, rd);
+        ld_ray32(io.ray_in, slot, ro, rd);
         ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
-        ps.mask = mk3(ro.w, rd.w, WF_LD(io.mask_z + pid));
+        ps.mask = mk3(ro.w, rd.w, WF_LD(io.mask_in + slot));
     }
     ps.accu = mk3(0.0f, 0.0f, 0.0f);      // accu stays in memory (shade_bounce, accu_slot)
 }
@@ -240,32 +241,26 @@ __device__ __forceinline__ bool shade_finish_path(const DevScene& sc, const Prim
     // accu[pid] is touched inside only on a miss or an emitting hit (always written at bounce 0); when the path is over its
     // radiance (tracer.cu:305, or bkColor on a miss :141) stays there until the wave's samples are summed per pixel
     const bool cont = shade_bounce<FIRST, FAST>(sc, gen.p, s_spheres, s_boxes, h, (uint32_t)gen.pix0 + (pid - s_local * n_wave), gen.sample0 + s_local, bounce, ps, io.accu + pid);
-    const bool survive = cont && !last_bounce;
-    if (survive) {
-        st_ray32(io.ray, pid, make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x), make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y));
-        WF_ST(io.mask_z + pid, ps.mask.z);
-    }
-    return survive;
+    return cont && !last_bounce;          // the survivor's record is stored by the caller, at the queue slot the compaction gives it
 }
 
-// survivors of a warp -> the next bounce's queue: one atomic per warp
-__device__ __forceinline__ void shade_compact(const bool survive, const uint32_t pid, unsigned int* n_out, uint32_t* queue_out, const unsigned lane)
+// survivors of a warp -> slots of the next bounce's queue: one atomic per warp.  Returns this lane's slot (only meaningful if it survives)
+__device__ __forceinline__ unsigned shade_compact(const bool survive, unsigned int* n_out, const unsigned lane)
 {
     const unsigned m = __ballot_sync(GPT_FULL_MASK, survive);
+    unsigned base = 0;
     if (m) {
-        unsigned base = 0;
         const int leader = __ffs(m) - 1;
         if ((int)lane == leader) base = atomicAdd(n_out, (unsigned)__popc(m));
         base = __shfl_sync(GPT_FULL_MASK, base, leader);
-        if (survive) WF_ST(queue_out + (base + (unsigned)__popc(m & ((1u << lane) - 1u))), pid);
     }
+    return base + (unsigned)__popc(m & ((1u << lane) - 1u));
 }
 
 // the same for a whole CTA of 256 threads: ONE atomic per CTA and trip instead of one per warp.  All the queue atomics of a launch hit
 // one address, and the L2's atomic unit serialises them (~0.85 cycles each: 1 M warp-level atomics of a 33 M-path launch are
 // 0.45 ms of a 1.2 ms kernel, and every warp queues behind the others for its result).  Every thread of the CTA must call it.
-__device__ __forceinline__ void shade_compact_cta(const bool survive, const uint32_t pid, unsigned int* n_out, uint32_t* queue_out, const unsigned lane,
-                                                  unsigned* s_cnt, unsigned* s_base)
+__device__ __forceinline__ unsigned shade_compact_cta(const bool survive, unsigned int* n_out, const unsigned lane, unsigned* s_cnt, unsigned* s_base)
 {
     const unsigned m = __ballot_sync(GPT_FULL_MASK, survive);
     const unsigned w = threadIdx.x >> 5;
@@ -278,7 +273,7 @@ __device__ __forceinline__ void shade_compact_cta(const bool survive, const uint
         *s_base = tot ? atomicAdd(n_out, tot) : 0u;
     }
     __syncthreads();
-    if (survive) WF_ST(queue_out + (*s_base + s_cnt[w] + (unsigned)__popc(m & ((1u << lane) - 1u))), pid);
+    return *s_base + s_cnt[w] + (unsigned)__popc(m & ((1u << lane) - 1u));
 }
 
 #ifndef WF_SHADE_CTA_AGG
@@ -308,36 +303,35 @@ k_wf_shade(const DevScene sc, const PrimaryGen gen, const uint32_t bounce, const
     const unsigned n_round = WF_SHADE_CTA_AGG ? ((n + 255u) & ~255u) : ((n + 31u) & ~31u);      // CTA-uniform trip counts for the barriers
     const unsigned stride = gridDim.x * blockDim.x;
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    // A trip starts with three dependent fetches (queue slot -> path id -> ray / hit / mask of that path, scattered 32-B
-    // records): WF_SHADE_PIPE fetches the NEXT trip's path id one trip ahead, WF_SHADE_PF = 1 / 2 also asks L1 / L2 for that
-    // path's records while this trip computes (ncu: long-scoreboard stalls are what the kernel waits on once its arithmetic is cheap)
-    uint32_t pid_next = 0;
-    if (!FIRST && WF_SHADE_PIPE && i < n) pid_next = WF_LD(io.queue_in + i);
+    // Every record of a trip is read at the trip's own queue position i (path id, ray, mask, hit: neighbouring lanes read neighbouring
+    // records, nothing depends on a fetched id); WF_SHADE_PF = 1 / 2 asks L1 / L2 for the next trip's records while this one computes.
     for (; i < n_round; i += stride) {
         bool survive = false, valid = i < n;
         uint32_t pid = 0;
         PathState ps;
         SceneHit h; h.t = GPT_F32_MAX; h.geom = GEO_NONE; h.prim = -1;
-        const bool more = !FIRST && WF_SHADE_PIPE && i + stride < n;
         if (valid) {
-            pid = FIRST ? i : (WF_SHADE_PIPE ? pid_next : WF_LD(io.queue_in + i));
-            if (more) pid_next = WF_LD(io.queue_in + (i + stride));
-            shade_load_path<FIRST>(gen, io, pid, ps);
+            pid = FIRST ? i : WF_LD(io.queue_in + i);
+            shade_load_path<FIRST>(gen, io, pid, i, ps);
             float tri_t = GPT_F32_MAX; int tri = -1;
-            if (has_mesh) { const int2 hh = WF_LD(io.hit + pid); tri_t = __int_as_float(hh.x); tri = hh.y; }
+            if (has_mesh) { const int2 hh = WF_LD(io.hit + i); tri_t = __int_as_float(hh.x); tri = hh.y; }
+            if (WF_SHADE_PF && i + stride < n) {
+                const unsigned i2 = i + stride;
+                if (!FIRST) { shade_prefetch<WF_SHADE_PF>(io.ray_in + 2 * (size_t)i2); if ((lane & 7u) == 0u) { shade_prefetch<WF_SHADE_PF>(io.mask_in + i2); shade_prefetch<WF_SHADE_PF>(io.queue_in + i2); } }
+                if (has_mesh && (lane & 3u) == 0u) shade_prefetch<WF_SHADE_PF>(io.hit + i2);
+            }
             // spheres staged in shared memory: the sweep reads them through the __shared__ array itself (LDS.128), not through the
             // generic pointer, whose 4 x 32-bit LD per sphere wait on the long scoreboard (ncu: the kernel's largest stall)
             if (WF_SPHERE_LDS && sc.n_spheres <= GPT_MAX_SMEM_SPHERES) h = finish_scene_hit_smem<FAST>(sc, sm.posrad, s_boxes, tri_t, tri, ps.o, ps.d);
             else h = finish_scene_hit<FAST>(sc, s_spheres, s_boxes, tri_t, tri, ps.o, ps.d);
-            if (more && WF_SHADE_PF) {
-                shade_prefetch<WF_SHADE_PF>(io.ray + 2 * (size_t)pid_next);
-                shade_prefetch<WF_SHADE_PF>(io.mask_z + pid_next);
-                if (has_mesh) shade_prefetch<WF_SHADE_PF>(io.hit + pid_next);
-            }
         }
         if (valid) survive = shade_finish_path<FIRST, FAST>(sc, gen, io, s_spheres, s_boxes, h, pid, bounce, last_bounce, ps);
-        if (WF_SHADE_CTA_AGG) shade_compact_cta(survive, pid, n_out, io.queue_out, lane, s_cnt, &s_base);
-        else shade_compact(survive, pid, n_out, io.queue_out, lane);
+        const unsigned slot = WF_SHADE_CTA_AGG ? shade_compact_cta(survive, n_out, lane, s_cnt, &s_base) : shade_compact(survive, n_out, lane);
+        if (survive) {
+            st_ray32(io.ray_out, slot, make_float4(ps.o.x, ps.o.y, ps.o.z, ps.mask.x), make_float4(ps.d.x, ps.d.y, ps.d.z, ps.mask.y));
+            WF_ST(io.mask_out + slot, ps.mask.z);
+            WF_ST(io.queue_out + slot, pid);
+        }
     }
 }
 
@@ -426,7 +420,7 @@ __host__ __device__ __forceinline__ int wf_sort_bits(const int mode) { return mo
 // key = Morton cell of the origin (ob bits per axis of the mesh bounds) above Morton cell of the direction (db bits per axis):
 // mode 1: 7 + 1 (octant) = 24 bits   mode 2: 6 + 2 = 24   mode 3: 7 + 3 = 30   mode 4: 9 + 1 = 30   mode 5: 8 + 2 = 30   mode 6: 6 + 4 = 30   mode 7: 5 + 5 = 30   mode 8: 4 + 1 = 15 (two radix passes)   mode 9: 3 + 2 = 15
 __global__ void __launch_bounds__(256)
-k_wf_sort_keys(const DevScene sc, const uint32_t* __restrict__ queue, const unsigned int* __restrict__ n_ptr, const unsigned n_slots,
+k_wf_sort_keys(const DevScene sc, uint32_t* __restrict__ iota, const unsigned int* __restrict__ n_ptr, const unsigned n_slots,
                const float4* __restrict__ ray, uint32_t* __restrict__ keys, const int mode)
 {
     const unsigned n = *n_ptr;
@@ -442,10 +436,10 @@ k_wf_sort_keys(const DevScene sc, const uint32_t* __restrict__ queue, const unsi
     const float ds = (float)(1 << db) * 0.4999f, dmax = (float)((1 << db) - 1);
     for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n_slots; j += gridDim.x * blockDim.x) {
         unsigned key = kmax;
+        iota[j] = j;                                  // the values the keys are sorted with: queue slots
         if (j < n) {
-            const uint32_t pid = queue[j];
             float4 o, d;
-            ld_ray32(ray, pid, o, d);
+            ld_ray32(ray, j, o, d);
             const unsigned cx = (unsigned)fminf(fmaxf((o.x - lox) * sx, 0.0f), omax);
             const unsigned cy = (unsigned)fminf(fmaxf((o.y - loy) * sy, 0.0f), omax);
             const unsigned cz = (unsigned)fminf(fmaxf((o.z - loz) * sz, 0.0f), omax);
@@ -492,14 +486,14 @@ void gptk_wave_launch_cfg(WaveLaunchCfg* cfg, int sm_count)
 
 template <bool PRIMARY>
 static void launch_extend(const DevScene& sc, const RenderParams& p, const WaveLaunchCfg& cfg, const uint32_t* q, unsigned int* n_ptr, unsigned int* fetch,
-                          const WaveBuffers& wb, int node_k, const PrimaryGen& gen, cudaStream_t st)
+                          const float4* ray_in, const WaveBuffers& wb, int node_k, const PrimaryGen& gen, cudaStream_t st)
 {
     if (sc.wnodes) {
-        if (p.cull) k_wf_extend_ww<true, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray, wb.hit, cfg.refill_min, node_k, gen);
-        else k_wf_extend_ww<false, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray, wb.hit, cfg.refill_min, node_k, gen);
+        if (p.cull) k_wf_extend_ww<true, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, ray_in, wb.hit, cfg.refill_min, node_k, gen);
+        else k_wf_extend_ww<false, true, PRIMARY><<<cfg.wide_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, ray_in, wb.hit, cfg.refill_min, node_k, gen);
     } else {
-        if (p.cull) k_wf_extend_ww<true, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray, wb.hit, cfg.refill_min, node_k, gen);
-        else k_wf_extend_ww<false, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, wb.ray, wb.hit, cfg.refill_min, node_k, gen);
+        if (p.cull) k_wf_extend_ww<true, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, ray_in, wb.hit, cfg.refill_min, node_k, gen);
+        else k_wf_extend_ww<false, false, PRIMARY><<<cfg.ext_grid, WF_THREADS, 0, st>>>(sc, q, n_ptr, fetch, ray_in, wb.hit, cfg.refill_min, node_k, gen);
     }
 }
 
@@ -525,7 +519,7 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
     const int n_pix = p.width * p.height;
     const int n_counters = (int)gptk_wave_counter_count(p.depth);
     // A wave = a run of consecutive pixels x a run of consecutive samples, as many paths as the scratch arrays
-    // hold (68 B/path).  Big waves matter: every launch has a fixed cost (launch gap + the tail where the
+    // hold (104 B/path).  Big waves matter: every launch has a fixed cost (launch gap + the tail where the
     // persistent extend kernel drains), measured at ~19 us, and a 1080p x 1 spp wave needs 17 launches.
     size_t cap = wb.capacity;
     if (cfg.wave_cap_env && cfg.wave_cap_env < cap) cap = cfg.wave_cap_env < 1024 ? 1024 : cfg.wave_cap_env;
@@ -548,27 +542,34 @@ cudaError_t gptk_render_wavefront(const DevScene& sc, const RenderParams& p, con
             int cgrid = (n_wave + 255) / 256; if (cgrid > sm_count * 8) cgrid = sm_count * 8; if (cgrid < 1) cgrid = 1;
             PrimaryGen gen; gen.p = p; gen.sample0 = sample_begin + s0; gen.pix0 = pix0; gen.n_wave = n_wave; gen.n_paths = (unsigned)n_paths;
             for (uint32_t b = 0; b < p.depth; ++b) {
+                // path ids, rays and masks of the paths alive at bounce b lie in queue order in the buffers of parity b & 1; the shade
+                // kernel of bounce b writes the survivors' records into the buffers of the other parity
                 const uint32_t* q_in = b == 0 ? nullptr : wb.queue[b & 1u];
-                const uint32_t* q_ext = q_in;       // order in which the extend kernel fetches the rays
+                const float4* ray_in = wb.ray + (size_t)(b & 1u) * 2 * wb.capacity;
+                float4* ray_out = wb.ray + (size_t)((b + 1u) & 1u) * 2 * wb.capacity;
+                const float* mask_in = wb.mask_z + (size_t)(b & 1u) * wb.capacity;
+                float* mask_out = wb.mask_z + (size_t)((b + 1u) & 1u) * wb.capacity;
+                const uint32_t* q_ext = nullptr;    // order in which the extend kernel fetches the slots: queue order, or the re-ordering's permutation
                 if (has_mesh && b > 0 && wb.sort_vals) {
                     if (kt) kt->tick(KT_OTHER, st);
-                    k_wf_sort_keys<<<grid, 256, 0, st>>>(sc, q_in, wb.counters + b, (unsigned)n_paths, wb.ray, wb.sort_keys[0], cfg.sort_mode);
+                    uint32_t* iota = wb.queue[(b + 1u) & 1u];      // free until this bounce's shade kernel fills it
+                    k_wf_sort_keys<<<grid, 256, 0, st>>>(sc, iota, wb.counters + b, (unsigned)n_paths, ray_in, wb.sort_keys[0], cfg.sort_mode);
                     size_t tb = wb.sort_tmp_bytes;
-                    if ((e = cub::DeviceRadixSort::SortPairs(wb.sort_tmp, tb, (const uint32_t*)wb.sort_keys[0], wb.sort_keys[1], q_in, wb.sort_vals,
+                    if ((e = cub::DeviceRadixSort::SortPairs(wb.sort_tmp, tb, (const uint32_t*)wb.sort_keys[0], wb.sort_keys[1], (const uint32_t*)iota, wb.sort_vals,
                                                              (long long)n_paths, 0, wf_sort_bits(cfg.sort_mode), st)) != cudaSuccess) return e;
                     *launches += 4;
                     q_ext = wb.sort_vals;
                 }
                 if (has_mesh) {
                     if (kt) kt->tick(KT_EXTEND, st);
-                    if (b == 0) launch_extend<true>(sc, p, cfg, nullptr, wb.counters, wb.counters + p.depth + 1, wb, node_k, gen, st);
-                    else launch_extend<false>(sc, p, cfg, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, wb, node_k, gen, st);
+                    if (b == 0) launch_extend<true>(sc, p, cfg, nullptr, wb.counters, wb.counters + p.depth + 1, ray_in, wb, node_k, gen, st);
+                    else launch_extend<false>(sc, p, cfg, q_ext, wb.counters + b, wb.counters + p.depth + 1 + b, ray_in, wb, node_k, gen, st);
                     *launches += 1;
                 }
                 if (kt) kt->tick(KT_SHADE, st);
                 ShadeIo io;
                 io.queue_in = q_in; io.counters = wb.counters; io.queue_out = wb.queue[(b + 1u) & 1u];
-                io.ray = wb.ray; io.hit = wb.hit; io.mask_z = wb.mask_z; io.accu = wb.accu;
+                io.ray_in = ray_in; io.ray_out = ray_out; io.mask_in = mask_in; io.mask_out = mask_out; io.hit = wb.hit; io.accu = wb.accu;
                 if (p.flags & RP_FAST) {
                     if (b == 0) k_wf_shade<true, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, stats);
                     else k_wf_shade<false, true><<<sgrid, 256, 0, st>>>(sc, gen, b, io, stats);

@@ -233,7 +233,7 @@ GPT_API int gpt_render(gpt_ctx* ctx, const gpt_kernel_info* info, float* accum_f
 /* gpt_render without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
  * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same contract, same
  * samples and bit-identical sums as gpt_render on the wavefront pipeline, but the pipeline's scratch (per-path state of one wave,
- * per-pixel sums, queue counters) is a fixed file-scope device array inside the library instead of buffers grown on demand: 21 MiB
+ * per-pixel sums, queue counters) is a fixed file-scope device array inside the library instead of buffers grown on demand: 30 MiB
  * that EVERY GPU that loads the library holds until the process exits.  Limits, checked on entry (GPT_ERR_INVALID and a message
  * from gpt_last_error_string beyond them; use gpt_render there):
  *     info->width * info->height <= GPT_STATIC_MAX_PIXELS (262 144, e.g. 512 x 512);  info->depth <= GPT_STATIC_MAX_DEPTH (64);
