@@ -348,6 +348,7 @@ k_split_build(const float4* __restrict__ nodes_old, const int n_inner, const flo
                 }
             }
         }
+        if (n > 1 && best_axis < 0) { best_axis = 0; best_k = a + n / 2; }          // no finite cost (non-finite vertices): any valid cut keeps the tree well-formed
         // SplitBVHBuilder.cpp:142: a leaf where the leaf's SAH is the minimum AND it is small enough
         const bool leaf = n == 1 || (n <= max_leaf && !(parent_area + best < parent_area * (float)n));
         if (leaf) {
