@@ -239,8 +239,9 @@ GPT_API int gpt_render(gpt_ctx* ctx, const gpt_kernel_info* info, float* accum_f
  *     info->width * info->height <= GPT_STATIC_MAX_PIXELS (262 144, e.g. 512 x 512);  info->depth <= GPT_STATIC_MAX_DEPTH (64);
  *     any sample_count: calls of more than GPT_STATIC_MAX_PATHS (262 144) paths run as several waves.
  * The scene must have been uploaded before (gpt_upload_scene / gpt_set_triangle_materials are the set-up calls and do allocate);
- * BVH pointers in info->bvhData are ignored (packing them allocates), info->sphereTex is read live as in gpt_render.  The binary
- * tree is traversed unless an earlier gpt_render call already built the 4-wide tree and chose it; no timed trial, no ray
+ * BVH pointers in info->bvhData are ignored (packing them allocates), info->sphereTex is read live as in gpt_render.  The tree
+ * in use is traversed (gpt_tree_info: as uploaded until a trial of earlier gpt_render / gpt_launch calls has chosen another; the
+ * 4-wide tree only if such a call already built it); the call itself takes part in no timed trial, no ray
  * re-ordering, no per-kernel timing.  The call itself makes no cudaMalloc / cudaFree and never synchronises; the first call on
  * each device resolves the array's device address (cudaGetSymbolAddress), so make one call before capturing.
  * SHARED STATE: all calls on a device share the array, whichever context they come through.  It keeps the last call's contents;
